@@ -1,0 +1,738 @@
+// mcp_abi.cu -- the C ABI (include/mcp_b200.h) and the host-side orchestration of the kernels.
+//
+//   K0 prep.cuh        row / query norms, penalty statistics
+//   K1 scan_fp32.cuh   fp32 streaming distance + telemetry score            (small batches)
+//   K2 gemm_tf32.cuh   tcgen05 / TMEM TF32 distance GEMM, fused score + top-k' filter (large batches)
+//   K3 select.cuh      radix top-k' selection / list reduction
+//   K4 rescore.cuh     exact fp64 rescoring, final sort, certificate, fp64 fallback scan
+//   K5 merge.cuh       shard merge
+//   K6 kahn.cuh        batched Kahn levels
+//
+// There is no CPU implementation of any of these in the library: without a device every entry
+// point fails with MCP_ECUDA.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/mcp_b200.h"
+
+#define MCP_MAX_K_POW2 256
+#define MCP_STR2(x) #x
+#define MCP_STR(x) MCP_STR2(x)
+#include "common.cuh"
+#include "prep.cuh"
+#include "scan_fp32.cuh"
+#include "select.cuh"
+#include "rescore.cuh"
+#include "merge.cuh"
+#include "kahn.cuh"
+#include "gemm_tf32.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(e_ == cudaErrorMemoryAllocation ? MCP_ENOMEM : MCP_ECUDA, "%s:%d %s -> %s", \
+                        __FILE__, __LINE__, #call, cudaGetErrorString(e_));                        \
+    } while (0)
+#define KCHECK() CU(cudaGetLastError())
+#define KL() do { idx->stats.kernel_launches++; KCHECK(); } while (0)
+
+extern "C" const char *mcp_last_error(void) { return g_err.c_str(); }
+
+extern "C" int mcp_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" const char *mcp_build_info(void) {
+    return "mcp_b200 sm_100a nvcc " MCP_STR(__CUDACC_VER_MAJOR__) "." MCP_STR(__CUDACC_VER_MINOR__)
+           " kernels: prep_rows scan_fp32 gemm_tf32_tcgen05 select_from_scores select_from_lists rescore"
+           " finalize exact_scan exact_select merge_shards kahn_levels";
+}
+
+// ---------------------------------------------------------------------------------------------
+// device buffer that only grows
+// ---------------------------------------------------------------------------------------------
+struct Buf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return MCP_OK;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        CU(cudaMalloc(&p, want));
+        cap = want;
+        return MCP_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct mcp_index {
+    int device = 0, dim = 0, metric = 0, n_sm = 148;
+    int64_t n_rows = 0, ld = 0, id_base = 0;
+    const float *d_rows = nullptr;
+    Buf own_rows, norm2, inv_norm, penalty, consts;
+    bool has_penalty = false;
+    TableConsts h_consts{};
+    // options
+    int opt_path = MCP_PATH_AUTO, opt_kprime = 0, opt_max_fallback = 4, opt_time_coarse = 0;
+    // workspace
+    Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, exact_key, exact_row, flags,
+        exact_all, out_ids, out_scores, out_scores64, gemm_ws, q_pad;
+    int *h_status = nullptr;   // pinned: [0] certificate failures, [1] unresolved
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    bool pending = false;
+    cudaStream_t last_stream = nullptr;
+    std::vector<cudaEvent_t> ev;   // pairs bracketing coarse scans when opt_time_coarse
+    int ev_used = 0;
+    GemmPlan gemm;
+    std::mutex mu;
+    mcp_stats stats{};
+};
+
+#define SCORE_BUDGET_BYTES (512ull << 20)
+
+static int check_idx(const mcp_index *idx) { return idx ? MCP_OK : fail(MCP_EINVAL, "index handle is NULL"); }
+
+extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int metric) {
+    if (!out) return fail(MCP_EINVAL, "out is NULL");
+    if (dim < 1 || dim > 8192) return fail(MCP_EINVAL, "dim %d outside [1, 8192]", dim);
+    if (metric != MCP_METRIC_COSINE && metric != MCP_METRIC_L2) return fail(MCP_EINVAL, "unknown metric %d", metric);
+    int n = 0;
+    CU(cudaGetDeviceCount(&n));
+    if (device_id < 0 || device_id >= n) return fail(MCP_EINVAL, "device %d of %d", device_id, n);
+    CU(cudaSetDevice(device_id));
+    mcp_index *idx = new mcp_index();
+    idx->device = device_id; idx->dim = dim; idx->metric = metric;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device_id));
+    idx->n_sm = prop.multiProcessorCount;
+    if (prop.major != 10) { delete idx; return fail(MCP_ECUDA, "device %d is sm_%d%d; this library holds sm_100a code only", device_id, prop.major, prop.minor); }
+    CU(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&idx->done, cudaEventDisableTiming));
+    CU(cudaMallocHost(&idx->h_status, 4 * sizeof(int)));
+    idx->h_status[0] = idx->h_status[1] = 0;
+    int rc = idx->consts.ensure(sizeof(TableConsts));
+    if (!rc) rc = idx->flags.ensure(sizeof(int) * 4096);
+    if (rc) { delete idx; return rc; }
+    CU(cudaMemset(idx->flags.p, 0, sizeof(int) * 8));
+    *out = idx;
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_destroy(mcp_index *idx) {
+    if (!idx) return MCP_OK;
+    cudaSetDevice(idx->device);
+    cudaDeviceSynchronize();
+    Buf *bufs[] = {&idx->own_rows, &idx->norm2, &idx->inv_norm, &idx->penalty, &idx->consts, &idx->q_copy,
+                   &idx->nq2, &idx->inv_nq, &idx->qflag, &idx->scores, &idx->listsA, &idx->listsB, &idx->cntA,
+                   &idx->cntB, &idx->exact_key, &idx->exact_row, &idx->flags, &idx->exact_all, &idx->out_ids,
+                   &idx->out_scores, &idx->out_scores64, &idx->gemm_ws, &idx->q_pad};
+    for (Buf *b : bufs) b->release();
+    for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
+    if (idx->h_status) cudaFreeHost(idx->h_status);
+    if (idx->done) cudaEventDestroy(idx->done);
+    if (idx->stream) cudaStreamDestroy(idx->stream);
+    delete idx;
+    return MCP_OK;
+}
+
+extern "C" int64_t mcp_index_rows(const mcp_index *idx) { return idx ? idx->n_rows : -1; }
+
+// K0 over the adopted / loaded rows; synchronous (load time).
+static int prepare_table(mcp_index *idx, cudaStream_t st) {
+    int rc;
+    if ((rc = idx->norm2.ensure(sizeof(double) * (size_t)idx->n_rows))) return rc;
+    if ((rc = idx->inv_norm.ensure(sizeof(float) * (size_t)idx->n_rows))) return rc;
+    CU(cudaMemsetAsync(idx->consts.p, 0, sizeof(TableConsts), st));
+    unsigned blocks = (unsigned)((idx->n_rows + PREP_ROWS - 1) / PREP_ROWS);
+    prep_rows_kernel<false><<<blocks, PREP_ROWS, 0, st>>>(idx->d_rows, idx->n_rows, idx->dim, idx->ld,
+                                                          idx->norm2.as<double>(), idx->inv_norm.as<float>(),
+                                                          nullptr, idx->consts.as<TableConsts>());
+    KCHECK();
+    CU(cudaMemcpyAsync(&idx->h_consts, idx->consts.p, sizeof(TableConsts), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    idx->has_penalty = false;
+    if (idx->h_consts.bad_rows)
+        return fail(MCP_EINVAL, "%u rows hold NaN/Inf elements (pgvector rejects these at input)", idx->h_consts.bad_rows);
+    idx->gemm.valid = false;
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_rows, int64_t id_base) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    if (!rows_host || n_rows < 1) return fail(MCP_EINVAL, "rows NULL or n_rows < 1");
+    if (n_rows >= (1ll << 31) || id_base < 0 || id_base + n_rows > (1ll << 31)) return fail(MCP_EINVAL, "ids must fit int32");
+    std::lock_guard<std::mutex> lk(idx->mu);
+    CU(cudaSetDevice(idx->device));
+    int64_t ld = (idx->dim + 3) & ~3;                       // 16-byte rows; pad columns are zero
+    int rc = idx->own_rows.ensure(sizeof(float) * (size_t)n_rows * (size_t)ld);
+    if (rc) return rc;
+    if (ld != idx->dim) CU(cudaMemsetAsync(idx->own_rows.p, 0, sizeof(float) * (size_t)n_rows * (size_t)ld, idx->stream));
+    CU(cudaMemcpy2DAsync(idx->own_rows.p, sizeof(float) * ld, rows_host, sizeof(float) * idx->dim,
+                         sizeof(float) * idx->dim, (size_t)n_rows, cudaMemcpyHostToDevice, idx->stream));
+    idx->d_rows = idx->own_rows.as<float>();
+    idx->n_rows = n_rows; idx->ld = ld; idx->id_base = id_base;
+    return prepare_table(idx, idx->stream);
+}
+
+extern "C" int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, int64_t n_rows, int64_t ld,
+                                      int64_t id_base, void *stream) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    if (!rows_device || n_rows < 1) return fail(MCP_EINVAL, "rows NULL or n_rows < 1");
+    if (ld < idx->dim || (ld & 3) || (idx->dim & 3)) return fail(MCP_EINVAL, "adopt needs dim %% 4 == 0 and ld %% 4 == 0, ld >= dim");
+    if (((uintptr_t)rows_device) & 15) return fail(MCP_EINVAL, "rows must be 16-byte aligned");
+    if (n_rows >= (1ll << 31) || id_base < 0 || id_base + n_rows > (1ll << 31)) return fail(MCP_EINVAL, "ids must fit int32");
+    std::lock_guard<std::mutex> lk(idx->mu);
+    CU(cudaSetDevice(idx->device));
+    idx->own_rows.release();
+    idx->d_rows = rows_device; idx->n_rows = n_rows; idx->ld = ld; idx->id_base = id_base;
+    return prepare_table(idx, (cudaStream_t)stream);
+}
+
+static int penalty_stats(mcp_index *idx, cudaStream_t st) {
+    TableConsts *c = idx->consts.as<TableConsts>();
+    CU(cudaMemsetAsync(&c->pen_max, 0, 3 * sizeof(unsigned int), st));   // pen_max, pen_absmax, bad_pen
+    penalty_stats_kernel<<<idx->n_sm * 4, 256, 0, st>>>(idx->penalty.as<float>(), idx->n_rows, c);
+    KCHECK();
+    penalty_stats_finish_kernel<<<1, 1, 0, st>>>(c);
+    KCHECK();
+    CU(cudaMemcpyAsync(&idx->h_consts, c, sizeof(TableConsts), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (idx->h_consts.bad_pen) {
+        idx->has_penalty = false;
+        return fail(MCP_EINVAL, "penalty holds %u NaN/Inf values", idx->h_consts.bad_pen);
+    }
+    idx->has_penalty = true;
+    return MCP_OK;
+}
+
+static int clear_penalty(mcp_index *idx, cudaStream_t st) {
+    idx->has_penalty = false;
+    TableConsts *c = idx->consts.as<TableConsts>();
+    CU(cudaMemsetAsync(&c->pen_max, 0, 3 * sizeof(unsigned int), st));
+    CU(cudaStreamSynchronize(st));
+    idx->h_consts.pen_max = idx->h_consts.pen_absmax = 0.f;
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_set_penalty(mcp_index *idx, const float *penalty_host) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!idx->n_rows) return fail(MCP_ESTATE, "set_penalty before load");
+    CU(cudaSetDevice(idx->device));
+    if (idx->pending) { CU(cudaEventSynchronize(idx->done)); }
+    idx->last_stream = idx->stream;
+    if (!penalty_host) return clear_penalty(idx, idx->stream);
+    int rc = idx->penalty.ensure(sizeof(float) * (size_t)idx->n_rows);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(idx->penalty.p, penalty_host, sizeof(float) * (size_t)idx->n_rows, cudaMemcpyHostToDevice, idx->stream));
+    return penalty_stats(idx, idx->stream);
+}
+
+extern "C" int mcp_index_set_penalty_device(mcp_index *idx, const float *penalty_device, void *stream) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!idx->n_rows) return fail(MCP_ESTATE, "set_penalty before load");
+    CU(cudaSetDevice(idx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (idx->pending && idx->last_stream != st) { CU(cudaEventSynchronize(idx->done)); }
+    if (!penalty_device) return clear_penalty(idx, st);
+    int rc = idx->penalty.ensure(sizeof(float) * (size_t)idx->n_rows);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(idx->penalty.p, penalty_device, sizeof(float) * (size_t)idx->n_rows, cudaMemcpyDeviceToDevice, st));
+    return penalty_stats(idx, st);
+}
+
+extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t value) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    if (!name) return fail(MCP_EINVAL, "option name is NULL");
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!strcmp(name, "path")) {
+        if (value < MCP_PATH_AUTO || value > MCP_PATH_EXACT_FP64) return fail(MCP_EINVAL, "path %lld", (long long)value);
+        idx->opt_path = (int)value;
+    } else if (!strcmp(name, "kprime")) {
+        if (value < 0 || value > FINAL_MAX) return fail(MCP_EINVAL, "kprime %lld outside [0, %d]", (long long)value, FINAL_MAX);
+        idx->opt_kprime = (int)value;
+    } else if (!strcmp(name, "max_fallback")) {
+        if (value < 1 || value > 64) return fail(MCP_EINVAL, "max_fallback %lld outside [1, 64]", (long long)value);
+        idx->opt_max_fallback = (int)value;
+    } else if (!strcmp(name, "time_coarse")) {
+        idx->opt_time_coarse = value != 0;
+    } else
+        return fail(MCP_EINVAL, "unknown option '%s'", name);
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_get_stats(mcp_index *idx, mcp_stats *out) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    if (!out) return fail(MCP_EINVAL, "out is NULL");
+    std::lock_guard<std::mutex> lk(idx->mu);
+    *out = idx->stats;
+    return MCP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// search
+// ---------------------------------------------------------------------------------------------
+__global__ void status_accumulate_kernel(int *n_flag, int *status, int max_fallback) {
+    int f = *n_flag;
+    status[0] += f;
+    status[1] += f > max_fallback ? f - max_fallback : 0;
+    *n_flag = 0;
+}
+__global__ void flag_all_kernel(int *flag_list, int *n_flag, int q0, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag_list[i] = q0 + i;
+    if (i == 0) *n_flag = n;
+}
+__global__ void clear_flag_kernel(int *n_flag) { *n_flag = 0; }
+__global__ void pad_queries_kernel(const float *q, int dim, int dimp, float *out) {
+    for (int i = threadIdx.x; i < dimp; i += blockDim.x)
+        out[(int64_t)blockIdx.x * dimp + i] = i < dim ? q[(int64_t)blockIdx.x * dim + i] : 0.f;
+}
+
+// add finished coarse-scan event pairs to the stats (blocks on the last one)
+static int harvest_events(mcp_index *idx) {
+    for (int i = 0; i + 1 < idx->ev_used; i += 2) {
+        CU(cudaEventSynchronize(idx->ev[i + 1]));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, idx->ev[i], idx->ev[i + 1]));
+        idx->stats.coarse_ms += ms;
+        idx->stats.coarse_timed++;
+    }
+    idx->ev_used = 0;
+    return MCP_OK;
+}
+static int coarse_event(mcp_index *idx, cudaStream_t st) {
+    if (!idx->opt_time_coarse) return MCP_OK;
+    if (idx->ev_used == (int)idx->ev.size()) {
+        if (idx->ev.size() >= 512 && (idx->ev_used & 1) == 0) { int rc = harvest_events(idx); if (rc) return rc; }
+        else { cudaEvent_t e; CU(cudaEventCreate(&e)); idx->ev.push_back(e); }
+    }
+    CU(cudaEventRecord(idx->ev[idx->ev_used++], st));
+    return MCP_OK;
+}
+// the workspace is shared by all searches of an index: same-stream calls queue, others wait
+static int order_after_previous(mcp_index *idx, cudaStream_t st) {
+    if (idx->pending && idx->last_stream != st) CU(cudaEventSynchronize(idx->done));
+    idx->last_stream = st;
+    return MCP_OK;
+}
+
+static int pow2_at_least(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+template <int QT, int NJ>
+static cudaError_t launch_scan(int metric, int grid, size_t smem, cudaStream_t st, const float *rows, int64_t n, int dim,
+                               int64_t ld, const float *q, const float *inv_nq, const float *inv_ne, const float *pen,
+                               float *scores, int64_t stride, int nvalid) {
+    if (metric == 0) {
+        cudaFuncSetAttribute(scan_fp32_kernel<QT, NJ, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        scan_fp32_kernel<QT, NJ, 0><<<grid, SCAN_THREADS, smem, st>>>(rows, n, dim, ld, q, inv_nq, inv_ne, pen, scores, stride, nvalid);
+    } else {
+        cudaFuncSetAttribute(scan_fp32_kernel<QT, NJ, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        scan_fp32_kernel<QT, NJ, 1><<<grid, SCAN_THREADS, smem, st>>>(rows, n, dim, ld, q, inv_nq, inv_ne, pen, scores, stride, nvalid);
+    }
+    return cudaGetLastError();
+}
+
+// K1 over one pass of up to 8 queries
+static int run_scan_pass(mcp_index *idx, cudaStream_t st, const float *q, int dim, const float *inv_nq, int nvalid,
+                         float *scores, int64_t stride) {
+    int qt = nvalid <= 1 ? 1 : nvalid <= 2 ? 2 : nvalid <= 4 ? 4 : 8;
+    if (nvalid > qt) return fail(MCP_EINVAL, "internal: scan pass of %d > %d", nvalid, qt);
+    size_t smem = (size_t)qt * dim * 4;
+    if (smem > 200 * 1024) return fail(MCP_EINVAL, "internal: scan pass needs %zu bytes of shared memory", smem);
+    int per_sm = qt >= 8 ? 2 : 4;
+    int64_t want = (idx->n_rows + (SCAN_THREADS / 32) - 1) / (SCAN_THREADS / 32);
+    int grid = (int)std::min<int64_t>((int64_t)idx->n_sm * per_sm, want);
+    const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
+    const float *inv_ne = idx->inv_norm.as<float>();
+    bool nj12 = dim == 1536;
+    cudaError_t e;
+#define SCAN_CASE(QT)                                                                                               \
+    e = nj12 ? launch_scan<QT, 12>(idx->metric, grid, smem, st, idx->d_rows, idx->n_rows, dim, idx->ld, q, inv_nq, \
+                                   inv_ne, pen, scores, stride, nvalid)                                             \
+             : launch_scan<QT, 0>(idx->metric, grid, smem, st, idx->d_rows, idx->n_rows, dim, idx->ld, q, inv_nq, \
+                                  inv_ne, pen, scores, stride, nvalid)
+    switch (qt) {
+        case 1: SCAN_CASE(1); break;
+        case 2: SCAN_CASE(2); break;
+        case 4: SCAN_CASE(4); break;
+        default: SCAN_CASE(8); break;
+    }
+#undef SCAN_CASE
+    if (e != cudaSuccess) return fail(MCP_ECUDA, "scan_fp32 launch: %s", cudaGetErrorString(e));
+    idx->stats.kernel_launches++;
+    return MCP_OK;
+}
+
+// reduce [nq][L][cap] lists until one list per query is left; returns the final buffers
+static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64 *in, int *in_cnt, int L, int cap,
+                        bool in_is_A, u64 **out_keys, int **out_cnt, int *out_stride) {
+    int rc;
+    bool first = true;
+    while (L > 1 || first) {
+        if (L == 1 && cap <= kprime) break;       // already one list of at most k' keys
+        first = false;
+        int G = std::max(1, SEL_MAX / cap);
+        int L_out = (L + G - 1) / G;
+        Buf &ob = in_is_A ? idx->listsB : idx->listsA;
+        Buf &oc = in_is_A ? idx->cntB : idx->cntA;
+        if ((rc = ob.ensure(sizeof(u64) * (size_t)nq * L_out * kprime))) return rc;
+        if ((rc = oc.ensure(sizeof(int) * (size_t)nq * L_out))) return rc;
+        select_from_lists_kernel<<<dim3(L_out, nq), SEL_THREADS, 0, st>>>(in, in_cnt, L, cap, G, kprime, ob.as<u64>(),
+                                                                          oc.as<int>(), kprime);
+        KL();
+        in = ob.as<u64>(); in_cnt = oc.as<int>(); L = L_out; cap = kprime; in_is_A = !in_is_A;
+    }
+    *out_keys = in; *out_cnt = in_cnt; *out_stride = cap;
+    return MCP_OK;
+}
+
+static int choose_kprime(const mcp_index *idx, int k) {
+    int kp = idx->opt_kprime ? std::max(idx->opt_kprime, k) : std::max(2 * k, k + 32);
+    kp = (kp + 31) & ~31;
+    return std::min(kp, FINAL_MAX);
+}
+
+static int choose_path(const mcp_index *idx, int nq) {
+    if (idx->h_consts.odd_rows) return MCP_PATH_EXACT_FP64;   // rows the fp32 coarse pass cannot bound
+    if (idx->opt_path != MCP_PATH_AUTO) return idx->opt_path;
+    return (nq >= 8 && gemm_supported(idx->dim, idx->ld)) ? MCP_PATH_GEMM_TF32 : MCP_PATH_STREAM_FP32;
+}
+
+// fp64 scan + exact select for flagged slots [slot0, slot0 + slots)
+static int run_exact(mcp_index *idx, cudaStream_t st, const float *d_q, const double *nq2, int k, int slots,
+                     int32_t *out_ids, float *out_scores, double *out_scores64) {
+    int rc;
+    if ((rc = idx->exact_all.ensure(sizeof(u64) * (size_t)slots * (size_t)idx->n_rows))) return rc;
+    int *flag_list = idx->flags.as<int>() + 8, *n_flag = idx->flags.as<int>();
+    const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
+    int64_t want = (idx->n_rows + 255) / 256;
+    int gx = (int)std::min<int64_t>((int64_t)idx->n_sm * 8, want);
+    exact_scan_kernel<<<dim3(gx, slots), 256, sizeof(float) * idx->dim, st>>>(
+        idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen,
+        idx->metric, flag_list, n_flag, 0, idx->exact_all.as<u64>());
+    KL();
+    exact_select_kernel<<<slots, EXSEL_THREADS, 0, st>>>(idx->exact_all.as<u64>(), idx->n_rows, k, idx->id_base,
+                                                         flag_list, n_flag, 0, out_ids, out_scores, out_scores64);
+    KL();
+    return MCP_OK;
+}
+
+static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_t *out_ids, float *out_scores,
+                         double *out_scores64, cudaStream_t st) {
+    int rc;
+    const int dim = idx->dim;
+    const int64_t n = idx->n_rows;
+    const int path = choose_path(idx, nq);
+    const int kprime = choose_kprime(idx, k);
+    const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
+
+    if ((rc = idx->nq2.ensure(sizeof(double) * nq))) return rc;
+    if ((rc = idx->inv_nq.ensure(sizeof(float) * nq))) return rc;
+    if ((rc = idx->qflag.ensure(nq))) return rc;
+    if ((size_t)(nq + 8) * sizeof(int) > idx->flags.cap) return fail(MCP_EINVAL, "n_queries %d exceeds the flag buffer", nq);
+    // flags: [0] n_flag (zero between kernels) [1] certificate failures [2] unresolved (both since last sync_status) [8..] list
+    int *n_flag = idx->flags.as<int>(), *status = n_flag + 1, *flag_list = n_flag + 8;
+    prep_rows_kernel<true><<<(nq + PREP_ROWS - 1) / PREP_ROWS, PREP_ROWS, 0, st>>>(
+        d_q, nq, dim, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), nullptr);
+    KL();
+
+    idx->stats.searches++; idx->stats.queries += nq; idx->stats.last_path = path; idx->stats.last_kprime = kprime;
+
+    if (path == MCP_PATH_EXACT_FP64) {
+        const int slots = idx->opt_max_fallback;
+        for (int q0 = 0; q0 < nq; q0 += slots) {
+            int c = std::min(slots, nq - q0);
+            flag_all_kernel<<<(c + 127) / 128, 128, 0, st>>>(flag_list, n_flag, q0, c);
+            KL();
+            if ((rc = run_exact(idx, st, d_q, idx->nq2.as<double>(), k, c, out_ids, out_scores, out_scores64))) return rc;
+        }
+        clear_flag_kernel<<<1, 1, 0, st>>>(n_flag);
+        KL();
+        idx->stats.exact_scans += nq;
+        return MCP_OK;
+    }
+
+    // query chunking keeps the K1 score matrix within budget; K2 needs no score matrix
+    int chunk = nq;
+    if (path == MCP_PATH_STREAM_FP32)
+        chunk = (int)std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(SCORE_BUDGET_BYTES / (4ull * (size_t)n))));
+    const int kc = (int)std::min<int64_t>(kprime, n);
+    if ((rc = idx->exact_key.ensure(sizeof(u64) * (size_t)chunk * kprime))) return rc;
+    if ((rc = idx->exact_row.ensure(sizeof(int) * (size_t)chunk * kprime))) return rc;
+
+    CertParams cp;
+    cp.metric = idx->metric; cp.path = path; cp.complete = (n <= kprime);
+    const double u = 5.9604644775390625e-08;   // 2^-24
+    if (path == MCP_PATH_STREAM_FP32) cp.rel = 2.0 * (dim / 32.0 + 16.0) * u;
+    else cp.rel = 1.02 * 0.001953125 + dim * 4.0 * u;      // TF32 truncation of both operands (2^-9) + fp32 accumulation
+    cp.abs_pen = 8.0 * u;
+
+    for (int q0 = 0; q0 < nq; q0 += chunk) {
+        const int cq = std::min(chunk, nq - q0);
+        const float *dq = d_q + (int64_t)q0 * dim;
+        u64 *cand; int *cand_cnt; int cand_stride;
+        if ((rc = coarse_event(idx, st))) return rc;
+        if (path == MCP_PATH_STREAM_FP32) {
+            // the scan reads 128-bit words: rows are padded to ld by load(); queries get the same zero padding
+            const int dimp = (dim + 3) & ~3;
+            const float *dqs = dq;
+            if (dimp != dim) {
+                if ((rc = idx->q_pad.ensure(sizeof(float) * (size_t)cq * dimp))) return rc;
+                pad_queries_kernel<<<cq, 128, 0, st>>>(dq, dim, dimp, idx->q_pad.as<float>());
+                KL();
+                dqs = idx->q_pad.as<float>();
+            }
+            if ((rc = idx->scores.ensure(sizeof(float) * (size_t)cq * (size_t)n))) return rc;
+            int qt_max = 8;
+            while (qt_max > 1 && (size_t)qt_max * dimp * 4 > 160 * 1024) qt_max >>= 1;
+            for (int p = 0; p < cq; p += qt_max) {
+                int nv = std::min(qt_max, cq - p);
+                if ((rc = run_scan_pass(idx, st, dqs + (int64_t)p * dimp, dimp, idx->inv_nq.as<float>() + q0 + p, nv,
+                                        idx->scores.as<float>() + (int64_t)p * n, n)))
+                    return rc;
+            }
+            if ((rc = coarse_event(idx, st))) return rc;
+            int P = (int)((n + SEL_MAX - 1) / SEL_MAX);
+            if ((rc = idx->listsA.ensure(sizeof(u64) * (size_t)cq * P * kprime))) return rc;
+            if ((rc = idx->cntA.ensure(sizeof(int) * (size_t)cq * P))) return rc;
+            select_from_scores_kernel<<<dim3(P, cq), SEL_THREADS, 0, st>>>(idx->scores.as<float>(), n, n, kprime,
+                                                                          idx->listsA.as<u64>(), idx->cntA.as<int>(), kprime);
+            KL();
+            if ((rc = reduce_lists(idx, st, cq, kprime, idx->listsA.as<u64>(), idx->cntA.as<int>(), P, kprime, true,
+                                   &cand, &cand_cnt, &cand_stride)))
+                return rc;
+        } else {
+            int L, cap; u64 *lists; int *cnts;
+            if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, idx->d_rows, n, dim, idx->ld, dq, cq,
+                                    idx->inv_nq.as<float>() + q0, idx->nq2.as<double>() + q0, idx->inv_norm.as<float>(),
+                                    idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap)))
+                return rc;
+            if ((rc = coarse_event(idx, st))) return rc;
+            // the GEMM's lists live in gemm_ws; reductions ping-pong between listsA / listsB
+            if (L == 1 && cap <= kprime) { cand = lists; cand_cnt = cnts; cand_stride = cap; }
+            else if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride)))
+                return rc;
+        }
+        rescore_kernel<<<dim3((cand_stride + RESCORE_THREADS - 1) / RESCORE_THREADS, cq), RESCORE_THREADS,
+                         sizeof(float) * dim, st>>>(idx->d_rows, dim, idx->ld, dq, idx->nq2.as<double>() + q0,
+                                                    idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt,
+                                                    cand_stride, idx->exact_key.as<u64>(), idx->exact_row.as<int>());
+        KL();
+        finalize_kernel<<<cq, FINAL_THREADS, 0, st>>>(
+            idx->exact_key.as<u64>(), idx->exact_row.as<int>(), cand, cand_cnt, cand_stride,
+            pow2_at_least(std::max(std::min(cand_stride, kprime), 2)), k, idx->id_base, idx->nq2.as<double>() + q0,
+            idx->qflag.as<unsigned char>() + q0, idx->consts.as<TableConsts>(), cp, out_ids + (int64_t)q0 * k,
+            out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag);
+        KL();
+        // certificate failures: fp64 scan on the device, flag_list holds chunk-local query numbers
+        if ((rc = run_exact(idx, st, dq, idx->nq2.as<double>() + q0, k, idx->opt_max_fallback, out_ids + (int64_t)q0 * k, out_scores + (int64_t)q0 * k,
+                            out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr)))
+            return rc;
+        status_accumulate_kernel<<<1, 1, 0, st>>>(n_flag, status, idx->opt_max_fallback);
+        KL();
+        idx->stats.rows_scanned += n;
+        idx->stats.bytes_scanned += n * (int64_t)dim * 4;
+        idx->stats.candidates_rescored += (int64_t)cq * kc;
+    }
+    return MCP_OK;
+}
+
+static int validate_search(const mcp_index *idx, const void *q, int nq, int k, const void *ids, const void *sc) {
+    if (!idx->n_rows) return fail(MCP_ESTATE, "search before load");
+    if (!q || !ids || !sc) return fail(MCP_EINVAL, "NULL buffer");
+    if (nq < 1 || nq > 4000) return fail(MCP_EINVAL, "n_queries %d outside [1, 4000]", nq);
+    if (k < 1 || k > MCP_MAX_K) return fail(MCP_EINVAL, "k %d outside [1, %d]", k, MCP_MAX_K);
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_search_device(mcp_index *idx, const float *queries_device, int n_queries, int k,
+                                       int32_t *out_ids_device, float *out_scores_device,
+                                       double *out_scores64_device, void *stream) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    int rc = validate_search(idx, queries_device, n_queries, k, out_ids_device, out_scores_device);
+    if (rc) return rc;
+    CU(cudaSetDevice(idx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if ((rc = order_after_previous(idx, st))) return rc;
+    rc = search_locked(idx, queries_device, n_queries, k, out_ids_device, out_scores_device, out_scores64_device, st);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(idx->h_status, idx->flags.as<int>() + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(idx->done, st));
+    idx->pending = true;
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_failures, int32_t *n_unresolved) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    CU(cudaSetDevice(idx->device));
+    int fails = 0, unresolved = 0;
+    if (idx->pending) {
+        CU(cudaEventSynchronize(idx->done));
+        idx->pending = false;
+        fails = idx->h_status[0]; unresolved = idx->h_status[1];
+        idx->stats.certificate_failures += fails;
+        idx->stats.exact_scans += fails - unresolved;
+        CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), idx->last_stream));
+        CU(cudaStreamSynchronize(idx->last_stream));
+    }
+    int rc = harvest_events(idx);
+    if (rc) return rc;
+    if (n_certificate_failures) *n_certificate_failures = fails;
+    if (n_unresolved) *n_unresolved = unresolved;
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n_queries, int k, int32_t *out_ids,
+                                float *out_scores, double *out_scores64) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::unique_lock<std::mutex> lk(idx->mu);
+    int rc = validate_search(idx, queries_host, n_queries, k, out_ids, out_scores);
+    if (rc) return rc;
+    CU(cudaSetDevice(idx->device));
+    cudaStream_t st = idx->stream;
+    if (idx->pending) {   // fold an unfinished search_device into the stats first: this call reports only its own status
+        CU(cudaEventSynchronize(idx->done));
+        idx->pending = false;
+        idx->stats.certificate_failures += idx->h_status[0];
+        idx->stats.exact_scans += idx->h_status[0] - idx->h_status[1];
+    }
+    CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
+    idx->last_stream = st;
+    const size_t nk = (size_t)n_queries * k;
+    if ((rc = idx->q_copy.ensure(sizeof(float) * (size_t)n_queries * idx->dim))) return rc;
+    if ((rc = idx->out_ids.ensure(sizeof(int32_t) * nk))) return rc;
+    if ((rc = idx->out_scores.ensure(sizeof(float) * nk))) return rc;
+    if ((rc = idx->out_scores64.ensure(sizeof(double) * nk))) return rc;
+    CU(cudaMemcpyAsync(idx->q_copy.p, queries_host, sizeof(float) * (size_t)n_queries * idx->dim, cudaMemcpyHostToDevice, st));
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        int saved = idx->opt_path;
+        if (attempt == 1) idx->opt_path = MCP_PATH_EXACT_FP64;      // leftovers beyond the device-side fallback slots
+        rc = search_locked(idx, idx->q_copy.as<float>(), n_queries, k, idx->out_ids.as<int32_t>(),
+                           idx->out_scores.as<float>(), idx->out_scores64.as<double>(), st);
+        idx->opt_path = saved;
+        if (rc) return rc;
+        CU(cudaMemcpyAsync(idx->h_status, idx->flags.as<int>() + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (attempt == 0) {
+            idx->stats.certificate_failures += idx->h_status[0];
+            idx->stats.exact_scans += idx->h_status[0] - idx->h_status[1];
+        }
+        CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
+        if (idx->h_status[1] == 0) break;
+    }
+    CU(cudaMemcpyAsync(out_ids, idx->out_ids.p, sizeof(int32_t) * nk, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(out_scores, idx->out_scores.p, sizeof(float) * nk, cudaMemcpyDeviceToHost, st));
+    if (out_scores64) CU(cudaMemcpyAsync(out_scores64, idx->out_scores64.p, sizeof(double) * nk, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return MCP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// shard merge
+// ---------------------------------------------------------------------------------------------
+extern "C" int mcp_merge_topk_device(const double *scores64_device, const int32_t *ids_device, int n_shards,
+                                     int n_queries, int k, int32_t *out_ids_device, float *out_scores_device,
+                                     double *out_scores64_device, void *stream) {
+    if (!scores64_device || !ids_device || !out_ids_device || !out_scores_device) return fail(MCP_EINVAL, "NULL buffer");
+    if (n_shards < 1 || n_queries < 1 || k < 1 || k > MCP_MAX_K) return fail(MCP_EINVAL, "bad sizes");
+    if ((int64_t)n_shards * k > MERGE_MAX) return fail(MCP_EINVAL, "n_shards * k = %d exceeds %d", n_shards * k, MERGE_MAX);
+    int npow2 = pow2_at_least(std::max(n_shards * k, 2));
+    size_t smem = (size_t)npow2 * (sizeof(u64) + sizeof(int));
+    CU(cudaFuncSetAttribute(merge_shards_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    merge_shards_kernel<<<n_queries, MERGE_THREADS, smem, (cudaStream_t)stream>>>(
+        scores64_device, ids_device, n_shards, n_queries, k, npow2, out_ids_device, out_scores_device, out_scores64_device);
+    KCHECK();
+    return MCP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// DAG levels
+// ---------------------------------------------------------------------------------------------
+extern "C" int mcp_dag_levels_device(const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
+                                     int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels,
+                                     uint8_t *out_status, void *stream) {
+    if (!n_nodes || !edge_off || !out_level || !out_n_levels || !out_status) return fail(MCP_EINVAL, "NULL buffer");
+    if (n_dags < 0) return fail(MCP_EINVAL, "n_dags < 0");
+    if (n_dags == 0) return MCP_OK;
+    if (((uintptr_t)edges) & 1) return fail(MCP_EINVAL, "edges must be 2-byte aligned");
+    int dev = 0, n_sm = 148;
+    CU(cudaGetDevice(&dev));
+    CU(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+    int64_t want = (n_dags + KAHN_WARPS - 1) / KAHN_WARPS;
+    int grid = (int)std::min<int64_t>((int64_t)n_sm * 8, want);
+    if (out_order)
+        kahn_levels_kernel<true><<<grid, KAHN_THREADS, 0, (cudaStream_t)stream>>>(n_nodes, edge_off, edges, n_dags, out_level,
+                                                                                 out_order, out_n_levels, out_status);
+    else
+        kahn_levels_kernel<false><<<grid, KAHN_THREADS, 0, (cudaStream_t)stream>>>(n_nodes, edge_off, edges, n_dags, out_level,
+                                                                                  nullptr, out_n_levels, out_status);
+    KCHECK();
+    return MCP_OK;
+}
+
+extern "C" int mcp_dag_levels(int device_id, const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
+                              int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels,
+                              uint8_t *out_status) {
+    if (!n_nodes || !edge_off || !out_level || !out_n_levels || !out_status) return fail(MCP_EINVAL, "NULL buffer");
+    if (n_dags < 0) return fail(MCP_EINVAL, "n_dags < 0");
+    if (n_dags == 0) return MCP_OK;
+    for (int64_t b = 0; b < n_dags; ++b) {
+        if (n_nodes[b] > MCP_MAX_DAG_NODES) return fail(MCP_EINVAL, "DAG %lld has %d nodes (max %d)", (long long)b, n_nodes[b], MCP_MAX_DAG_NODES);
+        if (edge_off[b + 1] < edge_off[b]) return fail(MCP_EINVAL, "edge_off not monotone at %lld", (long long)b);
+    }
+    size_t n_edges = edge_off[n_dags];
+    if (n_edges && !edges) return fail(MCP_EINVAL, "edges is NULL");
+    CU(cudaSetDevice(device_id));
+    Buf dn, doff, de, dl, dord, dnl, dst;
+    int rc = MCP_OK;
+    cudaStream_t st = nullptr;
+    auto cleanup = [&]() { dn.release(); doff.release(); de.release(); dl.release(); dord.release(); dnl.release(); dst.release(); };
+#define TRY(x) do { rc = (x); if (rc) { cleanup(); return rc; } } while (0)
+#define CUT(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(MCP_ECUDA, "%s -> %s", #x, cudaGetErrorString(e_)); } } while (0)
+    TRY(dn.ensure((size_t)n_dags)); TRY(doff.ensure(sizeof(uint32_t) * (size_t)(n_dags + 1))); TRY(de.ensure(2 * n_edges + 2));
+    TRY(dl.ensure((size_t)n_dags * 64)); TRY(dnl.ensure((size_t)n_dags)); TRY(dst.ensure((size_t)n_dags));
+    if (out_order) TRY(dord.ensure((size_t)n_dags * 64));
+    CUT(cudaMemcpyAsync(dn.p, n_nodes, (size_t)n_dags, cudaMemcpyHostToDevice, st));
+    CUT(cudaMemcpyAsync(doff.p, edge_off, sizeof(uint32_t) * (size_t)(n_dags + 1), cudaMemcpyHostToDevice, st));
+    if (n_edges) CUT(cudaMemcpyAsync(de.p, edges, 2 * n_edges, cudaMemcpyHostToDevice, st));
+    TRY(mcp_dag_levels_device(dn.as<uint8_t>(), doff.as<uint32_t>(), de.as<uint8_t>(), n_dags, dl.as<uint8_t>(),
+                              out_order ? dord.as<uint8_t>() : nullptr, dnl.as<uint8_t>(), dst.as<uint8_t>(), st));
+    CUT(cudaMemcpyAsync(out_level, dl.p, (size_t)n_dags * 64, cudaMemcpyDeviceToHost, st));
+    if (out_order) CUT(cudaMemcpyAsync(out_order, dord.p, (size_t)n_dags * 64, cudaMemcpyDeviceToHost, st));
+    CUT(cudaMemcpyAsync(out_n_levels, dnl.p, (size_t)n_dags, cudaMemcpyDeviceToHost, st));
+    CUT(cudaMemcpyAsync(out_status, dst.p, (size_t)n_dags, cudaMemcpyDeviceToHost, st));
+    CUT(cudaStreamSynchronize(st));
+    cleanup();
+#undef TRY
+#undef CUT
+    return MCP_OK;
+}

@@ -1,0 +1,270 @@
+// rescore.cuh -- K4: exact rescoring of the oversampled candidates, final (score,id) sort,
+// exactness certificate, and the fp64 full scan the certificate falls back to.
+//
+// Why: ids must be bit-exact against the fp64 oracle, but the coarse scans (fp32 tree sums,
+// TF32 tensor-core products) order near neighbours differently.  So the coarse pass keeps
+// k' > k candidates, this stage recomputes their scores with the oracle's own arithmetic
+// (common.cuh exact_*), sorts by (score, id) and takes k.  The certificate then proves no row
+// outside the candidate set could have entered the top-k:
+//     every dropped row j has coarse score c_j >= T  (T = worst surviving coarse score,
+//     select.cuh invariant) and exact score s_j >= c_j - eps  (eps = coarse error bound)
+//     =>  if the k-th exact score s_(k) < T - eps the answer is the true top-k.
+// Queries that fail are re-answered by the fp64 scan, so "bit-exact" is a guarantee.
+#pragma once
+#include "common.cuh"
+#include "prep.cuh"
+
+#define RESCORE_THREADS 128
+#define FINAL_THREADS 256
+#define FINAL_MAX 512        // max k' (power of two)
+#define EXSEL_THREADS 1024
+
+struct CertParams {
+    int metric;
+    int path;              // MCP_PATH_*
+    int complete;          // candidate set == all rows: nothing was dropped
+    double rel;            // relative coarse error bound of the dot product / squared distance
+    double abs_pen;        // multiplier of pen_absmax for fp32 rounding of the final add
+};
+
+// ---- K4a: one thread per (query, candidate) ----------------------------------------------------
+// grid (ceil(kc / RESCORE_THREADS), Q). The query is staged in shared memory (broadcast reads);
+// each thread walks its own candidate row in index order.
+__global__ void __launch_bounds__(RESCORE_THREADS)
+rescore_kernel(const float *__restrict__ rows, int dim, int64_t ld,
+               const float *__restrict__ queries, const double *__restrict__ nq2,
+               const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
+               const u64 *__restrict__ cand, const int *__restrict__ cand_cnt, int cand_stride,
+               u64 *__restrict__ exact_key, int *__restrict__ exact_row) {
+    extern __shared__ float sqv[];
+    int q = blockIdx.y;
+    const float *qv = queries + (int64_t)q * dim;
+    for (int i = threadIdx.x; i < dim; i += blockDim.x) sqv[i] = qv[i];
+    __syncthreads();
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    int cnt = cand_cnt[q];
+    if (j >= cand_stride) return;
+    int64_t o = (int64_t)q * cand_stride + j;
+    if (j >= cnt) { exact_key[o] = ~0ull; exact_row[o] = MCP_PAD_ROW; return; }
+    uint32_t row = (uint32_t)(cand[o] & 0xFFFFFFFFull);
+    const float *e = rows + (int64_t)row * ld;
+    ExactAcc a; a.acc = 0.0;
+    int d4 = dim & ~3;
+    if (metric == 0) {
+        for (int i = 0; i < d4; i += 4) {
+            float4 v = *reinterpret_cast<const float4 *>(e + i);
+            a.cos_step(sqv[i], v.x); a.cos_step(sqv[i + 1], v.y);
+            a.cos_step(sqv[i + 2], v.z); a.cos_step(sqv[i + 3], v.w);
+        }
+        for (int i = d4; i < dim; ++i) a.cos_step(sqv[i], e[i]);
+    } else {
+        for (int i = 0; i < d4; i += 4) {
+            float4 v = *reinterpret_cast<const float4 *>(e + i);
+            a.l2_step(sqv[i], v.x); a.l2_step(sqv[i + 1], v.y);
+            a.l2_step(sqv[i + 2], v.z); a.l2_step(sqv[i + 3], v.w);
+        }
+        for (int i = d4; i < dim; ++i) a.l2_step(sqv[i], e[i]);
+    }
+    double s = exact_finish(a.acc, metric, nq2[q], ne2[row]);
+    if (penalty) s = s + (double)penalty[row];
+    exact_key[o] = f64_ord(s);
+    exact_row[o] = (int)row;
+}
+
+// ---- K4b: final sort + outputs + certificate; one CTA per query --------------------------------
+__global__ void __launch_bounds__(FINAL_THREADS)
+finalize_kernel(const u64 *__restrict__ exact_key, const int *__restrict__ exact_row,
+                const u64 *__restrict__ cand, const int *__restrict__ cand_cnt, int cand_stride,
+                int npow2, int k, int64_t id_base, const double *__restrict__ nq2,
+                const unsigned char *__restrict__ qflag, const TableConsts *__restrict__ consts,
+                CertParams cp, int32_t *__restrict__ out_ids, float *__restrict__ out_scores,
+                double *__restrict__ out_scores64, int *__restrict__ flag_list, int *__restrict__ n_flag) {
+    __shared__ u64 sk[FINAL_MAX];
+    __shared__ int sv[FINAL_MAX];
+    __shared__ unsigned int s_tmax;
+    int q = blockIdx.x;
+    int cnt = min(cand_cnt[q], cand_stride);
+    if (threadIdx.x == 0) s_tmax = 0;
+    __syncthreads();
+    unsigned int tmax = 0;
+    for (int i = threadIdx.x; i < npow2; i += blockDim.x) {
+        if (i < cnt) {
+            int64_t o = (int64_t)q * cand_stride + i;
+            sk[i] = exact_key[o]; sv[i] = exact_row[o];
+            tmax = max(tmax, (unsigned int)(cand[o] >> 32));
+        } else { sk[i] = ~0ull; sv[i] = MCP_PAD_ROW; }
+    }
+    atomicMax(&s_tmax, tmax);
+    cta_bitonic_sort_pairs(sk, sv, npow2);
+    for (int i = threadIdx.x; i < k; i += blockDim.x) {
+        int64_t o = (int64_t)q * k + i;
+        bool real = (i < cnt) && sv[i] != MCP_PAD_ROW;
+        double s = real ? ord_f64(sk[i]) : CUDART_INF;
+        out_ids[o] = real ? (int32_t)(id_base + sv[i]) : -1;
+        out_scores[o] = (float)s;
+        if (out_scores64) out_scores64[o] = s;
+    }
+    if (threadIdx.x == 0) {
+        bool pass;
+        if (qflag[q]) pass = false;                          // degenerate query: always the fp64 scan
+        else if (cp.complete) pass = true;
+        else if (s_tmax == 0xFFFFFFFFu) pass = true;         // worst survivor is NaN: every dropped row is NaN with a larger id
+        else if (cnt < k) pass = false;                      // cannot happen when !complete; be safe
+        else {
+            double T = (double)ord_f32(s_tmax);
+            double sk_k = ord_f64(sk[k - 1]);                // NaN if fewer than k numeric scores
+            double qn = sqrt(nq2[q]);
+            double en = sqrt(__longlong_as_double((long long)consts->max_norm2_bits));
+            double pen_abs = (double)consts->pen_absmax, pen_max = (double)consts->pen_max;
+            double eps;
+            if (cp.metric == 0) {
+                eps = cp.rel + cp.abs_pen * (2.0 + pen_abs);
+            } else if (cp.path == 2) {
+                // squared distance assembled from norms and a TF32 dot: |d2c - d2| <= delta
+                double delta = 2.0 * cp.rel * qn * en + 4.0 * 5.96e-8 * (qn + en) * (qn + en);
+                double x0 = T - pen_max; x0 = x0 > 0.0 ? x0 * x0 : 0.0;   // every dropped row has coarse d2 >= x0
+                eps = sqrt(x0) - sqrt(fmax(x0 - delta, 0.0)) + cp.abs_pen * (sqrt(x0) + pen_abs);
+            } else {
+                eps = cp.rel * (qn + en) + cp.abs_pen * ((qn + en) + pen_abs);
+            }
+            pass = (sk_k == sk_k) && (sk_k < T - eps);
+        }
+        if (!pass) flag_list[atomicAdd(n_flag, 1)] = q;
+    }
+}
+
+// ---- K4c: fp64 scan of every row for the flagged queries ---------------------------------------
+// grid (blocks, max_fallback); slot f serves query flag_list[slot0 + f]; slots past *n_flag exit.
+__global__ void __launch_bounds__(256)
+exact_scan_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64_t ld,
+                  const float *__restrict__ queries, const double *__restrict__ nq2,
+                  const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
+                  const int *__restrict__ flag_list, const int *__restrict__ n_flag, int slot0,
+                  u64 *__restrict__ exact_all /* [slots][n_rows] */) {
+    extern __shared__ float sqv[];
+    int f = blockIdx.y;
+    if (slot0 + f >= *n_flag) return;
+    int q = flag_list[slot0 + f];
+    const float *qv = queries + (int64_t)q * dim;
+    for (int i = threadIdx.x; i < dim; i += blockDim.x) sqv[i] = qv[i];
+    __syncthreads();
+    double qn2 = nq2[q];
+    u64 *out = exact_all + (int64_t)f * n_rows;
+    int d4 = dim & ~3;
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+        const float *e = rows + r * ld;
+        ExactAcc a; a.acc = 0.0;
+        if (metric == 0) {
+            for (int i = 0; i < d4; i += 4) {
+                float4 v = *reinterpret_cast<const float4 *>(e + i);
+                a.cos_step(sqv[i], v.x); a.cos_step(sqv[i + 1], v.y);
+                a.cos_step(sqv[i + 2], v.z); a.cos_step(sqv[i + 3], v.w);
+            }
+            for (int i = d4; i < dim; ++i) a.cos_step(sqv[i], e[i]);
+        } else {
+            for (int i = 0; i < d4; i += 4) {
+                float4 v = *reinterpret_cast<const float4 *>(e + i);
+                a.l2_step(sqv[i], v.x); a.l2_step(sqv[i + 1], v.y);
+                a.l2_step(sqv[i + 2], v.z); a.l2_step(sqv[i + 3], v.w);
+            }
+            for (int i = d4; i < dim; ++i) a.l2_step(sqv[i], e[i]);
+        }
+        double s = exact_finish(a.acc, metric, qn2, ne2[r]);
+        if (penalty) s = s + (double)penalty[r];
+        out[r] = f64_ord(s);
+    }
+}
+
+// ---- K4d: exact top-k of one fp64 score vector; one CTA per slot ---------------------------------
+// Radix select on the 64-bit score image (values may repeat), then rows with the boundary value
+// are taken in row order, which is the "ties -> lowest id" rule.
+__global__ void __launch_bounds__(EXSEL_THREADS)
+exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, int64_t id_base,
+                    const int *__restrict__ flag_list, const int *__restrict__ n_flag, int slot0,
+                    int32_t *__restrict__ out_ids, float *__restrict__ out_scores,
+                    double *__restrict__ out_scores64) {
+    __shared__ uint32_t hist[256];
+    __shared__ int s_digit, s_cnt, s_warp_base[EXSEL_THREADS / 32 + 1], s_taken, s_nless;
+    __shared__ long long s_need;
+    __shared__ u64 sk[MCP_MAX_K_POW2];
+    __shared__ int sv[MCP_MAX_K_POW2];
+    int f = blockIdx.x;
+    if (slot0 + f >= *n_flag) return;
+    int q = flag_list[slot0 + f];
+    const u64 *E = exact_all + (int64_t)f * n_rows;
+    int kk = (int)min((int64_t)k, n_rows);
+    u64 prefix = 0, mask = 0, thr = ~0ull;
+    long long need = kk;
+    bool whole_bin = (kk >= n_rows);
+    if (!whole_bin) {
+        for (int shift = 56; shift >= 0; shift -= 8) {
+            for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+            __syncthreads();
+            for (int64_t i = threadIdx.x; i < n_rows; i += blockDim.x) {
+                u64 key = E[i];
+                if ((key & mask) == prefix) atomicAdd(&hist[(uint32_t)(key >> shift) & 255u], 1u);
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                long long run = 0;
+                for (int d = 0; d < 256; ++d) {
+                    if (need <= run + (long long)hist[d]) { s_digit = d; s_need = need - run; s_cnt = (int)hist[d]; break; }
+                    run += hist[d];
+                }
+            }
+            __syncthreads();
+            prefix |= (u64)s_digit << shift;
+            mask |= 0xFFull << shift;
+            need = s_need;
+            if ((long long)s_cnt == need) { thr = prefix | (shift ? ((1ull << shift) - 1ull) : 0ull); whole_bin = true; break; }
+            __syncthreads();
+        }
+        if (!whole_bin) thr = prefix;    // boundary value repeats: `need` of its rows are wanted, lowest rows first
+    }
+    for (int i = threadIdx.x; i < MCP_MAX_K_POW2; i += blockDim.x) { sk[i] = ~0ull; sv[i] = MCP_PAD_ROW; }
+    if (threadIdx.x == 0) { s_nless = 0; s_taken = 0; }
+    __syncthreads();
+    // pass 1: everything strictly better than the boundary (or <= when the whole bin is taken)
+    for (int64_t i = threadIdx.x; i < n_rows; i += blockDim.x) {
+        u64 key = E[i];
+        if (whole_bin ? (key <= thr) : (key < thr)) {
+            int p = atomicAdd(&s_nless, 1);
+            sk[p] = key; sv[p] = (int)i;
+        }
+    }
+    __syncthreads();
+    if (!whole_bin) {
+        // pass 2: boundary-valued rows in row order until `need` are taken
+        int base_out = s_nless;
+        int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        for (int64_t c0 = 0; c0 < n_rows; c0 += blockDim.x) {
+            int64_t i = c0 + threadIdx.x;
+            bool hit = (i < n_rows) && (E[i] == thr);
+            unsigned int b = __ballot_sync(MCP_FULL, hit);
+            if (lane == 0) s_warp_base[warp] = __popc(b);
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                int run = s_taken;
+                for (int w = 0; w < EXSEL_THREADS / 32; ++w) { int c = s_warp_base[w]; s_warp_base[w] = run; run += c; }
+                s_taken = run;
+            }
+            __syncthreads();
+            if (hit) {
+                int p = s_warp_base[warp] + __popc(b & ((1u << lane) - 1u));
+                if (p < need) { sk[base_out + p] = thr; sv[base_out + p] = (int)i; }
+            }
+            bool done = s_taken >= need;
+            __syncthreads();
+            if (done) break;
+        }
+    }
+    cta_bitonic_sort_pairs(sk, sv, MCP_MAX_K_POW2);
+    for (int i = threadIdx.x; i < k; i += blockDim.x) {
+        int64_t o = (int64_t)q * k + i;
+        bool real = sv[i] != MCP_PAD_ROW;
+        double s = real ? ord_f64(sk[i]) : CUDART_INF;
+        out_ids[o] = real ? (int32_t)(id_base + sv[i]) : -1;
+        out_scores[o] = (float)s;
+        if (out_scores64) out_scores64[o] = s;
+    }
+}

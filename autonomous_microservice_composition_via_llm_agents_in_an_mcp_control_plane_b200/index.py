@@ -1,0 +1,176 @@
+"""``ServiceIndex`` -- the HBM-resident image of ``service_schemas.input_schema_vector``.
+
+Host face of ``mcp_index_*`` (include/mcp_b200.h).  It replaces what
+``GraphPlanner.__init__`` / ``_fetch_embeddings_metadata`` do with a pgvector connection
+(control_plane.py:46-55): rows are loaded once, then ``search`` answers
+``ORDER BY input_schema_vector <op> :q (+ penalty) LIMIT k`` exactly.
+
+Two faces of the same calls:
+  * numpy in / numpy out (``load``, ``set_penalty``, ``search``): host buffers, copies inside;
+  * torch CUDA tensors (``adopt``, ``search_device``): device pointers on the current stream,
+    nothing copied -- torch is only the allocator / stream provider here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import numpy as np
+
+from . import _native as nat
+
+_METRICS = {"cosine": nat.METRIC_COSINE, "l2": nat.METRIC_L2, 0: 0, 1: 1}
+_PATHS = {"auto": nat.PATH_AUTO, "stream_fp32": nat.PATH_STREAM_FP32, "gemm_tf32": nat.PATH_GEMM_TF32,
+          "exact_fp64": nat.PATH_EXACT_FP64}
+
+
+def _np_ptr(a: np.ndarray) -> C.c_void_p:
+    return C.c_void_p(a.ctypes.data)
+
+
+def _stream_ptr() -> C.c_void_p:
+    import torch
+
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class ServiceIndex:
+    def __init__(self, dim: int, metric="cosine", device: int = 0):
+        self._lib = nat.lib()
+        self._h = C.c_void_p()
+        self.dim, self.device = int(dim), int(device)
+        self.metric = _METRICS[metric]
+        nat.check(self._lib.mcp_index_create(C.byref(self._h), self.device, self.dim, self.metric))
+        self._keep = []  # adopted tensors must outlive the handle
+
+    # ---- lifetime -----------------------------------------------------------------------
+    def close(self) -> None:
+        if self._h:
+            self._lib.mcp_index_destroy(self._h)
+            self._h = C.c_void_p()
+            self._keep.clear()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    @property
+    def n_rows(self) -> int:
+        return int(self._lib.mcp_index_rows(self._h))
+
+    # ---- table ---------------------------------------------------------------------------
+    def load(self, rows: np.ndarray, id_base: int = 0) -> "ServiceIndex":
+        rows = np.ascontiguousarray(rows, dtype=np.float32)
+        if rows.ndim != 2 or rows.shape[1] != self.dim:
+            raise ValueError(f"rows must be [N, {self.dim}] float32, got {rows.shape}")
+        nat.check(self._lib.mcp_index_load(self._h, _np_ptr(rows), rows.shape[0], int(id_base)))
+        self._keep.clear()
+        return self
+
+    def adopt(self, rows, id_base: int = 0) -> "ServiceIndex":
+        """Use a CUDA float32 tensor [N, dim] (row stride >= dim) in place; the caller must not modify it."""
+        import torch
+
+        if not (rows.is_cuda and rows.dtype == torch.float32 and rows.dim() == 2 and rows.stride(1) == 1):
+            raise ValueError("adopt needs a CUDA float32 [N, dim] tensor with unit column stride")
+        if rows.shape[1] != self.dim or rows.device.index != self.device:
+            raise ValueError("adopt: wrong dim or device")
+        nat.check(self._lib.mcp_index_adopt_device(self._h, C.c_void_p(rows.data_ptr()), rows.shape[0],
+                                                   rows.stride(0), int(id_base), _stream_ptr()))
+        self._keep = [rows]
+        return self
+
+    def set_penalty(self, penalty) -> "ServiceIndex":
+        if penalty is None:
+            nat.check(self._lib.mcp_index_set_penalty(self._h, None))
+        elif isinstance(penalty, np.ndarray):
+            p = np.ascontiguousarray(penalty, dtype=np.float32)
+            if p.shape != (self.n_rows,):
+                raise ValueError(f"penalty must be [{self.n_rows}]")
+            nat.check(self._lib.mcp_index_set_penalty(self._h, _np_ptr(p)))
+        else:
+            import torch
+
+            if not (penalty.is_cuda and penalty.dtype == torch.float32 and penalty.is_contiguous()
+                    and tuple(penalty.shape) == (self.n_rows,)):
+                raise ValueError("penalty tensor must be contiguous CUDA float32 [N]")
+            nat.check(self._lib.mcp_index_set_penalty_device(self._h, C.c_void_p(penalty.data_ptr()), _stream_ptr()))
+        return self
+
+    # ---- search --------------------------------------------------------------------------
+    def search(self, queries: np.ndarray, k: int) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+        """Host buffers in and out: (ids int32 [Q,k], scores fp32 [Q,k], scores fp64 [Q,k])."""
+        q = np.ascontiguousarray(np.atleast_2d(queries), dtype=np.float32)
+        if q.shape[1] != self.dim:
+            raise ValueError(f"queries must be [Q, {self.dim}]")
+        nq = q.shape[0]
+        ids = np.empty((nq, k), np.int32)
+        sc = np.empty((nq, k), np.float32)
+        sc64 = np.empty((nq, k), np.float64)
+        nat.check(self._lib.mcp_index_search(self._h, _np_ptr(q), nq, int(k), _np_ptr(ids), _np_ptr(sc), _np_ptr(sc64)))
+        return ids, sc, sc64
+
+    def search_device(self, queries, k: int, out: Optional[tuple] = None):
+        """CUDA tensors in and out, enqueued on the current stream; call ``sync_status`` to learn
+        whether every answer was certified."""
+        import torch
+
+        if not (queries.is_cuda and queries.dtype == torch.float32 and queries.is_contiguous()
+                and queries.dim() == 2 and queries.shape[1] == self.dim):
+            raise ValueError("queries must be contiguous CUDA float32 [Q, dim]")
+        nq = queries.shape[0]
+        if out is None:
+            dev = queries.device
+            out = (torch.empty((nq, k), dtype=torch.int32, device=dev),
+                   torch.empty((nq, k), dtype=torch.float32, device=dev),
+                   torch.empty((nq, k), dtype=torch.float64, device=dev))
+        ids, sc, sc64 = out
+        nat.check(self._lib.mcp_index_search_device(
+            self._h, C.c_void_p(queries.data_ptr()), nq, int(k), C.c_void_p(ids.data_ptr()),
+            C.c_void_p(sc.data_ptr()), C.c_void_p(sc64.data_ptr()) if sc64 is not None else None, _stream_ptr()))
+        return ids, sc, sc64
+
+    def sync_status(self) -> Tuple[int, int]:
+        a, b = C.c_int32(), C.c_int32()
+        nat.check(self._lib.mcp_index_sync_status(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    # ---- knobs ---------------------------------------------------------------------------
+    def set_option(self, name: str, value) -> "ServiceIndex":
+        if name == "path" and isinstance(value, str):
+            value = _PATHS[value]
+        nat.check(self._lib.mcp_index_set_option(self._h, name.encode(), int(value)))
+        return self
+
+    def stats(self) -> dict:
+        s = nat.McpStats()
+        nat.check(self._lib.mcp_index_get_stats(self._h, C.byref(s)))
+        return {f: getattr(s, f) for f, _ in s._fields_}
+
+
+def merge_topk_device(scores64, ids, out: Optional[tuple] = None):
+    """[S,Q,k] per-shard sorted lists (CUDA fp64 / int32) -> global (ids, scores32, scores64)."""
+    import torch
+
+    s, q, k = ids.shape
+    if not (scores64.is_cuda and scores64.dtype == torch.float64 and scores64.is_contiguous()
+            and ids.dtype == torch.int32 and ids.is_contiguous() and tuple(scores64.shape) == (s, q, k)):
+        raise ValueError("merge needs contiguous CUDA [S,Q,k] fp64 scores and int32 ids")
+    if out is None:
+        dev = ids.device
+        out = (torch.empty((q, k), dtype=torch.int32, device=dev),
+               torch.empty((q, k), dtype=torch.float32, device=dev),
+               torch.empty((q, k), dtype=torch.float64, device=dev))
+    oi, os32, os64 = out
+    nat.check(nat.lib().mcp_merge_topk_device(C.c_void_p(scores64.data_ptr()), C.c_void_p(ids.data_ptr()), s, q, k,
+                                              C.c_void_p(oi.data_ptr()), C.c_void_p(os32.data_ptr()),
+                                              C.c_void_p(os64.data_ptr()), _stream_ptr()))
+    return oi, os32, os64

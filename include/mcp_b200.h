@@ -1,0 +1,157 @@
+/*
+ * mcp_b200.h -- C ABI of the B200-native retrieval + level-scheduling hot path.
+ *
+ * The reference (control_plane.py) has no plugin / operator / FFI interface; its seams are
+ * Python methods.  This header is the boundary a maintainer of the
+ * reference would bind with ctypes (INTEGRATION.md shows the stub).  Each entry point names
+ * the reference interface it stands behind.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative MCP_E* code on failure; the message is
+ *     available from mcp_last_error() (thread-local, valid until the next failing call on the
+ *     same thread).  No exception, no torch type, crosses this boundary.
+ *   - the caller owns every buffer it passes; the library owns the handle and all device
+ *     memory it allocates.  "host" pointers are ordinary process memory, "device" pointers are
+ *     CUDA device memory on the index's device; `stream` is a cudaStream_t passed as void*
+ *     (NULL = the legacy default stream).
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails.
+ *   - an index may be used from any thread; calls on one index serialise on an internal lock.
+ *   - ids are int32 service ids = id_base + row number; ranking key is (score, id) ascending,
+ *     NaN scores (zero vector under cosine) rank last; when k exceeds the number of rows the
+ *     tail is id -1 / score +inf.
+ */
+#ifndef MCP_B200_H
+#define MCP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCP_METRIC_COSINE 0 /* pgvector `<=>`: 1 - clamp(q.e / sqrt(|q|^2 |e|^2), -1, 1) */
+#define MCP_METRIC_L2 1     /* pgvector `<->`: sqrt(sum (q_i - e_i)^2)                    */
+
+#define MCP_OK 0
+#define MCP_EINVAL (-1)   /* bad argument (NULL, size out of range, non-finite input)    */
+#define MCP_ECUDA (-2)    /* a CUDA runtime / driver call failed                          */
+#define MCP_ESTATE (-3)   /* call order (search before load, penalty before load ...)     */
+#define MCP_ENOMEM (-4)   /* device or host allocation failed                              */
+
+#define MCP_MAX_K 256       /* largest k a search accepts                                   */
+#define MCP_MAX_DAG_NODES 64
+
+/* which coarse-scan kernel a search uses (mcp_index_set_option "path") */
+#define MCP_PATH_AUTO 0
+#define MCP_PATH_STREAM_FP32 1 /* K1: fp32 CUDA-core streaming scan                        */
+#define MCP_PATH_GEMM_TF32 2   /* K2: tcgen05 / TMEM TF32 distance GEMM                    */
+#define MCP_PATH_EXACT_FP64 3  /* full fp64 scan (the certificate's fallback, also a checker) */
+
+typedef struct mcp_index mcp_index;
+
+/* counters since creation; see mcp_index_get_stats */
+typedef struct mcp_stats {
+    int64_t searches;          /* search calls                                             */
+    int64_t queries;           /* queries answered                                         */
+    int64_t rows_scanned;      /* sum over searches of n_rows (coarse pass)                */
+    int64_t bytes_scanned;     /* rows_scanned * dim * 4                                    */
+    int64_t candidates_rescored;
+    int64_t certificate_failures; /* queries the exact-rescoring certificate sent to the fp64 scan */
+    int64_t exact_scans;       /* queries answered by the full fp64 scan                    */
+    int64_t kernel_launches;   /* kernels this library launched for searches               */
+    int64_t coarse_timed;      /* coarse-scan stages timed (option "time_coarse")           */
+    double coarse_ms;          /* sum of their CUDA-event durations, milliseconds           */
+    int32_t last_path;         /* MCP_PATH_* of the last search                            */
+    int32_t last_kprime;       /* oversampled candidate count of the last search           */
+} mcp_stats;
+
+/* ---- lifetime ------------------------------------------------------------------------------
+ * Stands where GraphPlanner.__init__ opens its pgvector connection (control_plane.py:46-49):
+ * the handle is the "connection" to the embedding table, now resident in HBM.              */
+int mcp_index_create(mcp_index **out, int device_id, int dim, int metric);
+int mcp_index_destroy(mcp_index *idx);
+
+/* ---- table load ----------------------------------------------------------------------------
+ * Replaces GraphPlanner._fetch_embeddings_metadata (control_plane.py:51-55), the only read of
+ * service_schemas.input_schema_vector: rows are the N x dim fp32 vectors in table order.
+ * load copies host rows to the device; adopt uses caller-owned device memory in place
+ * (row pitch `ld` floats, ld >= dim, ld % 4 == 0, base 16-byte aligned; the caller keeps it
+ * alive and unmodified until destroy or the next load/adopt).  Both compute per-row fp64
+ * squared norms and reject NaN/Inf elements (pgvector rejects them at input).
+ * id_base is the service id of row 0 (a row shard of a larger table passes its offset).     */
+int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_rows, int64_t id_base);
+int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, int64_t n_rows, int64_t ld,
+                           int64_t id_base, void *stream);
+
+/* ---- telemetry fold --------------------------------------------------------------------------
+ * One fp32 penalty per service, added to the distance before ranking.  The reference names the
+ * fields (cost_profile: control_plane.py:31, README.md:93; latency / error rate: README.md:43-48)
+ * but holds no formula; the host layer folds them (telemetry.py) and hands the result here.
+ * NULL clears the penalty.  May be called between searches at any time.                      */
+int mcp_index_set_penalty(mcp_index *idx, const float *penalty_host);
+int mcp_index_set_penalty_device(mcp_index *idx, const float *penalty_device, void *stream);
+
+/* ---- search ----------------------------------------------------------------------------------
+ * The candidate-retrieval step that belongs between control_plane.py:58 and :65 in
+ * GraphPlanner.plan: ORDER BY input_schema_vector <op> query (+ penalty) LIMIT k, exact.
+ * out_ids [n_queries*k], out_scores [n_queries*k] fp32 (the fp64 score rounded once);
+ * out_scores64 may be NULL.  The host variant copies in/out and returns finished results.
+ * The device variant only enqueues work on `stream`; queries that fail the exactness
+ * certificate are re-answered on the device by the fp64 scan inside the same call, up to an
+ * internal per-batch limit -- mcp_index_sync_status reports whether any were left over (the
+ * host variant handles those itself).                                                        */
+int mcp_index_search(mcp_index *idx, const float *queries_host, int n_queries, int k,
+                     int32_t *out_ids, float *out_scores, double *out_scores64);
+int mcp_index_search_device(mcp_index *idx, const float *queries_device, int n_queries, int k,
+                            int32_t *out_ids_device, float *out_scores_device,
+                            double *out_scores64_device, void *stream);
+/* blocks until every search_device issued on this index has finished and reports the totals since
+ * the previous sync_status; n_* may be NULL.  n_unresolved > 0 means that many queries still hold
+ * uncertified results: re-run them with option "path" = MCP_PATH_EXACT_FP64.  Consecutive
+ * search_device calls on the same stream queue behind one another without host waits; a call on
+ * a different stream waits for the previous one first (they share the index's workspace).     */
+int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_failures, int32_t *n_unresolved);
+
+/* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
+ * query before exact rescoring, >= k), "max_fallback" (device-side fp64 re-scans per batch),
+ * "time_coarse" (1 = bracket every coarse scan with CUDA events on the caller's stream; the sums
+ * appear in mcp_stats after mcp_index_sync_status).                                            */
+int mcp_index_set_option(mcp_index *idx, const char *name, int64_t value);
+int mcp_index_get_stats(mcp_index *idx, mcp_stats *out);
+int64_t mcp_index_rows(const mcp_index *idx);
+
+/* ---- shard merge -----------------------------------------------------------------------------
+ * Row-sharded registries: every shard answers the same queries, the per-shard sorted lists
+ * [n_shards][n_queries][k] (as gathered by ncclAllGather) are merged with the same (score, id)
+ * key.  No counterpart in the reference (it is single-process); north_star's exchange step.  */
+int mcp_merge_topk_device(const double *scores64_device, const int32_t *ids_device, int n_shards,
+                          int n_queries, int k, int32_t *out_ids_device, float *out_scores_device,
+                          double *out_scores64_device, void *stream);
+
+/* ---- DAG level scheduling --------------------------------------------------------------------
+ * Batched replacement for the ordering step of Orchestrator.execute (control_plane.py:104,
+ * nx.topological_sort -> networkx topological_generations, dag.py:166-240) on graphs built as
+ * control_plane.py:94-100 builds them.  DAG b has n_nodes[b] <= 64 nodes numbered in insertion
+ * order and owns the (src,dst) byte pairs edge_off[b] .. edge_off[b+1] of `edges`, in insertion
+ * order (duplicates allowed: a DiGraph keeps one).
+ *   out_level   [n_dags*64]  generation of each node; 0xFF = no such node / never emitted (cycle)
+ *   out_order   [n_dags*64]  nodes in the order nx.topological_sort yields them; may be NULL
+ *   out_n_levels[n_dags]     generations yielded
+ *   out_status  [n_dags]     0 ok, 1 = NetworkXUnfeasible (cycle)
+ * The host variant copies in/out on `device_id`; the device variant enqueues on `stream`.    */
+int mcp_dag_levels(int device_id, const uint8_t *n_nodes, const uint32_t *edge_off,
+                   const uint8_t *edges, int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
+                   uint8_t *out_n_levels, uint8_t *out_status);
+int mcp_dag_levels_device(const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
+                          int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
+                          uint8_t *out_n_levels, uint8_t *out_status, void *stream);
+
+/* ---- misc ------------------------------------------------------------------------------------ */
+const char *mcp_last_error(void);
+int mcp_device_count(void);          /* 0 when no CUDA device is usable */
+const char *mcp_build_info(void);    /* arch, nvcc version, kernel list */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCP_B200_H */

@@ -1,0 +1,90 @@
+"""Bit-exact parity of the batched Kahn kernel (K6) against the oracle / NetworkX golden file."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+GOLD = Path(__file__).parent / "golden"
+
+
+def _same(res, level, order, nlev, status):
+    assert np.array_equal(res.level, level)
+    assert np.array_equal(res.n_levels, nlev)
+    assert np.array_equal(res.status, status)
+    if res.order.shape[1]:
+        assert np.array_equal(res.order, order)
+
+
+def test_networkx_golden(mcp):
+    g = np.load(GOLD / "dag_golden.npz")
+    enc = mcp.dag.EncodedDags(g["n_nodes"], g["edge_off"], g["edges"], [])
+    _same(mcp.dag.levels(enc), g["level"], g["order"], g["n_levels"], g["status"])
+    res = mcp.dag.levels(enc, with_order=False)
+    assert np.array_equal(res.level, g["level"]) and res.order.shape[1] == 0
+
+
+def test_edge_cases_against_live_networkx(mcp, oracle):
+    graphs = [
+        {"nodes": [], "edges": []},
+        {"nodes": [{"name": "a"}], "edges": []},
+        {"nodes": [{"name": "a"}], "edges": [{"from": "a", "to": "a"}]},
+        {"nodes": [{"name": "a"}, {"name": "b"}], "edges": [{"from": "a", "to": "b"}] * 5},
+        {"nodes": [{"name": "a"}], "edges": [{"from": "q", "to": "a"}, {"from": "a", "to": "r"}]},
+        {"nodes": [{"name": f"n{i}"} for i in range(64)],
+         "edges": [{"from": f"n{i}", "to": f"n{i + 1}"} for i in range(63)]},               # 64-level chain
+        {"nodes": [{"name": f"n{i}"} for i in range(64)],
+         "edges": [{"from": f"n{i}", "to": f"n{j}"} for i in range(64) for j in range(i + 1, 64)]},  # complete DAG, 2016 edges
+        {"nodes": [{"name": f"n{i}"} for i in range(64)], "edges": []},                    # 64 roots
+        {"nodes": [{"name": n} for n in "abcd"],
+         "edges": [{"from": "a", "to": "b"}, {"from": "b", "to": "c"}, {"from": "c", "to": "b"}, {"from": "c", "to": "d"}]},
+    ]
+    enc = mcp.dag.encode_graphs(graphs)
+    res = mcp.dag.levels(enc)
+    for i, g in enumerate(graphs):
+        lv, od, st = oracle.nx_levels(g)
+        glv, god, gst = mcp.dag.decode(enc, res, i)
+        assert (glv, god, gst) == (lv, od, st), i
+        import networkx as nx
+
+        if not st and g["nodes"]:
+            G = nx.DiGraph()
+            G.add_nodes_from(n["name"] for n in g["nodes"])
+            G.add_edges_from((e["from"], e["to"]) for e in g["edges"])
+            assert mcp.dag.generations(enc, res, i) == [list(x) for x in nx.topological_generations(G)]
+
+
+def test_synthetic_100k_bit_exact(mcp, oracle):
+    enc = mcp.dag.synthetic_dags(100_000, seed=4004)
+    level, order, nlev, status = oracle.dag_levels(enc.n_nodes, enc.edge_off, enc.edges)
+    _same(mcp.dag.levels(enc), level, order, nlev, status)
+    assert 500 < status.sum() < 1500                                                      # about 1 % cyclic
+
+
+def test_device_api_and_invariants(mcp):
+    """device-pointer entry point; and the size-independent property: for every edge (u,v) of an
+    acyclic DAG level[u] < level[v], and every non-root has a parent exactly one level up."""
+    import torch
+
+    enc = mcp.dag.synthetic_dags(200_000, seed=5)
+    dev = torch.device("cuda:0")
+    nn = torch.from_numpy(enc.n_nodes).to(dev)
+    off = torch.from_numpy(enc.edge_off.view(np.int32)).to(dev)
+    ed = torch.from_numpy(enc.edges).to(dev).contiguous()
+    level, order, nlev, status = mcp.dag.levels_device(nn, off, ed)
+    torch.cuda.synchronize()
+    lv, st = level.cpu().numpy(), status.cpu().numpy()
+    dag_of_edge = np.repeat(np.arange(len(enc)), np.diff(enc.edge_off.astype(np.int64)))
+    ok = st[dag_of_edge] == 0
+    lu = lv[dag_of_edge, enc.edges[:, 0]].astype(np.int32)
+    lvv = lv[dag_of_edge, enc.edges[:, 1]].astype(np.int32)
+    assert (lu[ok] < lvv[ok]).all()
+    best_parent = np.zeros((len(enc), 64), np.int32) - 1
+    np.maximum.at(best_parent, (dag_of_edge[ok], enc.edges[ok, 1]), lu[ok])
+    acyc = st == 0
+    has_parent = best_parent >= 0
+    assert (best_parent[has_parent & acyc[:, None]] + 1 == lv[has_parent & acyc[:, None]]).all()
+    ordn = order.cpu().numpy()
+    n_emitted = (ordn != 0xFF).sum(1)
+    assert (n_emitted[acyc] == enc.n_nodes[acyc]).all()
+    assert (nlev.cpu().numpy()[acyc] == lv[acyc].astype(np.int32).max(1, initial=-1, where=lv[acyc] != 0xFF) + 1).all()

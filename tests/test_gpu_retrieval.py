@@ -1,0 +1,199 @@
+"""Parity of the CUDA retrieval path against the CPU oracle, through the C ABI.
+
+Bar (BASELINE.json north_star): top-k ids bit-exact with ties -> lowest id; scores within 1e-5
+relative (they are in fact bit-equal: the rescoring kernel repeats the oracle's fp64 arithmetic).
+"""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import cases
+
+pytestmark = pytest.mark.gpu
+GOLD = Path(__file__).parent / "golden"
+REL_TOL = 1e-5
+PATHS = ["stream_fp32", "gemm_tf32", "exact_fp64"]
+
+
+def _gemm_ready(mcp, dim):
+    """The TF32 path only exists for dims its TMA tiling accepts; otherwise it must refuse loudly."""
+    return dim % 4 == 0
+
+
+def _assert_parity(got, want_ids, want_s64):
+    ids, s32, s64 = got
+    assert ids.dtype == np.int32 and np.array_equal(ids, want_ids), \
+        f"ids differ at {np.argwhere(ids != want_ids)[:5].tolist()}"
+    fin = np.isfinite(want_s64)
+    assert np.array_equal(np.isnan(s64), np.isnan(want_s64))
+    assert np.allclose(s64[fin], want_s64[fin], rtol=REL_TOL, atol=0)
+    assert np.array_equal(s64, want_s64, equal_nan=True), "fp64 scores are expected to be bit-equal"
+    assert np.array_equal(s32, want_s64.astype(np.float32), equal_nan=True)
+
+
+def _run(mcp, c, path, k=None, kprime=None):
+    with mcp.ServiceIndex(c["rows"].shape[1], "cosine" if c["metric"] == 0 else "l2") as idx:
+        idx.load(c["rows"])
+        if c["penalty"] is not None:
+            idx.set_penalty(c["penalty"])
+        idx.set_option("path", path)
+        if kprime:
+            idx.set_option("kprime", kprime)
+        out = idx.search(c["queries"], k or c["k"])
+        return out, idx.stats()
+
+
+@pytest.mark.parametrize("path", PATHS)
+@pytest.mark.parametrize("name", ["config1", "small_l2", "edge_cases", "config2_small"])
+def test_golden_and_oracle(mcp, oracle, name, path):
+    c = {"config1": cases.config1, "small_l2": lambda: cases.small_l2(oracle.telemetry_penalty),
+         "edge_cases": lambda: cases.edge_cases(oracle.telemetry_penalty),
+         "config2_small": lambda: cases.config2_small(oracle.telemetry_penalty)}[name]()
+    if path == "gemm_tf32" and not _gemm_ready(mcp, c["rows"].shape[1]):
+        pytest.skip("dim not a multiple of 4: the GEMM path does not take it")
+    k = min(c["k"], 256)
+    g = np.load(GOLD / f"retrieval_{name}.npz")
+    got, stats = _run(mcp, c, path, k=k)
+    _assert_parity(got, g["ids"][:, :k], g["scores64"][:, :k])
+    assert stats["last_path"] == {"stream_fp32": 1, "gemm_tf32": 2, "exact_fp64": 3}[path]
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+@pytest.mark.parametrize("path", PATHS)
+def test_seeded_batches(mcp, oracle, metric, path):
+    """ragged sizes: N not a multiple of any tile, Q = 1 .. 37, k from 1 to 256, un-normalised rows."""
+    rng = np.random.default_rng(100 + metric)
+    for n, d, q, k in [(1, 64, 1, 1), (37, 128, 3, 64), (5000, 256, 37, 100), (4097, 1536, 9, 256), (20000, 768, 16, 10)]:
+        rows = (rng.standard_normal((n, d), dtype=np.float32) * rng.uniform(0.5, 2.0, (n, 1)).astype(np.float32))
+        qs = rng.standard_normal((q, d), dtype=np.float32)
+        pen = (rng.random(n) * 0.05).astype(np.float32)
+        c = dict(rows=rows, queries=qs, k=k, metric=metric, penalty=pen)
+        want_ids, want_s64, _ = oracle.topk(rows, qs, k, metric, pen)
+        got, _ = _run(mcp, c, path)
+        _assert_parity(got, want_ids, want_s64)
+
+
+@pytest.mark.parametrize("path", ["stream_fp32", "gemm_tf32"])
+def test_certificate_catches_near_ties(mcp, oracle, path):
+    """Rows that differ from each other by ~1 ulp in score: the coarse pass cannot order them, the
+    certificate must notice when k' is too small and the fp64 scan must fix it."""
+    rng = np.random.default_rng(7)
+    d = 256
+    base = rng.standard_normal(d).astype(np.float32)
+    rows = np.tile(base, (3000, 1))
+    rows += (rng.standard_normal((3000, d)) * 1e-7).astype(np.float32) * np.abs(base)   # near-duplicates
+    qs = (base + rng.standard_normal((5, d)).astype(np.float32) * 0.01).astype(np.float32)
+    for metric in (0, 1):
+        c = dict(rows=rows, queries=qs, k=20, metric=metric, penalty=None)
+        want_ids, want_s64, _ = oracle.topk(rows, qs, 20, metric, None)
+        got, stats = _run(mcp, c, path, kprime=32)
+        _assert_parity(got, want_ids, want_s64)
+        assert stats["certificate_failures"] > 0, "adversarial near-ties should have failed the certificate"
+        assert stats["exact_scans"] >= stats["certificate_failures"]
+
+
+def test_zero_query_and_degenerate_inputs(mcp, oracle):
+    rng = np.random.default_rng(9)
+    rows = rng.standard_normal((500, 64), dtype=np.float32)
+    qs = rng.standard_normal((3, 64), dtype=np.float32)
+    qs[1] = 0.0                                                   # cosine: every score NaN -> ids 0..k-1
+    want_ids, want_s64, _ = oracle.topk(rows, qs, 7, 0, None)
+    got, _ = _run(mcp, dict(rows=rows, queries=qs, k=7, metric=0, penalty=None), "auto")
+    _assert_parity(got, want_ids, want_s64)
+    assert got[0][1].tolist() == list(range(7)) and np.isnan(got[2][1]).all()
+    with mcp.ServiceIndex(64) as idx:
+        bad = rows.copy()
+        bad[3, 5] = np.nan
+        with pytest.raises(mcp.McpError):
+            idx.load(bad)                                         # pgvector rejects NaN at input; so do we
+        idx.load(rows)
+        with pytest.raises(mcp.McpError):
+            idx.search(qs, 0)
+        with pytest.raises(mcp.McpError):
+            idx.search(qs, 257)
+        with pytest.raises(ValueError):
+            idx.search(qs[:, :10], 3)
+        ids, _, _ = idx.search(qs[:1], 5)
+        idx.set_penalty(np.where(np.arange(500) == ids[0, 0], 100.0, 0.0).astype(np.float32))
+        ids2, _, _ = idx.search(qs[:1], 5)
+        assert ids2[0, 0] == ids[0, 1]                            # the penalised best service drops out
+        idx.set_penalty(None)
+        assert np.array_equal(idx.search(qs[:1], 5)[0], ids)
+
+
+def test_k_exceeds_rows_and_id_base(mcp, oracle):
+    rows = np.eye(3, 8, dtype=np.float32)
+    qs = np.ones((2, 8), np.float32)
+    with mcp.ServiceIndex(8, "l2") as idx:
+        idx.load(rows, id_base=1000)
+        ids, s32, s64 = idx.search(qs, 6)
+    want_ids, want_s64, _ = oracle.topk(rows, qs, 6, 1, None, id_base=1000)
+    _assert_parity((ids, s32, s64), want_ids, want_s64)
+    assert ids[0].tolist() == [1000, 1001, 1002, -1, -1, -1]
+
+
+def test_device_pointer_api_and_shard_merge(mcp, oracle):
+    """search_device on torch tensors; 4 row shards merged by the K5 kernel == unsharded answer."""
+    import torch
+
+    from autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 import sharded
+
+    c = cases.config2_small(oracle.telemetry_penalty, n=6000, q=20, k=32)
+    want_ids, want_s64, _ = oracle.topk(c["rows"], c["queries"], 32, 0, c["penalty"])
+    dev = torch.device("cuda:0")
+    rows = torch.from_numpy(c["rows"]).to(dev)
+    qs = torch.from_numpy(c["queries"]).to(dev)
+    pen = torch.from_numpy(c["penalty"]).to(dev)
+    parts_s, parts_i, keep = [], [], []
+    for r in range(4):
+        lo, hi = sharded.shard_bounds(6000, 4, r)
+        idx = mcp.ServiceIndex(1536).adopt(rows[lo:hi], id_base=lo)
+        idx.set_penalty(pen[lo:hi].contiguous())
+        ids, s32, s64 = idx.search_device(qs, 32)
+        assert idx.sync_status()[1] == 0
+        parts_s.append(s64)
+        parts_i.append(ids)
+        keep.append(idx)
+    mi, ms32, ms64 = mcp.merge_topk_device(torch.stack(parts_s).contiguous(), torch.stack(parts_i).contiguous())
+    torch.cuda.synchronize()
+    _assert_parity((mi.cpu().numpy(), ms32.cpu().numpy(), ms64.cpu().numpy()), want_ids, want_s64)
+    for idx in keep:
+        idx.close()
+
+
+@pytest.mark.parametrize("path", ["stream_fp32", "gemm_tf32"])
+def test_config2_full_size_properties(mcp, oracle, path):
+    """BASELINE config 2 at full size (100K x 1536, 256 queries, top-32, cosine + telemetry).
+    The oracle checks a sample of queries; every query is checked against the GPU fp64 scan
+    (itself oracle-checked above), plus sortedness and idempotence."""
+    import torch
+
+    dev = torch.device("cuda:0")
+    n, q, k = 100_000, 256, 32
+    g = torch.Generator(device=dev).manual_seed(1002)
+    rows = torch.randn((n, 1536), generator=g, device=dev)
+    rows /= rows.norm(dim=1, keepdim=True)
+    qs = torch.randn((q, 1536), generator=g, device=dev)
+    qs /= qs.norm(dim=1, keepdim=True)
+    pen_np = oracle.telemetry_penalty(*cases.telemetry(n, 3002))
+    idx = mcp.ServiceIndex(1536).adopt(rows)
+    idx.set_penalty(torch.from_numpy(pen_np).to(dev))
+    idx.set_option("path", path)
+    ids, s32, s64 = (t.clone() for t in idx.search_device(qs, k))
+    fails, unresolved = idx.sync_status()
+    assert unresolved == 0
+    ids_b, _, s64_b = idx.search_device(qs, k)
+    torch.cuda.synchronize()
+    assert torch.equal(ids, ids_b) and torch.equal(s64, s64_b)                   # idempotent
+    assert bool((s64[:, 1:] >= s64[:, :-1]).all())                              # ascending
+    idx.set_option("path", "exact_fp64")
+    ids_x, _, s64_x = idx.search_device(qs, k)
+    torch.cuda.synchronize()
+    assert torch.equal(ids, ids_x) and torch.equal(s64, s64_x)                   # == brute-force fp64 scan on the GPU
+    rows_np, qs_np = rows.cpu().numpy(), qs.cpu().numpy()
+    sample = [0, 1, 127, 128, 255]
+    want_ids, want_s64, _ = oracle.topk(rows_np, qs_np[sample], k, 0, pen_np)
+    _assert_parity((ids.cpu().numpy()[sample], s32.cpu().numpy()[sample], s64.cpu().numpy()[sample]), want_ids, want_s64)
+    assert fails <= 2, f"{fails} certificate failures on random data: oversampling is too tight"
+    idx.close()
