@@ -46,6 +46,7 @@ SIGNATURES = {
     "mcp_index_set_penalty_device": (_i32, [_vp, _vp, _vp]),
     "mcp_index_search": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "mcp_index_search_device": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "mcp_index_coarse_scores_device": (_i32, [_vp, _i32, _vp, _i32, _vp, _vp]),
     "mcp_index_sync_status": (_i32, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "mcp_index_set_option": (_i32, [_vp, C.c_char_p, _i64]),
     "mcp_index_get_stats": (_i32, [_vp, C.POINTER(McpStats)]),

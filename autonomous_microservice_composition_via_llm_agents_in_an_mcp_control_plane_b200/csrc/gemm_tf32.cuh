@@ -1,12 +1,409 @@
-// gemm_tf32.cuh -- K2 placeholder until the tcgen05 kernel lands (next commit).
+// gemm_tf32.cuh -- K2: tcgen05 / TMEM TF32 distance GEMM with the telemetry score and the
+// top-k' filter fused into the epilogue (large query batches).
+//
+//   D[128 queries x 256 rows] (fp32, TMEM) += Q[128 x 32] (smem, K-major) * E[256 x 32]^T (smem, K-major)
+//
+// Queries are the M operand so that one TMEM lane = one query: an epilogue thread owns a query,
+// keeps its running threshold in a register and sees that query's scores against 256 table rows
+// per tile.  Table rows are the N operand and are streamed once per query block; fp32 rows land
+// in shared memory by TMA (128-byte swizzle) and are consumed by kind::tf32 MMAs directly -- no
+// conversion pass, no shadow table, the bytes read are the fp32 table.
+//
+// Warp roles (192 threads, 1 CTA / SM, persistent over row tiles):
+//   warp 0   TMA producer: per k-block one 16 KB query tile + one 32 KB row tile into a 4-stage ring
+//   warp 1   TMEM allocator + MMA issuer: 4 x tcgen05.mma (M128 N256 K8) per stage, tcgen05.commit
+//            frees the stage; the last commit of a tile publishes the accumulator
+//   warps 2-5  epilogue: tcgen05.ld the accumulator (double-buffered in TMEM: 2 x 256 columns),
+//            score = 1 - dot * inv|q| * inv|e| + penalty (or sqrt(|q|^2+|e|^2-2 dot) + penalty),
+//            compare with the thread's threshold, append survivors to the (CTA, query) list in
+//            global memory; a list that fills is cut back to k' by a register-only warp radix
+//            select, which also tightens the threshold.
+//
+// Coarse error (certificate, rescore.cuh): kind::tf32 reads the top 19 bits of each fp32 operand,
+// i.e. truncates 13 mantissa bits: relative error < 2^-10 per operand, < 2^-9 (1 + 2^-11) per
+// product, so |dot_tf32 - dot| <= 2^-9 * 1.001 * sum|q_i e_i| + fp32 accumulation (<= dim * 2^-22 |q||e|).
 #pragma once
+#include <cuda.h>
+
 #include "common.cuh"
-struct GemmPlan { bool valid = false; };
-struct Buf;
-static inline bool gemm_supported(int, int64_t) { return false; }
-template <class B>
-static int gemm_tf32_run(GemmPlan &, B &, cudaStream_t, int, const float *, int64_t, int, int64_t, const float *, int,
-                         const float *, const double *, const float *, const double *, const float *, int, int,
-                         u64 **, int **, int *, int *) {
-    return -3;
+
+#define G_BM 128
+#define G_BN 256
+#define G_BK 32
+#define G_STAGES 4
+#define G_THREADS 192
+#define G_A_BYTES (G_BM * G_BK * 4)
+#define G_B_BYTES (G_BN * G_BK * 4)
+#define G_MAX_QBLOCKS 8
+
+struct GemmArgs {
+    int64_t n_rows;
+    int dim, nq, nqb, kprime, cap;
+    const float *inv_nq;       // [nq]
+    const double *nq2;         // [nq]
+    const float *inv_ne;       // [n_rows]
+    const double *ne2;         // [n_rows]
+    const float *penalty;      // [n_rows] or NULL
+    u64 *lists;                // [nq][L][cap]
+    int *list_cnt;             // [nq][L]
+    float *dump;               // debug: [nq][n_rows] coarse scores instead of lists, or NULL
+};
+
+struct GemmSmem {
+    float a[G_STAGES][G_BM * G_BK];
+    float b[G_STAGES][G_BN * G_BK];
+    float meta[2][2][G_BN];
+    u64 full[G_STAGES], empty[G_STAGES], tfull[2], tempty[2];
+    uint32_t tmem_base;
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64 *b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(u64 *b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(u64 *b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64 *b, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tm, int c0, int c1, u64 *bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(u64 *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc], kind::tf32, issued by one thread
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, u64 adesc, u64 bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 lanes x 32 consecutive columns: thread i of the warp gets TMEM lane (base lane + i)
+__device__ __forceinline__ void tc_ld_32x32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major, 128-byte swizzle shared-memory operand descriptor (cute::UMMA::SmemDescriptor layout):
+// [0,14) start >> 4, [16,30) LBO >> 4 (unused for swizzled K-major: 1), [32,46) SBO >> 4 = 1024 B between
+// 8-row groups, [46,48) version = 1, [61,64) layout = 2 (SWIZZLE_128B).
+__device__ __forceinline__ u64 umma_desc_k128(const void *tile) {
+    return (u64)((smem_u32(tile) & 0x3FFFF) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): c F32 (1<<4), a/b TF32 (2<<7, 2<<10), both K-major,
+// N >> 3 at [17,23), M >> 4 at [24,29)
+#define G_IDESC ((1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(G_BN >> 3) << 17) | ((uint32_t)(G_BM >> 4) << 24))
+
+// ---- register-only warp radix select --------------------------------------------------------------
+// The warp cuts lane `src`'s list (n keys in global memory, n > kprime) back to its kprime smallest
+// keys and returns the largest kept key (the new threshold).  Keys are unique.
+template <int KPL>
+__device__ __forceinline__ u64 warp_prune_list(u64 *lp, int n, int kprime, int lane) {
+    u64 kk[KPL];
+    uint32_t act = 0;
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) {
+        int idx = i * 32 + lane;
+        kk[i] = idx < n ? lp[idx] : ~0ull;
+        act |= (idx < n ? 1u : 0u) << i;
+    }
+    int need = kprime, tot = n;
+    for (int bit = 63; bit >= 0 && tot != need; --bit) {
+        uint32_t z = 0;
+        int c0 = 0;
+#pragma unroll
+        for (int i = 0; i < KPL; ++i) {
+            bool zero = ((act >> i) & 1u) && !((kk[i] >> bit) & 1ull);
+            z |= (zero ? 1u : 0u) << i;
+            c0 += __popc(__ballot_sync(MCP_FULL, zero));
+        }
+        if (need <= c0) { act = z; tot = c0; }
+        else { act &= ~z; need -= c0; tot -= c0; }
+    }
+    // every remaining active key is kept; threshold = their maximum
+    u64 mx = 0;
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) if ((act >> i) & 1u) mx = kk[i] > mx ? kk[i] : mx;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        u64 t = __shfl_xor_sync(MCP_FULL, mx, o);
+        mx = t > mx ? t : mx;
+    }
+    int base = 0;
+#pragma unroll
+    for (int i = 0; i < KPL; ++i) {
+        bool keep = kk[i] <= mx;
+        uint32_t b = __ballot_sync(MCP_FULL, keep);
+        if (keep) lp[base + __popc(b & ((1u << lane) - 1u))] = kk[i];
+        base += __popc(b);
+    }
+    return mx;
+}
+
+template <int KPL, int METRIC>
+__global__ void __launch_bounds__(G_THREADS, 1)
+gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs a) {
+    extern __shared__ unsigned char g_smem_raw[];
+    GemmSmem &s = *reinterpret_cast<GemmSmem *>(((uintptr_t)g_smem_raw + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qb = blockIdx.x % a.nqb, group = blockIdx.x / a.nqb, ngroups = gridDim.x / a.nqb;
+    const int n_tiles = (int)((a.n_rows + G_BN - 1) / G_BN);
+    const int my_tiles = group < n_tiles ? (n_tiles - group + ngroups - 1) / ngroups : 0;
+    const int KB = (a.dim + G_BK - 1) / G_BK;
+    constexpr int CAP = KPL * 32;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < G_STAGES; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull[i], 1); mbar_init(&s.tempty[i], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s.tmem_base;
+
+    if (warp == 0) {
+        // ===== TMA producer (whole warp walks the loop, lane 0 issues) =====
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+        }
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int i = 0; i < my_tiles; ++i) {
+            const int t = group + i * ngroups;
+            for (int kb = 0; kb < KB; ++kb) {
+                mbar_wait(&s.empty[stage], phase ^ 1u);
+                if (lane == 0) {
+                    mbar_expect_tx(&s.full[stage], G_A_BYTES + G_B_BYTES);
+                    tma_load_2d(s.a[stage], &tmA, kb * G_BK, qb * G_BM, &s.full[stage]);
+                    tma_load_2d(s.b[stage], &tmB, kb * G_BK, t * G_BN, &s.full[stage]);
+                }
+                __syncwarp();
+                if (++stage == G_STAGES) { stage = 0; phase ^= 1u; }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int i = 0; i < my_tiles; ++i) {
+            const int buf = i & 1;
+            const uint32_t tphase = (uint32_t)(i >> 1) & 1u;
+            mbar_wait(&s.tempty[buf], tphase ^ 1u);           // epilogue has drained this accumulator
+            tc_fence_after();
+            const uint32_t d_tmem = tmem + (uint32_t)(buf * G_BN);
+            for (int kb = 0; kb < KB; ++kb) {
+                mbar_wait(&s.full[stage], phase);             // TMA bytes have landed
+                tc_fence_after();
+                if (lane == 0) {
+                    const u64 ad = umma_desc_k128(s.a[stage]), bd = umma_desc_k128(s.b[stage]);
+#pragma unroll
+                    for (int k = 0; k < G_BK / 8; ++k)        // +32 bytes along K inside the swizzle atom = +2 in the address field
+                        tc_mma_tf32(d_tmem, ad + (u64)(2 * k), bd + (u64)(2 * k), G_IDESC, (uint32_t)((kb | k) != 0));
+                    tc_commit(&s.empty[stage]);               // frees the smem stage when these MMAs retire
+                    if (kb == KB - 1) tc_commit(&s.tfull[buf]);
+                }
+                __syncwarp();
+                if (++stage == G_STAGES) { stage = 0; phase ^= 1u; }
+            }
+        }
+    } else {
+        // ===== epilogue: one thread = one query (TMEM lane) =====
+        const int quarter = warp & 3;                          // a warp may only touch TMEM lanes 32*(warp%4)..+31
+        const int m = quarter * 32 + lane;
+        const int qg = qb * G_BM + m;
+        const bool qvalid = qg < a.nq;
+        const float inq = qvalid ? a.inv_nq[qg] : 0.f;
+        const float nq2f = qvalid ? (float)a.nq2[qg] : 0.f;
+        const int et = threadIdx.x - 64;
+        u64 *mylist = a.lists + ((int64_t)(qvalid ? qg : 0) * ngroups + group) * CAP;
+        int cnt = 0;
+        u64 tau = ~0ull;
+        for (int i = 0; i < my_tiles; ++i) {
+            const int t = group + i * ngroups, buf = i & 1;
+            const uint32_t tphase = (uint32_t)(i >> 1) & 1u;
+            const int64_t row0 = (int64_t)t * G_BN;
+            const int rows_here = (int)min((int64_t)G_BN, a.n_rows - row0);
+            // per-row constants of this tile (meta[buf] was last read two tiles ago; the named barrier of the
+            // tile in between ordered those reads before these writes)
+            for (int r = et; r < G_BN; r += 128) {
+                const bool ok = r < rows_here;
+                float m0 = 0.f, m1 = 0.f;
+                if (ok) {
+                    m0 = METRIC == 0 ? a.inv_ne[row0 + r] : (float)a.ne2[row0 + r];
+                    m1 = a.penalty ? a.penalty[row0 + r] : 0.f;
+                }
+                s.meta[buf][0][r] = m0; s.meta[buf][1][r] = m1;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            mbar_wait(&s.tfull[buf], tphase);
+            tc_fence_after();
+            const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * G_BN);
+            for (int c = 0; c < G_BN; c += 32) {
+                uint32_t v[32];
+                tc_ld_32x32(taddr + (uint32_t)c, v);
+                tc_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int r = c + j;
+                    const float acc = __uint_as_float(v[j]);
+                    const float m0 = s.meta[buf][0][r], m1 = s.meta[buf][1][r];
+                    float sc;
+                    if (METRIC == 0) sc = fmaf(-(acc * inq), m0, 1.0f) + m1;
+                    else             sc = sqrtf(fmaxf(nq2f + m0 - 2.0f * acc, 0.f)) + m1;
+                    if (a.dump) {
+                        if (qvalid && r < rows_here) a.dump[(int64_t)qg * a.n_rows + row0 + r] = sc;
+                    } else {
+                        const u64 key = coarse_key(sc, (uint32_t)(row0 + r));
+                        if (qvalid && r < rows_here && key < tau) mylist[cnt++] = key;
+                    }
+                }
+                // a list within 32 of its capacity is cut back to k' (every chunk appends at most 32)
+                uint32_t full_mask = __ballot_sync(MCP_FULL, cnt > CAP - 32);
+                while (full_mask) {
+                    const int src = __ffs(full_mask) - 1;
+                    full_mask &= full_mask - 1;
+                    u64 *lp = (u64 *)__shfl_sync(MCP_FULL, (u64)(uintptr_t)mylist, src);
+                    const int n = __shfl_sync(MCP_FULL, cnt, src);
+                    __syncwarp();
+                    const u64 thr = warp_prune_list<KPL>(lp, n, a.kprime, lane);
+                    if (lane == src) { cnt = a.kprime; tau = thr; }
+                    __syncwarp();
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&s.tempty[buf]);
+        }
+        if (qvalid && !a.dump) a.list_cnt[(int64_t)qg * ngroups + group] = cnt;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct GemmPlan {
+    bool valid = false;
+    CUtensorMap tmB;
+    const float *rows = nullptr;
+    int64_t n_rows = 0, ld = 0;
+    int dim = 0;
+    PFN_encodeTiled encode = nullptr;
+    char err[256] = {0};
+};
+
+static inline bool gemm_supported(int dim, int64_t ld) { return (dim % 4) == 0 && (ld % 4) == 0 && dim >= 4; }
+
+static int gemm_encode_2d(GemmPlan &p, CUtensorMap *tm, const float *base, int64_t rows, int dim, int64_t ld, int box_rows) {
+    if (!p.encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+            snprintf(p.err, sizeof p.err, "cuTensorMapEncodeTiled entry point unavailable (%s)", cudaGetErrorString(e));
+            return -2;
+        }
+        p.encode = (PFN_encodeTiled)fn;
+    }
+    cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {G_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = p.encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)base, gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        snprintf(p.err, sizeof p.err, "cuTensorMapEncodeTiled failed with CUresult %d (rows %lld dim %d ld %lld)", (int)r,
+                 (long long)rows, dim, (long long)ld);
+        return -2;
+    }
+    return 0;
+}
+
+static inline int gemm_kpl_for(int kprime) { return kprime <= 64 ? 4 : kprime <= 128 ? 8 : 16; }
+static inline int gemm_max_kprime() { return 256; }
+
+// One launch over <= G_MAX_QBLOCKS * 128 queries.  Lists come back as [nq][L][cap] in `ws`.
+// Returns 0, or a negative MCP_E* code with the message in plan.err.
+template <class BufT>
+static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const float *rows, int64_t n_rows, int dim,
+                         int64_t ld, const float *queries, int nq, const float *inv_nq, const double *nq2,
+                         const float *inv_ne, const double *ne2, const float *penalty, int metric, int kprime,
+                         u64 **out_lists, int **out_cnt, int *out_L, int *out_cap, float *dump = nullptr) {
+    if (!gemm_supported(dim, ld)) { snprintf(p.err, sizeof p.err, "gemm_tf32 needs dim %% 4 == 0 (dim %d, ld %lld)", dim, (long long)ld); return -1; }
+    if (kprime > gemm_max_kprime()) { snprintf(p.err, sizeof p.err, "gemm_tf32 keeps at most %d candidates (asked %d)", gemm_max_kprime(), kprime); return -1; }
+    if (nq > G_MAX_QBLOCKS * G_BM) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch takes at most %d queries", G_MAX_QBLOCKS * G_BM); return -1; }
+    if (!p.valid || p.rows != rows || p.n_rows != n_rows || p.ld != ld || p.dim != dim) {
+        int rc = gemm_encode_2d(p, &p.tmB, rows, n_rows, dim, ld, G_BN);
+        if (rc) return rc;
+        p.rows = rows; p.n_rows = n_rows; p.ld = ld; p.dim = dim; p.valid = true;
+    }
+    CUtensorMap tmA;
+    int rc = gemm_encode_2d(p, &tmA, queries, nq, dim, dim, G_BM);
+    if (rc) return rc;
+    const int nqb = (nq + G_BM - 1) / G_BM;
+    const int n_tiles = (int)((n_rows + G_BN - 1) / G_BN);
+    int ngroups = std::max(1, std::min(n_sm / nqb, n_tiles));
+    const int kpl = gemm_kpl_for(kprime), cap = kpl * 32;
+    const size_t list_bytes = sizeof(u64) * (size_t)nq * ngroups * cap;
+    const size_t cnt_off = (list_bytes + 255) & ~(size_t)255;
+    if ((rc = ws.ensure(cnt_off + sizeof(int) * (size_t)nq * ngroups))) { snprintf(p.err, sizeof p.err, "workspace allocation failed"); return rc; }
+    GemmArgs a;
+    a.n_rows = n_rows; a.dim = dim; a.nq = nq; a.nqb = nqb; a.kprime = kprime; a.cap = cap;
+    a.inv_nq = inv_nq; a.nq2 = nq2; a.inv_ne = inv_ne; a.ne2 = ne2; a.penalty = penalty;
+    a.lists = reinterpret_cast<u64 *>(ws.p);
+    a.list_cnt = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(ws.p) + cnt_off);
+    a.dump = dump;
+    const size_t smem = sizeof(GemmSmem) + 1024;
+    cudaError_t e = cudaSuccess;
+#define G_LAUNCH(KPL, MET)                                                                                      \
+    do {                                                                                                        \
+        e = cudaFuncSetAttribute(gemm_tf32_kernel<KPL, MET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e == cudaSuccess) {                                                                                 \
+            gemm_tf32_kernel<KPL, MET><<<nqb * ngroups, G_THREADS, smem, st>>>(tmA, p.tmB, a);                  \
+            e = cudaGetLastError();                                                                             \
+        }                                                                                                       \
+    } while (0)
+    if (metric == 0) { if (kpl == 4) G_LAUNCH(4, 0); else if (kpl == 8) G_LAUNCH(8, 0); else G_LAUNCH(16, 0); }
+    else             { if (kpl == 4) G_LAUNCH(4, 1); else if (kpl == 8) G_LAUNCH(8, 1); else G_LAUNCH(16, 1); }
+#undef G_LAUNCH
+    if (e != cudaSuccess) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch: %s", cudaGetErrorString(e)); return -2; }
+    *out_lists = a.lists; *out_cnt = a.list_cnt; *out_L = ngroups; *out_cap = cap;
+    return 0;
 }

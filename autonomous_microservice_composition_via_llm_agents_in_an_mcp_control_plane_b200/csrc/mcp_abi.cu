@@ -450,7 +450,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     const int dim = idx->dim;
     const int64_t n = idx->n_rows;
     const int path = choose_path(idx, nq);
-    const int kprime = choose_kprime(idx, k);
+    int kprime = choose_kprime(idx, k);
+    if (path == MCP_PATH_GEMM_TF32) kprime = std::min(kprime, gemm_max_kprime());   // >= k since k <= 256
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
 
     if ((rc = idx->nq2.ensure(sizeof(double) * nq))) return rc;
@@ -480,7 +481,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     }
 
     // query chunking keeps the K1 score matrix within budget; K2 needs no score matrix
-    int chunk = nq;
+    int chunk = std::min(nq, G_MAX_QBLOCKS * G_BM);
     if (path == MCP_PATH_STREAM_FP32)
         chunk = (int)std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(SCORE_BUDGET_BYTES / (4ull * (size_t)n))));
     const int kc = (int)std::min<int64_t>(kprime, n);
@@ -533,7 +534,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, idx->d_rows, n, dim, idx->ld, dq, cq,
                                     idx->inv_nq.as<float>() + q0, idx->nq2.as<double>() + q0, idx->inv_norm.as<float>(),
                                     idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap)))
-                return rc;
+                return fail(rc, "%s", idx->gemm.err);
+            idx->stats.kernel_launches++;
             if ((rc = coarse_event(idx, st))) return rc;
             // the GEMM's lists live in gemm_ws; reductions ping-pong between listsA / listsB
             if (L == 1 && cap <= kprime) { cand = lists; cand_cnt = cnts; cand_stride = cap; }
@@ -653,6 +655,47 @@ extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n
     CU(cudaMemcpyAsync(out_scores, idx->out_scores.p, sizeof(float) * nk, cudaMemcpyDeviceToHost, st));
     if (out_scores64) CU(cudaMemcpyAsync(out_scores64, idx->out_scores64.p, sizeof(double) * nk, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    return MCP_OK;
+}
+
+// coarse scores of every (query,row) pair from one coarse kernel: lets tests check the error bounds the
+// certificate assumes, and localises a wrong tensor-core descriptor to the element.
+extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const float *queries_device, int n_queries,
+                                              float *out_scores_device, void *stream) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!idx->n_rows) return fail(MCP_ESTATE, "coarse_scores before load");
+    if (!queries_device || !out_scores_device || n_queries < 1 || n_queries > G_MAX_QBLOCKS * G_BM) return fail(MCP_EINVAL, "bad arguments");
+    CU(cudaSetDevice(idx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc;
+    if ((rc = order_after_previous(idx, st))) return rc;
+    const int dim = idx->dim;
+    if ((rc = idx->nq2.ensure(sizeof(double) * n_queries))) return rc;
+    if ((rc = idx->inv_nq.ensure(sizeof(float) * n_queries))) return rc;
+    if ((rc = idx->qflag.ensure(n_queries))) return rc;
+    prep_rows_kernel<true><<<(n_queries + PREP_ROWS - 1) / PREP_ROWS, PREP_ROWS, 0, st>>>(
+        queries_device, n_queries, dim, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), nullptr);
+    KCHECK();
+    const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
+    if (path == MCP_PATH_STREAM_FP32) {
+        if (dim & 3) return fail(MCP_EINVAL, "coarse_scores: dim %% 4 != 0");
+        for (int p = 0; p < n_queries; p += 8) {
+            int nv = std::min(8, n_queries - p);
+            if ((rc = run_scan_pass(idx, st, queries_device + (int64_t)p * dim, dim, idx->inv_nq.as<float>() + p, nv,
+                                    out_scores_device + (int64_t)p * idx->n_rows, idx->n_rows)))
+                return rc;
+        }
+    } else if (path == MCP_PATH_GEMM_TF32) {
+        u64 *l; int *c; int L, cap;
+        if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, idx->d_rows, idx->n_rows, dim, idx->ld, queries_device,
+                                n_queries, idx->inv_nq.as<float>(), idx->nq2.as<double>(), idx->inv_norm.as<float>(),
+                                idx->norm2.as<double>(), pen, idx->metric, 64, &l, &c, &L, &cap, out_scores_device)))
+            return fail(rc, "%s", idx->gemm.err);
+    } else
+        return fail(MCP_EINVAL, "coarse_scores: path must be STREAM_FP32 or GEMM_TF32");
+    CU(cudaEventRecord(idx->done, st));
+    idx->pending = true;
     return MCP_OK;
 }
 

@@ -138,6 +138,16 @@ class ServiceIndex:
             C.c_void_p(sc.data_ptr()), C.c_void_p(sc64.data_ptr()) if sc64 is not None else None, _stream_ptr()))
         return ids, sc, sc64
 
+    def coarse_scores_device(self, queries, path="gemm_tf32"):
+        """[Q, N] fp32 coarse scores exactly as one coarse kernel computes them (validation aid)."""
+        import torch
+
+        out = torch.empty((queries.shape[0], self.n_rows), dtype=torch.float32, device=queries.device)
+        nat.check(self._lib.mcp_index_coarse_scores_device(
+            self._h, _PATHS[path], C.c_void_p(queries.data_ptr()), queries.shape[0], C.c_void_p(out.data_ptr()),
+            _stream_ptr()))
+        return out
+
     def sync_status(self) -> Tuple[int, int]:
         a, b = C.c_int32(), C.c_int32()
         nat.check(self._lib.mcp_index_sync_status(self._h, C.byref(a), C.byref(b)))

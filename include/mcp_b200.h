@@ -112,6 +112,12 @@ int mcp_index_search_device(mcp_index *idx, const float *queries_device, int n_q
  * a different stream waits for the previous one first (they share the index's workspace).     */
 int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_failures, int32_t *n_unresolved);
 
+/* validation aid: the coarse score (distance + penalty, fp32) of every (query,row) pair as one coarse
+ * kernel computes it, out [n_queries * n_rows]; path = MCP_PATH_STREAM_FP32 or MCP_PATH_GEMM_TF32.
+ * The tests use it to check the error bounds the certificate assumes.  No reference counterpart. */
+int mcp_index_coarse_scores_device(mcp_index *idx, int path, const float *queries_device, int n_queries,
+                                   float *out_scores_device, void *stream);
+
 /* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
  * query before exact rescoring, >= k), "max_fallback" (device-side fp64 re-scans per batch),
  * "time_coarse" (1 = bracket every coarse scan with CUDA events on the caller's stream; the sums

@@ -197,3 +197,41 @@ def test_config2_full_size_properties(mcp, oracle, path):
     _assert_parity((ids.cpu().numpy()[sample], s32.cpu().numpy()[sample], s64.cpu().numpy()[sample]), want_ids, want_s64)
     assert fails <= 2, f"{fails} certificate failures on random data: oversampling is too tight"
     idx.close()
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+@pytest.mark.parametrize("path", ["stream_fp32", "gemm_tf32"])
+def test_coarse_scores_within_certified_bounds(mcp, oracle, metric, path):
+    """Every coarse score must lie within the error bound the certificate assumes for its kernel
+    (rescore.cuh / mcp_abi.cu CertParams); also localises a wrong TMA / UMMA descriptor to the element.
+    Ragged on purpose: N not a multiple of the 256-row tile, Q = 150 (second query block half empty),
+    dim = 200 is not a multiple of the 32-float k-block (TMA zero fill)."""
+    import torch
+
+    dev = torch.device("cuda:0")
+    u = 2.0 ** -24
+    for n, d, q in [(3000, 1536, 150), (777, 200, 5)]:
+        rng = np.random.default_rng(n + metric)
+        rows = (rng.standard_normal((n, d), dtype=np.float32) * rng.uniform(0.5, 2.0, (n, 1)).astype(np.float32))
+        qs = rng.standard_normal((q, d), dtype=np.float32)
+        pen = (rng.random(n) * 0.05).astype(np.float32)
+        exact = np.stack([oracle.scores(rows, qq, metric, pen) for qq in qs])
+        with mcp.ServiceIndex(d, "cosine" if metric == 0 else "l2") as idx:
+            idx.load(rows).set_penalty(pen)
+            got = idx.coarse_scores_device(torch.from_numpy(qs).to(dev), path)
+            torch.cuda.synchronize()
+            got = got.cpu().numpy().astype(np.float64)
+        rel = 2.0 * (d / 32.0 + 16.0) * u if path == "stream_fp32" else 1.02 * 2.0 ** -9 + d * 4.0 * u
+        qn = np.linalg.norm(qs.astype(np.float64), axis=1)[:, None]
+        en = np.linalg.norm(rows.astype(np.float64), axis=1)[None, :]
+        if metric == 0:
+            eps = rel + 8 * u * (2.0 + 0.05)
+        elif path == "stream_fp32":
+            eps = rel * (qn + en.max()) + 8 * u * (qn + en.max() + 0.05)
+        else:
+            delta = 2.0 * rel * qn * en.max() + 4 * u * (qn + en.max()) ** 2
+            d2 = (exact - pen[None, :].astype(np.float64)) ** 2
+            eps = np.sqrt(d2 + delta) - np.sqrt(d2) + 8 * u * (np.sqrt(d2) + 0.05) + 1e-6
+        err = np.abs(got - exact)
+        worst = np.unravel_index(np.argmax(err - eps), err.shape)
+        assert (err <= eps).all(), f"{path} metric {metric} n={n} d={d}: |coarse-exact|={err[worst]:.3e} at (q,row)={worst}, bound {np.broadcast_to(eps, err.shape)[worst]:.3e}"
