@@ -17,6 +17,7 @@ METRIC_COSINE, METRIC_L2 = 0, 1
 PATH_AUTO, PATH_STREAM_FP32, PATH_GEMM_TF32, PATH_EXACT_FP64 = 0, 1, 2, 3
 MAX_K = 256
 MAX_DAG_NODES = 64
+NOALLOC_MAX_ROWS, NOALLOC_MAX_QUERIES = 1 << 20, 64
 
 
 class McpStats(C.Structure):
@@ -47,6 +48,7 @@ SIGNATURES = {
     "mcp_index_search": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "mcp_index_search_device": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     "mcp_index_coarse_scores_device": (_i32, [_vp, _i32, _vp, _i32, _vp, _vp]),
+    "mcp_index_search_exact_noalloc_device": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     "mcp_index_sync_status": (_i32, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "mcp_index_set_option": (_i32, [_vp, C.c_char_p, _i64]),
     "mcp_index_get_stats": (_i32, [_vp, C.POINTER(McpStats)]),

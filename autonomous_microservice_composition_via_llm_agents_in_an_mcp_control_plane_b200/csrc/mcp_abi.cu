@@ -779,3 +779,103 @@ extern "C" int mcp_dag_levels(int device_id, const uint8_t *n_nodes, const uint3
 #undef CUT
     return MCP_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Exact search that allocates nothing (no counterpart in the reference)
+// ---------------------------------------------------------------------------------------------
+// Who this is for.  The ordinary search entry points grow the index's workspace with cudaMalloc the first
+// time a larger batch or table shows up.  Some callers of this library must not do that at request time:
+//   * a planner thread answering /plan while another stream of the same process is in the middle of a
+//     table scan -- cudaMalloc / cudaFree serialise against the whole device and would stall that scan;
+//   * a process whose HBM is fully budgeted (a 61 GB registry shard next to other tenants, or a fixed
+//     memory pool handed out at start-up), where an allocation in the request path can fail with
+//     out-of-memory long after start-up checks passed.
+// For them this entry point runs the fp64 full scan (the same kernels as path = MCP_PATH_EXACT_FP64) with
+// every byte of scratch taken from one fixed array that is part of the library image.
+//
+// The array: MCP_NOALLOC_SCRATCH_BYTES = 8 MiB + 4 KiB of device memory, resident on every GPU that loads
+// the library, from load until the process exits.  It bounds the call: n_rows <= MCP_NOALLOC_MAX_ROWS
+// (1,048,576) and n_queries <= MCP_NOALLOC_MAX_QUERIES (64); larger requests are refused with MCP_EINVAL.
+//
+// Sharing.  There is ONE array per device and every call on that device uses it.  It still holds whatever the
+// previous call left there; the call rewrites each part before reading it (query norms, the flag word and
+// list, one score per table row), so stale contents are never consumed.  Two calls whose GPU work overlaps
+// (different streams, or different indexes on the same device) race on the array and corrupt each other:
+// keep such calls on one stream or otherwise ordered.
+//
+// Set-up.  `g_noalloc_scratch` names the array only inside device code; on the host the symbol is a stand-in,
+// not an address the GPU can use.  The first call on each device therefore asks the runtime for the real
+// device address (cudaGetSymbolAddress, with that device current) and remembers it.  Make that first call
+// before starting any stream capture.
+#define MCP_NOALLOC_MAX_ROWS_ (1 << 20)
+#define MCP_NOALLOC_MAX_QUERIES_ 64
+#define NOALLOC_SCORES_BYTES ((size_t)MCP_NOALLOC_MAX_ROWS_ * sizeof(u64))   // one fp64 score image per row
+#define NOALLOC_TAIL_BYTES 4096                                               // norms, flags
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCORES_BYTES + NOALLOC_TAIL_BYTES];
+
+#define NOALLOC_MAX_DEVICES 64
+static std::mutex g_noalloc_mu;
+static unsigned char *g_noalloc_addr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// one-time, per device: turn the symbol into a device address (device must be current)
+static int noalloc_scratch_for(int device, unsigned char **out) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(MCP_EINVAL, "device %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_addr[device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(MCP_ECUDA, "cudaGetSymbolAddress(g_noalloc_scratch) on device %d -> %s", device, cudaGetErrorString(e));
+        g_noalloc_addr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_noalloc_addr[device];
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_device, int n_queries, int k,
+                                                     int32_t *out_ids_device, float *out_scores_device,
+                                                     double *out_scores64_device, void *stream) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!idx->n_rows) return fail(MCP_ESTATE, "search before load");
+    if (!queries_device || !out_ids_device || !out_scores_device) return fail(MCP_EINVAL, "NULL buffer");
+    if (k < 1 || k > MCP_MAX_K) return fail(MCP_EINVAL, "k %d outside [1, %d]", k, MCP_MAX_K);
+    if (n_queries < 1 || n_queries > MCP_NOALLOC_MAX_QUERIES_)
+        return fail(MCP_EINVAL, "n_queries %d outside [1, %d]: the fixed scratch array holds norms for at most %d queries",
+                    n_queries, MCP_NOALLOC_MAX_QUERIES_, MCP_NOALLOC_MAX_QUERIES_);
+    if (idx->n_rows > MCP_NOALLOC_MAX_ROWS_)
+        return fail(MCP_EINVAL, "table has %lld rows; the fixed scratch array holds one score per row for at most %d rows",
+                    (long long)idx->n_rows, MCP_NOALLOC_MAX_ROWS_);
+    CU(cudaSetDevice(idx->device));
+    unsigned char *base = nullptr;
+    int rc = noalloc_scratch_for(idx->device, &base);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    // carve the array: [scores | nq2 (64 f64) | inv_nq (64 f32) | qflag (64 B) | n_flag + flag list (ints)]
+    u64 *scores = reinterpret_cast<u64 *>(base);
+    unsigned char *tail = base + NOALLOC_SCORES_BYTES;
+    double *nq2 = reinterpret_cast<double *>(tail);
+    float *inv_nq = reinterpret_cast<float *>(tail + 512);
+    unsigned char *qflag = tail + 768;
+    int *n_flag = reinterpret_cast<int *>(tail + 1024);
+    int *flag_list = n_flag + 8;
+    const int dim = idx->dim;
+    const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
+    // every query's norm is rewritten here; nothing from an earlier call is read
+    prep_rows_kernel<true><<<1, PREP_ROWS, 0, st>>>(queries_device, n_queries, dim, dim, nq2, inv_nq, qflag, nullptr);
+    KCHECK();
+    const int64_t want = (idx->n_rows + 255) / 256;
+    const int gx = (int)std::min<int64_t>((int64_t)idx->n_sm * 8, want);
+    for (int q = 0; q < n_queries; ++q) {
+        flag_all_kernel<<<1, 32, 0, st>>>(flag_list, n_flag, q, 1);        // (re)sets the flag word and the one-entry list
+        KCHECK();
+        exact_scan_kernel<<<dim3(gx, 1), 256, sizeof(float) * dim, st>>>(idx->d_rows, idx->n_rows, dim, idx->ld, queries_device,
+                                                                       nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list,
+                                                                       n_flag, 0, scores);   // writes scores[0 .. n_rows)
+        KCHECK();
+        exact_select_kernel<<<1, EXSEL_THREADS, 0, st>>>(scores, idx->n_rows, k, idx->id_base, flag_list, n_flag, 0,
+                                                          out_ids_device, out_scores_device, out_scores64_device);
+        KCHECK();
+    }
+    return MCP_OK;
+}

@@ -138,6 +138,21 @@ class ServiceIndex:
             C.c_void_p(sc.data_ptr()), C.c_void_p(sc64.data_ptr()) if sc64 is not None else None, _stream_ptr()))
         return ids, sc, sc64
 
+    def search_exact_noalloc_device(self, queries, k: int, out: tuple):
+        """fp64 full scan through ``mcp_index_search_exact_noalloc_device``: the library allocates nothing, so the
+        caller hands in the outputs too -- ``out = (ids int32 [Q,k], scores fp32 [Q,k], scores fp64 [Q,k])`` CUDA
+        tensors made ahead of time.  For request paths that must not hit cudaMalloc (it would stall a scan
+        running on another stream, or fail when HBM is fully budgeted).  At most 1,048,576 rows and 64 queries;
+        all calls on one device share one fixed scratch array, so keep them on one stream.  The first call on a
+        device does a one-time address look-up: make it before starting any stream capture."""
+        ids, sc, sc64 = out
+        nq = queries.shape[0]
+        assert tuple(ids.shape) == (nq, k) and ids.is_contiguous() and sc.is_contiguous() and sc64.is_contiguous()
+        nat.check(self._lib.mcp_index_search_exact_noalloc_device(
+            self._h, C.c_void_p(queries.data_ptr()), nq, int(k), C.c_void_p(ids.data_ptr()),
+            C.c_void_p(sc.data_ptr()), C.c_void_p(sc64.data_ptr()), _stream_ptr()))
+        return ids, sc, sc64
+
     def coarse_scores_device(self, queries, path="gemm_tf32"):
         """[Q, N] fp32 coarse scores exactly as one coarse kernel computes them (validation aid)."""
         import torch

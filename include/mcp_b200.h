@@ -118,6 +118,27 @@ int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_failures, int32
 int mcp_index_coarse_scores_device(mcp_index *idx, int path, const float *queries_device, int n_queries,
                                    float *out_scores_device, void *stream);
 
+/* ---- exact search that allocates nothing ----------------------------------------------------------
+ * (No counterpart in the reference.)  For callers that must not allocate device memory at request
+ * time: a planner thread serving /plan while another stream of the process is mid-scan (cudaMalloc /
+ * cudaFree serialise against the whole device and would stall it), or a process whose HBM is fully
+ * budgeted, where a late allocation can fail.  Runs the fp64 full scan -- the same answer as
+ * mcp_index_search_device with option "path" = MCP_PATH_EXACT_FP64 -- taking all scratch from one fixed
+ * array inside the library: MCP_NOALLOC_SCRATCH_BYTES of device memory held by every GPU that loads the
+ * library until the process exits.  Limits: the index holds at most MCP_NOALLOC_MAX_ROWS rows and
+ * n_queries <= MCP_NOALLOC_MAX_QUERIES; anything larger returns MCP_EINVAL.  The caller still passes
+ * queries and outputs (device pointers); the table must already be loaded (that is where memory is
+ * allocated).  The array is shared by every call on a device and keeps the previous call's contents; each
+ * call rewrites what it reads, but calls whose GPU work overlaps (other streams, other indexes on the same
+ * device) race on it -- keep them ordered.  The first call on a device looks up the array's device address
+ * (one-time set-up): make that first call before starting any stream capture.                            */
+#define MCP_NOALLOC_MAX_ROWS (1 << 20)
+#define MCP_NOALLOC_MAX_QUERIES 64
+#define MCP_NOALLOC_SCRATCH_BYTES ((8u << 20) + 4096u)
+int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_device, int n_queries, int k,
+                                          int32_t *out_ids_device, float *out_scores_device,
+                                          double *out_scores64_device, void *stream);
+
 /* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
  * query before exact rescoring, >= k), "max_fallback" (device-side fp64 re-scans per batch),
  * "time_coarse" (1 = bracket every coarse scan with CUDA events on the caller's stream; the sums
