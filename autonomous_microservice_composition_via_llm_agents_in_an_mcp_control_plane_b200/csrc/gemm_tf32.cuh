@@ -9,15 +9,23 @@
 // in shared memory by TMA (128-byte swizzle) and are consumed by kind::tf32 MMAs directly -- no
 // conversion pass, no shadow table, the bytes read are the fp32 table.
 //
-// Warp roles (192 threads, 1 CTA / SM, persistent over row tiles):
+// Warp roles (320 threads, 1 CTA / SM, persistent over row tiles):
 //   warp 0   TMA producer: per k-block one 16 KB query tile + one 32 KB row tile into a 4-stage ring
 //   warp 1   TMEM allocator + MMA issuer: 4 x tcgen05.mma (M128 N256 K8) per stage, tcgen05.commit
 //            frees the stage; the last commit of a tile publishes the accumulator
-//   warps 2-5  epilogue: tcgen05.ld the accumulator (double-buffered in TMEM: 2 x 256 columns),
+//   warps 2-9  epilogue (two warps per scheduler, each thread = one query x half of the tile's rows):
+//            tcgen05.ld the accumulator (double-buffered in TMEM: 2 x 256 columns),
 //            score = 1 - dot * inv|q| * inv|e| + penalty (or sqrt(|q|^2+|e|^2-2 dot) + penalty),
 //            compare with the thread's threshold, append survivors to the (CTA, query) list in
 //            global memory; a list that fills is cut back to k' by a register-only warp radix
 //            select, which also tightens the threshold.
+//
+// Threshold bootstrap.  A fresh list accepts everything, and with ~70 lists per query the start-up transient
+// (fill, prune, fill, prune ...) used to dominate the kernel.  Instead every CTA first reads its first tile only
+// to find, per query, its m smallest keys (m = ceil(k'/L), registers), publishes the m-th, and waits until the L
+// CTAs that share its queries have done the same (cooperative launch: all CTAs are co-resident).  The largest
+// published key t0 has at least L*m >= k' keys of the union below it, so it bounds the final k'-th key from
+// above and every list starts with it; the first tile is then read from TMEM a second time through the filter.
 //
 // Coarse error (certificate, rescore.cuh): kind::tf32 reads the top 19 bits of each fp32 operand,
 // i.e. truncates 13 mantissa bits: relative error < 2^-10 per operand, < 2^-9 (1 + 2^-11) per
@@ -31,7 +39,7 @@
 #define G_BN 256
 #define G_BK 32
 #define G_STAGES 4
-#define G_THREADS 192
+#define G_THREADS 320         // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 #define G_A_BYTES (G_BM * G_BK * 4)
 #define G_B_BYTES (G_BN * G_BK * 4)
 #define G_MAX_QBLOCKS 8
@@ -47,12 +55,17 @@ struct GemmArgs {
     u64 *lists;                // [nq][L][cap]
     int *list_cnt;             // [nq][L]
     float *dump;               // debug: [nq][n_rows] coarse scores instead of lists, or NULL
+    // cross-CTA bootstrap of the per-query threshold (cooperative launch only; boot_m == 0 disables it)
+    u64 *pub;                  // [nq][L]  each (CTA, query)'s boot_m-th smallest key of its first tile
+    unsigned int *arrive;      // [nqb]    CTAs of a query block that have published
+    int boot_m;
 };
+#define G_BOOT_MAX 8
 
 struct GemmSmem {
     float a[G_STAGES][G_BM * G_BK];
     float b[G_STAGES][G_BN * G_BK];
-    float meta[2][2][G_BN];
+    float2 meta[2][G_BN];      // per row of the tile: (inv|e| or |e|^2, penalty)
     u64 full[G_STAGES], empty[G_STAGES], tfull[2], tempty[2];
     uint32_t tmem_base;
 };
@@ -178,7 +191,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < G_STAGES; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull[i], 1); mbar_init(&s.tempty[i], 128); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull[i], 1); mbar_init(&s.tempty[i], 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -237,52 +250,123 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
         }
     } else {
-        // ===== epilogue: one thread = one query (TMEM lane) =====
+        // ===== epilogue: 8 warps; a thread = one query (TMEM lane) x one half of the tile's 256 rows =====
         const int quarter = warp & 3;                          // a warp may only touch TMEM lanes 32*(warp%4)..+31
+        const int half = (warp - 2) >> 2;                      // columns [half*128, half*128+128)
         const int m = quarter * 32 + lane;
         const int qg = qb * G_BM + m;
         const bool qvalid = qg < a.nq;
         const float inq = qvalid ? a.inv_nq[qg] : 0.f;
         const float nq2f = qvalid ? (float)a.nq2[qg] : 0.f;
-        const int et = threadIdx.x - 64;
-        u64 *mylist = a.lists + ((int64_t)(qvalid ? qg : 0) * ngroups + group) * CAP;
+        const int et = threadIdx.x - 64;                       // 0..255
+        const int L = 2 * ngroups, li = 2 * group + half;      // one list per (CTA, query, half)
+        u64 *mylist = a.lists + ((int64_t)(qvalid ? qg : 0) * L + li) * CAP;
         int cnt = 0;
-        u64 tau = ~0ull;
+        u64 tau = ~0ull;                                       // keys below tau are kept
+        float tau_f = qvalid ? CUDART_INF_F : -CUDART_INF_F;   // float image of tau: the common-case reject is one FSETP
+        auto score = [&](float acc, float2 mm) -> float {
+            if (METRIC == 0) return fmaf(-(acc * inq), mm.x, 1.0f) + mm.y;
+            return sqrtf(fmaxf(nq2f + mm.x - 2.0f * acc, 0.f)) + mm.y;
+        };
         for (int i = 0; i < my_tiles; ++i) {
             const int t = group + i * ngroups, buf = i & 1;
             const uint32_t tphase = (uint32_t)(i >> 1) & 1u;
             const int64_t row0 = (int64_t)t * G_BN;
             const int rows_here = (int)min((int64_t)G_BN, a.n_rows - row0);
             // per-row constants of this tile (meta[buf] was last read two tiles ago; the named barrier of the
-            // tile in between ordered those reads before these writes)
-            for (int r = et; r < G_BN; r += 128) {
-                const bool ok = r < rows_here;
-                float m0 = 0.f, m1 = 0.f;
-                if (ok) {
+            // tile in between ordered those reads before these writes).  Rows past the table get +inf.
+            {
+                const int r = et;
+                float m0 = 0.f, m1 = CUDART_INF_F;
+                if (r < rows_here) {
                     m0 = METRIC == 0 ? a.inv_ne[row0 + r] : (float)a.ne2[row0 + r];
                     m1 = a.penalty ? a.penalty[row0 + r] : 0.f;
                 }
-                s.meta[buf][0][r] = m0; s.meta[buf][1][r] = m1;
+                s.meta[buf][r] = make_float2(m0, m1);
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             mbar_wait(&s.tfull[buf], tphase);
             tc_fence_after();
-            const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * G_BN);
-            for (int c = 0; c < G_BN; c += 32) {
-                uint32_t v[32];
-                tc_ld_32x32(taddr + (uint32_t)c, v);
+            const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * G_BN + half * 128);
+            const int cbase = half * 128;
+            if (a.dump) {
+                for (int c = 0; c < 128; c += 32) {
+                    uint32_t v[32];
+                    tc_ld_32x32(taddr + (uint32_t)c, v);
+                    tc_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int r = cbase + c + j;
+                        if (qvalid && r < rows_here)
+                            a.dump[(int64_t)qg * a.n_rows + row0 + r] = score(__uint_as_float(v[j]), s.meta[buf][r]);
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&s.tempty[buf]);
+                continue;
+            }
+            if (i == 0 && a.boot_m > 0) {
+                // ---- bootstrap pass over the first tile: my m smallest keys, publish, wait, take the max ----
+                u64 best[G_BOOT_MAX];
+#pragma unroll
+                for (int b = 0; b < G_BOOT_MAX; ++b) best[b] = ~0ull;
+                float best_f = CUDART_NAN_F;                   // NaN: nothing is rejected until 8 keys are held
+                for (int c = 0; c < 128; c += 32) {
+                    uint32_t v[32];
+                    tc_ld_32x32(taddr + (uint32_t)c, v);
+                    tc_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int r = cbase + c + j;
+                        const float sc = score(__uint_as_float(v[j]), s.meta[buf][r]);
+                        if (!(sc > best_f)) {
+                            const u64 key = coarse_key(sc, (uint32_t)(row0 + r));
+                            if (r < rows_here && key < best[G_BOOT_MAX - 1]) {
+                                best[G_BOOT_MAX - 1] = key;
+#pragma unroll
+                                for (int b = G_BOOT_MAX - 1; b > 0; --b)
+                                    if (best[b] < best[b - 1]) { const u64 x = best[b]; best[b] = best[b - 1]; best[b - 1] = x; }
+                                best_f = ord_f32((uint32_t)(best[G_BOOT_MAX - 1] >> 32));
+                            }
+                        }
+                    }
+                }
+                u64 mine = best[0];
+#pragma unroll
+                for (int b = 1; b < G_BOOT_MAX; ++b) if (b == a.boot_m - 1) mine = best[b];
+                if (qvalid) a.pub[(int64_t)qg * L + li] = mine;
+                __threadfence();
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                if (et == 0) {
+                    atomicAdd(&a.arrive[qb], 1u);
+                    while (*(volatile unsigned int *)&a.arrive[qb] < (unsigned int)ngroups) __nanosleep(64);
+                    __threadfence();
+                }
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                if (qvalid) {
+                    u64 t0 = 0;
+                    for (int l = 0; l < L; ++l) {
+                        const u64 x = __ldcg(&a.pub[(int64_t)qg * L + l]);
+                        t0 = x > t0 ? x : t0;
+                    }
+                    tau = t0 == ~0ull ? t0 : t0 + 1ull;      // the filter is `key < tau`: keep the bounding key itself
+                    tau_f = t0 == ~0ull ? CUDART_INF_F : ord_f32((uint32_t)(t0 >> 32));
+                }
+            }
+            // ---- filter pass: TMEM loads are issued one chunk ahead of the arithmetic ----
+            uint32_t va[32], vb[32];
+            tc_ld_32x32(taddr, va);
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc) {
+                uint32_t (&v)[32] = (cc & 1) ? vb : va;
+                uint32_t (&vn)[32] = (cc & 1) ? va : vb;
                 tc_ld_wait();
+                if (cc + 1 < 4) tc_ld_32x32(taddr + (uint32_t)((cc + 1) * 32), vn);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const int r = c + j;
-                    const float acc = __uint_as_float(v[j]);
-                    const float m0 = s.meta[buf][0][r], m1 = s.meta[buf][1][r];
-                    float sc;
-                    if (METRIC == 0) sc = fmaf(-(acc * inq), m0, 1.0f) + m1;
-                    else             sc = sqrtf(fmaxf(nq2f + m0 - 2.0f * acc, 0.f)) + m1;
-                    if (a.dump) {
-                        if (qvalid && r < rows_here) a.dump[(int64_t)qg * a.n_rows + row0 + r] = sc;
-                    } else {
+                    const int r = cbase + cc * 32 + j;
+                    const float sc = score(__uint_as_float(v[j]), s.meta[buf][r]);
+                    if (!(sc > tau_f)) {                       // rare: at or below the threshold, or NaN
                         const u64 key = coarse_key(sc, (uint32_t)(row0 + r));
                         if (qvalid && r < rows_here && key < tau) mylist[cnt++] = key;
                     }
@@ -296,14 +380,14 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     const int n = __shfl_sync(MCP_FULL, cnt, src);
                     __syncwarp();
                     const u64 thr = warp_prune_list<KPL>(lp, n, a.kprime, lane);
-                    if (lane == src) { cnt = a.kprime; tau = thr; }
+                    if (lane == src) { cnt = a.kprime; tau = thr + 1ull; tau_f = ord_f32((uint32_t)(thr >> 32)); }
                     __syncwarp();
                 }
             }
             tc_fence_before();
             mbar_arrive(&s.tempty[buf]);
         }
-        if (qvalid && !a.dump) a.list_cnt[(int64_t)qg * ngroups + group] = cnt;
+        if (qvalid && !a.dump) a.list_cnt[(int64_t)qg * L + li] = cnt;
     }
     tc_fence_before();
     __syncthreads();
@@ -325,6 +409,8 @@ struct GemmPlan {
     int64_t n_rows = 0, ld = 0;
     int dim = 0;
     PFN_encodeTiled encode = nullptr;
+    int coop = -1;             // device supports cooperative launch (-1 = not asked yet)
+    bool allow_boot = true;    // option "gemm_bootstrap"
     char err[256] = {0};
 };
 
@@ -381,29 +467,51 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     const int n_tiles = (int)((n_rows + G_BN - 1) / G_BN);
     int ngroups = std::max(1, std::min(n_sm / nqb, n_tiles));
     const int kpl = gemm_kpl_for(kprime), cap = kpl * 32;
-    const size_t list_bytes = sizeof(u64) * (size_t)nq * ngroups * cap;
+    const int L = 2 * ngroups;                       // one list per (CTA, query, half tile)
+    const size_t list_bytes = sizeof(u64) * (size_t)nq * L * cap;
     const size_t cnt_off = (list_bytes + 255) & ~(size_t)255;
-    if ((rc = ws.ensure(cnt_off + sizeof(int) * (size_t)nq * ngroups))) { snprintf(p.err, sizeof p.err, "workspace allocation failed"); return rc; }
+    const size_t pub_off = (cnt_off + sizeof(int) * (size_t)nq * L + 255) & ~(size_t)255;
+    const size_t arr_off = (pub_off + sizeof(u64) * (size_t)nq * L + 255) & ~(size_t)255;
+    if ((rc = ws.ensure(arr_off + 256))) { snprintf(p.err, sizeof p.err, "workspace allocation failed"); return rc; }
+    unsigned char *wsb = reinterpret_cast<unsigned char *>(ws.p);
     GemmArgs a;
     a.n_rows = n_rows; a.dim = dim; a.nq = nq; a.nqb = nqb; a.kprime = kprime; a.cap = cap;
     a.inv_nq = inv_nq; a.nq2 = nq2; a.inv_ne = inv_ne; a.ne2 = ne2; a.penalty = penalty;
-    a.lists = reinterpret_cast<u64 *>(ws.p);
-    a.list_cnt = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(ws.p) + cnt_off);
+    a.lists = reinterpret_cast<u64 *>(wsb);
+    a.list_cnt = reinterpret_cast<int *>(wsb + cnt_off);
+    a.pub = reinterpret_cast<u64 *>(wsb + pub_off);
+    a.arrive = reinterpret_cast<unsigned int *>(wsb + arr_off);
     a.dump = dump;
+    // bootstrap needs every CTA of a query block resident at once: cooperative launch, grid <= #SMs (1 CTA / SM)
+    const int m = (kprime + L - 1) / L;
+    if (p.coop < 0) {
+        int dev = 0, v = 0;
+        cudaGetDevice(&dev);
+        p.coop = (cudaDeviceGetAttribute(&v, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && v) ? 1 : 0;
+    }
+    a.boot_m = (!dump && p.coop == 1 && m <= G_BOOT_MAX && nqb * ngroups <= n_sm && p.allow_boot) ? m : 0;
     const size_t smem = sizeof(GemmSmem) + 1024;
     cudaError_t e = cudaSuccess;
+    if (a.boot_m) e = cudaMemsetAsync(a.arrive, 0, sizeof(unsigned int) * G_MAX_QBLOCKS, st);
+    void *kargs[3] = {(void *)&tmA, (void *)&p.tmB, (void *)&a};
 #define G_LAUNCH(KPL, MET)                                                                                      \
     do {                                                                                                        \
-        e = cudaFuncSetAttribute(gemm_tf32_kernel<KPL, MET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e == cudaSuccess)                                                                                   \
+            e = cudaFuncSetAttribute(gemm_tf32_kernel<KPL, MET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e == cudaSuccess) {                                                                                 \
-            gemm_tf32_kernel<KPL, MET><<<nqb * ngroups, G_THREADS, smem, st>>>(tmA, p.tmB, a);                  \
-            e = cudaGetLastError();                                                                             \
+            if (a.boot_m)                                                                                       \
+                e = cudaLaunchCooperativeKernel((const void *)gemm_tf32_kernel<KPL, MET>, dim3(nqb * ngroups),  \
+                                                dim3(G_THREADS), kargs, smem, st);                              \
+            else {                                                                                              \
+                gemm_tf32_kernel<KPL, MET><<<nqb * ngroups, G_THREADS, smem, st>>>(tmA, p.tmB, a);              \
+                e = cudaGetLastError();                                                                         \
+            }                                                                                                   \
         }                                                                                                       \
     } while (0)
     if (metric == 0) { if (kpl == 4) G_LAUNCH(4, 0); else if (kpl == 8) G_LAUNCH(8, 0); else G_LAUNCH(16, 0); }
     else             { if (kpl == 4) G_LAUNCH(4, 1); else if (kpl == 8) G_LAUNCH(8, 1); else G_LAUNCH(16, 1); }
 #undef G_LAUNCH
     if (e != cudaSuccess) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch: %s", cudaGetErrorString(e)); return -2; }
-    *out_lists = a.lists; *out_cnt = a.list_cnt; *out_L = ngroups; *out_cap = cap;
+    *out_lists = a.lists; *out_cnt = a.list_cnt; *out_L = L; *out_cap = cap;
     return 0;
 }

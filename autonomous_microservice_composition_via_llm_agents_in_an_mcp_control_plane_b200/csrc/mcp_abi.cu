@@ -135,6 +135,7 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     CU(cudaEventCreateWithFlags(&idx->done, cudaEventDisableTiming));
     CU(cudaMallocHost(&idx->h_status, 4 * sizeof(int)));
     idx->h_status[0] = idx->h_status[1] = 0;
+    CU(cudaFuncSetAttribute(rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SMEM_BYTES(8192)));
     int rc = idx->consts.ensure(sizeof(TableConsts));
     if (!rc) rc = idx->flags.ensure(sizeof(int) * 4096);
     if (rc) { delete idx; return rc; }
@@ -280,6 +281,8 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
     } else if (!strcmp(name, "max_fallback")) {
         if (value < 1 || value > 64) return fail(MCP_EINVAL, "max_fallback %lld outside [1, 64]", (long long)value);
         idx->opt_max_fallback = (int)value;
+    } else if (!strcmp(name, "gemm_bootstrap")) {
+        idx->gemm.allow_boot = value != 0;
     } else if (!strcmp(name, "time_coarse")) {
         idx->opt_time_coarse = value != 0;
     } else
@@ -398,7 +401,7 @@ static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64
     while (L > 1 || first) {
         if (L == 1 && cap <= kprime) break;       // already one list of at most k' keys
         first = false;
-        int G = std::max(1, SEL_MAX / cap);
+        int G = std::max(1, std::min(SEL_MAX / cap, SEL_THREADS));
         int L_out = (L + G - 1) / G;
         Buf &ob = in_is_A ? idx->listsB : idx->listsA;
         Buf &oc = in_is_A ? idx->cntB : idx->cntA;
@@ -460,8 +463,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     if ((size_t)(nq + 8) * sizeof(int) > idx->flags.cap) return fail(MCP_EINVAL, "n_queries %d exceeds the flag buffer", nq);
     // flags: [0] n_flag (zero between kernels) [1] certificate failures [2] unresolved (both since last sync_status) [8..] list
     int *n_flag = idx->flags.as<int>(), *status = n_flag + 1, *flag_list = n_flag + 8;
-    prep_rows_kernel<true><<<(nq + PREP_ROWS - 1) / PREP_ROWS, PREP_ROWS, 0, st>>>(
-        d_q, nq, dim, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), nullptr);
+    prep_queries_kernel<<<nq, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
+        d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>());
     KL();
 
     idx->stats.searches++; idx->stats.queries += nq; idx->stats.last_path = path; idx->stats.last_kprime = kprime;
@@ -542,8 +545,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             else if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride)))
                 return rc;
         }
-        rescore_kernel<<<dim3((cand_stride + RESCORE_THREADS - 1) / RESCORE_THREADS, cq), RESCORE_THREADS,
-                         sizeof(float) * dim, st>>>(idx->d_rows, dim, idx->ld, dq, idx->nq2.as<double>() + q0,
+        rescore_kernel<<<dim3((cand_stride + RS_ROWS - 1) / RS_ROWS, cq), RESCORE_THREADS,
+                         RS_SMEM_BYTES(dim), st>>>(idx->d_rows, dim, idx->ld, dq, idx->nq2.as<double>() + q0,
                                                     idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt,
                                                     cand_stride, idx->exact_key.as<u64>(), idx->exact_row.as<int>());
         KL();
@@ -674,8 +677,8 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     if ((rc = idx->nq2.ensure(sizeof(double) * n_queries))) return rc;
     if ((rc = idx->inv_nq.ensure(sizeof(float) * n_queries))) return rc;
     if ((rc = idx->qflag.ensure(n_queries))) return rc;
-    prep_rows_kernel<true><<<(n_queries + PREP_ROWS - 1) / PREP_ROWS, PREP_ROWS, 0, st>>>(
-        queries_device, n_queries, dim, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), nullptr);
+    prep_queries_kernel<<<n_queries, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
+        queries_device, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>());
     KCHECK();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     if (path == MCP_PATH_STREAM_FP32) {

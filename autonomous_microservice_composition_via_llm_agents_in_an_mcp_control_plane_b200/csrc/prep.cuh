@@ -66,6 +66,43 @@ prep_rows_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64_
     }
 }
 
+// Query batches are small (<= a few thousand vectors), so the table kernel above (128 rows per CTA) would leave
+// the GPU empty: here one CTA owns one query, all threads pull it into shared memory at once, and thread 0 walks
+// it in index order (the fp64 chain is the latency floor: dim dependent FMAs).
+#define PREPQ_THREADS 128
+__global__ void __launch_bounds__(PREPQ_THREADS)
+prep_queries_kernel(const float *__restrict__ queries, int dim, double *__restrict__ norm2,
+                    float *__restrict__ inv_norm, unsigned char *__restrict__ qflag) {
+    extern __shared__ __align__(16) float sq_prep[];
+    __shared__ int s_bad;
+    const int q = blockIdx.x;
+    const float *src = queries + (int64_t)q * dim;
+    if (threadIdx.x == 0) s_bad = 0;
+    __syncthreads();
+    bool bad = false;
+    for (int i = threadIdx.x; i < dim; i += PREPQ_THREADS) {
+        float v = src[i];
+        bad |= !isfinite(v);
+        sq_prep[i] = v;
+    }
+    if (bad) s_bad = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double acc = 0.0;
+        int d4 = dim & ~3;
+        for (int i = 0; i < d4; i += 4) {
+            float4 v = *reinterpret_cast<const float4 *>(sq_prep + i);
+            acc = fma((double)v.x, (double)v.x, acc); acc = fma((double)v.y, (double)v.y, acc);
+            acc = fma((double)v.z, (double)v.z, acc); acc = fma((double)v.w, (double)v.w, acc);
+        }
+        for (int i = d4; i < dim; ++i) acc = fma((double)sq_prep[i], (double)sq_prep[i], acc);
+        norm2[q] = acc;
+        inv_norm[q] = (float)(1.0 / sqrt(acc));
+        bool odd = (acc != 0.0) && (acc < 1e-30 || acc > 1e30);
+        qflag[q] = (unsigned char)((s_bad ? 2 : 0) | ((odd || acc == 0.0 || s_bad) ? 1 : 0));
+    }
+}
+
 __global__ void penalty_stats_kernel(const float *__restrict__ pen, int64_t n, TableConsts *consts) {
     float mx = -CUDART_INF_F, amx = 0.f;
     bool bad = false;

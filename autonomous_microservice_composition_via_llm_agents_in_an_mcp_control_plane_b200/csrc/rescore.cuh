@@ -27,48 +27,102 @@ struct CertParams {
     double abs_pen;        // multiplier of pen_absmax for fp32 rounding of the final add
 };
 
-// ---- K4a: one thread per (query, candidate) ----------------------------------------------------
-// grid (ceil(kc / RESCORE_THREADS), Q). The query is staged in shared memory (broadcast reads);
-// each thread walks its own candidate row in index order.
+// ---- K4a: exact rescoring ------------------------------------------------------------------------
+// One CTA = one query x 32 candidates.  The fp64 chain of a candidate (dim dependent FMAs, index order) is
+// the latency floor, and on B200 the fp32 -> fp64 conversion (F2F, ~12 cycles per warp instruction, measured
+// with tools/fp64_latency.cu) costs more than the FMA itself.  So: the query is converted to fp64 once per CTA
+// by all threads and kept in shared memory; all 128 threads stream the 32 candidate rows through a 3-stage
+// cp.async ring (64 floats per row per stage, 256 contiguous bytes per row); the 32 lanes of warp 0 each walk
+// their own row out of shared memory, converting only the row element.  grid (ceil(stride / 32), Q).
+#define RS_ROWS 32
+#define RS_COLS 64
+#define RS_PITCH (RS_COLS + 4)        // fp32 ring row pitch (floats): 16-byte aligned rows, conflict-free LDS.128
+#define RS_STAGES 3
+#define RS_SMEM_BYTES(dim) (sizeof(double) * (((dim) + 3) & ~3) + sizeof(float) * RS_STAGES * RS_ROWS * RS_PITCH + 16)
+__device__ __forceinline__ void cp_async16(void *dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 __global__ void __launch_bounds__(RESCORE_THREADS)
 rescore_kernel(const float *__restrict__ rows, int dim, int64_t ld,
                const float *__restrict__ queries, const double *__restrict__ nq2,
                const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
                const u64 *__restrict__ cand, const int *__restrict__ cand_cnt, int cand_stride,
                u64 *__restrict__ exact_key, int *__restrict__ exact_row) {
-    extern __shared__ float sqv[];
-    int q = blockIdx.y;
+    extern __shared__ __align__(16) unsigned char rs_raw[];
+    const int dimp = (dim + 3) & ~3;                       // rows are padded with zeros up to ld >= dimp
+    double *sq = reinterpret_cast<double *>(rs_raw);       // [dimp] the query, already fp64
+    float *tile = reinterpret_cast<float *>(sq + dimp);    // [RS_STAGES][RS_ROWS][RS_PITCH]
+    __shared__ int s_row[RS_ROWS];
+    const int q = blockIdx.y, j0 = blockIdx.x * RS_ROWS;
+    const int cnt = min(cand_cnt[q], cand_stride);
+    if (j0 >= cand_stride) return;
     const float *qv = queries + (int64_t)q * dim;
-    for (int i = threadIdx.x; i < dim; i += blockDim.x) sqv[i] = qv[i];
-    __syncthreads();
-    int j = blockIdx.x * blockDim.x + threadIdx.x;
-    int cnt = cand_cnt[q];
-    if (j >= cand_stride) return;
-    int64_t o = (int64_t)q * cand_stride + j;
-    if (j >= cnt) { exact_key[o] = ~0ull; exact_row[o] = MCP_PAD_ROW; return; }
-    uint32_t row = (uint32_t)(cand[o] & 0xFFFFFFFFull);
-    const float *e = rows + (int64_t)row * ld;
-    ExactAcc a; a.acc = 0.0;
-    int d4 = dim & ~3;
-    if (metric == 0) {
-        for (int i = 0; i < d4; i += 4) {
-            float4 v = *reinterpret_cast<const float4 *>(e + i);
-            a.cos_step(sqv[i], v.x); a.cos_step(sqv[i + 1], v.y);
-            a.cos_step(sqv[i + 2], v.z); a.cos_step(sqv[i + 3], v.w);
-        }
-        for (int i = d4; i < dim; ++i) a.cos_step(sqv[i], e[i]);
-    } else {
-        for (int i = 0; i < d4; i += 4) {
-            float4 v = *reinterpret_cast<const float4 *>(e + i);
-            a.l2_step(sqv[i], v.x); a.l2_step(sqv[i + 1], v.y);
-            a.l2_step(sqv[i + 2], v.z); a.l2_step(sqv[i + 3], v.w);
-        }
-        for (int i = d4; i < dim; ++i) a.l2_step(sqv[i], e[i]);
+    for (int i = threadIdx.x; i < dimp; i += blockDim.x) sq[i] = i < dim ? (double)qv[i] : 0.0;
+    if (threadIdx.x < RS_ROWS) {
+        int j = j0 + threadIdx.x;
+        s_row[threadIdx.x] = (j < cnt) ? (int)(cand[(int64_t)q * cand_stride + j] & 0xFFFFFFFFull) : -1;
     }
-    double s = exact_finish(a.acc, metric, nq2[q], ne2[row]);
-    if (penalty) s = s + (double)penalty[row];
-    exact_key[o] = f64_ord(s);
-    exact_row[o] = (int)row;
+    __syncthreads();
+    const int nchunks = (dimp + RS_COLS - 1) / RS_COLS;
+    auto issue = [&](int c) {
+        if (c < nchunks) {
+            const int c0 = c * RS_COLS, w4 = min(RS_COLS, dimp - c0) >> 2;
+            float *dst = tile + (size_t)(c % RS_STAGES) * RS_ROWS * RS_PITCH;
+#pragma unroll
+            for (int u = 0; u < (RS_ROWS * RS_COLS / 4) / RESCORE_THREADS; ++u) {
+                const int f = threadIdx.x + u * RESCORE_THREADS, rr = f / (RS_COLS / 4), c4 = f % (RS_COLS / 4);
+                const int row = s_row[rr];
+                if (row >= 0 && c4 < w4) cp_async16(dst + rr * RS_PITCH + c4 * 4, rows + (int64_t)row * ld + c0 + c4 * 4);
+            }
+        }
+        cp_async_commit();
+    };
+    for (int c = 0; c < RS_STAGES - 1; ++c) issue(c);
+    double acc = 0.0;
+    for (int c = 0; c < nchunks; ++c) {
+        cp_async_wait<RS_STAGES - 2>();
+        __syncthreads();                                   // chunk c has landed; everyone is done with chunk c-1's stage
+        issue(c + RS_STAGES - 1);
+        if (threadIdx.x < RS_ROWS) {
+            const int c0 = c * RS_COLS, w = min(RS_COLS, dimp - c0);
+            const float *e = tile + (size_t)(c % RS_STAGES) * RS_ROWS * RS_PITCH + threadIdx.x * RS_PITCH;
+            const double *qq = sq + c0;
+            if (metric == 0) {
+#pragma unroll 4
+                for (int i = 0; i < w; i += 4) {
+                    const float4 v = *reinterpret_cast<const float4 *>(e + i);
+                    const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
+                    acc = fma(u0.x, (double)v.x, acc); acc = fma(u0.y, (double)v.y, acc);
+                    acc = fma(u1.x, (double)v.z, acc); acc = fma(u1.y, (double)v.w, acc);
+                }
+            } else {
+#pragma unroll 4
+                for (int i = 0; i < w; i += 4) {
+                    const float4 v = *reinterpret_cast<const float4 *>(e + i);
+                    const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
+                    double d;
+                    d = __dsub_rn(u0.x, (double)v.x); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                    d = __dsub_rn(u0.y, (double)v.y); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                    d = __dsub_rn(u1.x, (double)v.z); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                    d = __dsub_rn(u1.y, (double)v.w); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                }
+            }
+        }
+    }
+    if (threadIdx.x < RS_ROWS && j0 + threadIdx.x < cand_stride) {
+        const int64_t o = (int64_t)q * cand_stride + j0 + threadIdx.x;
+        const int row = s_row[threadIdx.x];
+        if (row < 0) { exact_key[o] = ~0ull; exact_row[o] = MCP_PAD_ROW; }
+        else {
+            double s = exact_finish(acc, metric, nq2[q], ne2[row]);
+            if (penalty) s = s + (double)penalty[row];
+            exact_key[o] = f64_ord(s);
+            exact_row[o] = row;
+        }
+    }
 }
 
 // ---- K4b: final sort + outputs + certificate; one CTA per query --------------------------------

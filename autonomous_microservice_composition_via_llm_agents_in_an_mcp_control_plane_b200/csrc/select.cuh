@@ -99,28 +99,50 @@ select_from_scores_kernel(const float *__restrict__ scores, int64_t score_stride
 }
 
 // Stage B: lists[q][L_in][cap_in] -> lists[q][L_out][cap_out]; group g reduces G consecutive
-// input lists (G * cap_in <= SEL_MAX).  grid (L_out, Q).
+// input lists (G * cap_in <= SEL_MAX, G <= SEL_THREADS).  grid (L_out, Q).
+// Lists are usually far from full: when all of a query's lists together fit one CTA, group 0 takes them all and
+// the other groups hand back empty lists (the launch shape stays static, the work does not).
 __global__ void __launch_bounds__(SEL_THREADS)
 select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_cnt, int L_in,
                          int cap_in, int G, int kprime, u64 *__restrict__ out,
                          int *__restrict__ out_cnt, int cap_out) {
     __shared__ SelectSmem s;
-    __shared__ int base[SEL_MAX / 8 + 1];
-    int g = blockIdx.x, q = blockIdx.y, L_out = gridDim.x;
+    __shared__ int base[SEL_THREADS + 1];      // exclusive prefix of the list lengths
+    __shared__ int wsum[SEL_THREADS / 32];
+    const int g = blockIdx.x, q = blockIdx.y, L_out = gridDim.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // list lengths, one per thread, and their block-wide exclusive scan: all lists of the query when there are
+    // at most SEL_THREADS of them (lets group 0 take everything), else just this group's
     int l0 = g * G, l1 = min(l0 + G, L_in);
-    if (threadIdx.x == 0) {
-        int run = 0;
-        for (int l = l0; l < l1; ++l) { base[l - l0] = run; run += min(in_cnt[(int64_t)q * L_in + l], cap_in); }
-        base[l1 - l0] = run;
+    const bool whole = L_in <= SEL_THREADS;
+    const int lb = whole ? 0 : l0, nl = whole ? L_in : l1 - l0;
+    const int mycnt = (int)threadIdx.x < nl ? min(in_cnt[(int64_t)q * L_in + lb + threadIdx.x], cap_in) : 0;
+    int incl = mycnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(MCP_FULL, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < SEL_THREADS / 32 ? wsum[lane] : 0, wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(MCP_FULL, wi, o); if (lane >= o) wi += t; }
+        if (lane < SEL_THREADS / 32) wsum[lane] = wi - w;
     }
     __syncthreads();
-    int n = base[l1 - l0];
-    for (int l = l0; l < l1; ++l) {
-        int b = base[l - l0], c = base[l - l0 + 1] - b;
+    base[threadIdx.x] = wsum[warp] + incl - mycnt;             // base[i] = keys before list lb + i
+    if (threadIdx.x == SEL_THREADS - 1) base[SEL_THREADS] = wsum[warp] + incl;
+    __syncthreads();
+    if (whole && base[SEL_THREADS] <= SEL_MAX) {
+        if (g != 0) { if (threadIdx.x == 0) out_cnt[(int64_t)q * L_out + g] = 0; return; }
+        l0 = 0; l1 = L_in;
+    }
+    const int off = base[l0 - lb], n = base[l1 - lb] - off;
+    for (int l = l0 + warp; l < l1; l += SEL_THREADS / 32) {      // one warp per list
+        const int b = base[l - lb] - off, c = base[l - lb + 1] - base[l - lb];
         const u64 *src = in + ((int64_t)q * L_in + l) * cap_in;
-        for (int i = threadIdx.x; i < c; i += blockDim.x) s.keys[b + i] = src[i];
+        for (int i = lane; i < c; i += 32) s.keys[b + i] = src[i];
     }
     __syncthreads();
-    int64_t lo = (int64_t)q * L_out + g;
+    const int64_t lo = (int64_t)q * L_out + g;
     cta_select_write(s, n, min(kprime, n), out + lo * cap_out, out_cnt + lo);
 }

@@ -141,6 +141,7 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
 
 /* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
  * query before exact rescoring, >= k), "max_fallback" (device-side fp64 re-scans per batch),
+ * "gemm_bootstrap" (0 = K2 without the cross-CTA threshold bootstrap; default 1),
  * "time_coarse" (1 = bracket every coarse scan with CUDA events on the caller's stream; the sums
  * appear in mcp_stats after mcp_index_sync_status).                                            */
 int mcp_index_set_option(mcp_index *idx, const char *name, int64_t value);
