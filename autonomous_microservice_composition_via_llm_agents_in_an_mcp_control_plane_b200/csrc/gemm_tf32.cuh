@@ -38,8 +38,6 @@
 #define G_BM 128
 #define G_BN 256
 #define G_BK 32
-#define G_STAGES 4
-#define G_THREADS 320         // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 #define G_A_BYTES (G_BM * G_BK * 4)
 #define G_B_BYTES (G_BN * G_BK * 4)
 #define G_MAX_QBLOCKS 8
@@ -58,17 +56,14 @@ struct GemmArgs {
     // cross-CTA bootstrap of the per-query threshold (cooperative launch only; boot_m == 0 disables it)
     u64 *pub;                  // [nq][L]  each (CTA, query)'s boot_m-th smallest key of its first tile
     unsigned int *arrive;      // [nqb]    CTAs of a query block that have published
-    int boot_m;
+    int boot_m, boot_lists;    // lists 0 .. boot_lists-1 publish their boot_m-th smallest key (boot_lists even)
+    const float *rows;         // table base + row pitch, for the L2 row prefetch
+    int64_t ld;
+    int l2_prefetch;
+    int debug;                 // timing experiments only (results are wrong): 1 skip epilogue math, 2 skip row-tile loads, 4 skip query-tile loads, 8 skip MMAs
 };
-#define G_BOOT_MAX 8
+#define G_BOOT_MAX 4
 
-struct GemmSmem {
-    float a[G_STAGES][G_BM * G_BK];
-    float b[G_STAGES][G_BN * G_BK];
-    float2 meta[2][G_BN];      // per row of the tile: (inv|e| or |e|^2, penalty)
-    u64 full[G_STAGES], empty[G_STAGES], tfull[2], tempty[2];
-    uint32_t tmem_base;
-};
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -131,6 +126,10 @@ __device__ __forceinline__ u64 umma_desc_k128(const void *tile) {
 // N >> 3 at [17,23), M >> 4 at [24,29)
 #define G_IDESC ((1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(G_BN >> 3) << 17) | ((uint32_t)(G_BM >> 4) << 24))
 
+// K2 lists store raw pairs (fp32 score bits << 32 | row); selection works on the ordered image
+__device__ __forceinline__ u64 raw_to_key(u64 raw) { return ((u64)f32_ord(__uint_as_float((uint32_t)(raw >> 32))) << 32) | (raw & 0xFFFFFFFFull); }
+__device__ __forceinline__ u64 key_to_raw(u64 key) { return ((u64)__float_as_uint(ord_f32((uint32_t)(key >> 32))) << 32) | (key & 0xFFFFFFFFull); }
+
 // ---- register-only warp radix select --------------------------------------------------------------
 // The warp cuts lane `src`'s list (n keys in global memory, n > kprime) back to its kprime smallest
 // keys and returns the largest kept key (the new threshold).  Keys are unique.
@@ -141,7 +140,7 @@ __device__ __forceinline__ u64 warp_prune_list(u64 *lp, int n, int kprime, int l
 #pragma unroll
     for (int i = 0; i < KPL; ++i) {
         int idx = i * 32 + lane;
-        kk[i] = idx < n ? lp[idx] : ~0ull;
+        kk[i] = idx < n ? raw_to_key(lp[idx]) : ~0ull;
         act |= (idx < n ? 1u : 0u) << i;
     }
     int need = kprime, tot = n;
@@ -171,17 +170,42 @@ __device__ __forceinline__ u64 warp_prune_list(u64 *lp, int n, int kprime, int l
     for (int i = 0; i < KPL; ++i) {
         bool keep = kk[i] <= mx;
         uint32_t b = __ballot_sync(MCP_FULL, keep);
-        if (keep) lp[base + __popc(b & ((1u << lane) - 1u))] = kk[i];
+        if (keep) lp[base + __popc(b & ((1u << lane) - 1u))] = key_to_raw(kk[i]);
         base += __popc(b);
     }
     return mx;
 }
 
-template <int KPL, int METRIC>
-__global__ void __launch_bounds__(G_THREADS, 1)
+// MT = query blocks (of 128) per CTA.
+//   MT = 1: D[128 x 256], TMEM double-buffered (2 x 256 columns): epilogue of tile i overlaps the MMAs of tile i+1;
+//           48 KB per k-block stage, 4 stages.
+//   MT = 2: D[256 x 256] as two accumulators sharing the row tile (all 512 TMEM columns, single-buffered): the row
+//           tile is fetched once for 256 queries, which cuts shared-memory fill traffic per output by a third
+//           (6144 B x (1/256 + 1/256) instead of (1/128 + 1/256)); 64 KB per stage, 3 stages.  K2 is bound by
+//           L2 -> SM fill bandwidth (profiles/), so this is the better trade whenever there are >= 256 queries.
+template <int MT> struct GemmCfg {
+    static constexpr int STAGES = MT == 1 ? 4 : 3;
+    static constexpr int NBUF = MT == 1 ? 2 : 1;
+    static constexpr int A_BYTES = MT * G_BM * G_BK * 4;
+    static constexpr int EPI_THREADS = 256 * MT;
+    static constexpr int THREADS = 64 + EPI_THREADS;
+};
+template <int MT> struct GemmSmemT {
+    float a[GemmCfg<MT>::STAGES][MT * G_BM * G_BK];
+    float b[GemmCfg<MT>::STAGES][G_BN * G_BK];
+    float2 meta[2][G_BN];      // per row of the tile: (inv|e| or |e|^2, penalty)
+    u64 full[GemmCfg<MT>::STAGES], empty[GemmCfg<MT>::STAGES], tfull[2], tempty[2];
+    uint32_t tmem_base;
+};
+
+template <int MT, int KPL, int METRIC>
+__global__ void __launch_bounds__(GemmCfg<MT>::THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs a) {
+    using Cfg = GemmCfg<MT>;
     extern __shared__ unsigned char g_smem_raw[];
-    GemmSmem &s = *reinterpret_cast<GemmSmem *>(((uintptr_t)g_smem_raw + 1023) & ~(uintptr_t)1023);
+    // 1024-byte alignment for the 128-byte swizzle; plain pointer arithmetic on the __shared__ array keeps the
+    // accesses in the shared address space (a uintptr_t round trip turns them into generic loads)
+    GemmSmemT<MT> &s = *reinterpret_cast<GemmSmemT<MT> *>(g_smem_raw + ((1024u - (smem_u32(g_smem_raw) & 1023u)) & 1023u));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qb = blockIdx.x % a.nqb, group = blockIdx.x / a.nqb, ngroups = gridDim.x / a.nqb;
     const int n_tiles = (int)((a.n_rows + G_BN - 1) / G_BN);
@@ -190,8 +214,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     constexpr int CAP = KPL * 32;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < G_STAGES; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull[i], 1); mbar_init(&s.tempty[i], 256); }
+        for (int i = 0; i < Cfg::STAGES; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull[i], 1); mbar_init(&s.tempty[i], Cfg::EPI_THREADS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -214,14 +238,33 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int i = 0; i < my_tiles; ++i) {
             const int t = group + i * ngroups;
             for (int kb = 0; kb < KB; ++kb) {
+                // DRAM locality: a TMA box touches 256 rows x 128 B, i.e. 256 different DRAM pages, and comes back to
+                // each page one k-block later, long after other tiles have closed it.  Every 8 k-blocks the query
+                // block 0 CTA therefore pulls the *next* 1 KB of each of the tile's rows into L2 with one bulk prefetch
+                // per row (8 rows per lane): DRAM sees 1 KB bursts, the TMA boxes that follow hit L2.
+                if (a.l2_prefetch && qb == 0 && (kb & 7) == 0) {
+                    int pt = t, pk = kb + 8;
+                    if (pk >= KB) { pt = t + ngroups; pk = 0; }
+                    if (pt < n_tiles) {
+                        const int bytes = min(8 * G_BK, a.dim - pk * G_BK) * 4;
+                        const int64_t prow0 = (int64_t)pt * G_BN;
+#pragma unroll
+                        for (int u = 0; u < G_BN / 32; ++u) {
+                            const int64_t r = prow0 + u * 32 + lane;
+                            if (r < a.n_rows && bytes > 0)
+                                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.rows + r * a.ld + pk * G_BK), "r"(bytes & ~15) : "memory");
+                        }
+                    }
+                }
                 mbar_wait(&s.empty[stage], phase ^ 1u);
                 if (lane == 0) {
-                    mbar_expect_tx(&s.full[stage], G_A_BYTES + G_B_BYTES);
-                    tma_load_2d(s.a[stage], &tmA, kb * G_BK, qb * G_BM, &s.full[stage]);
-                    tma_load_2d(s.b[stage], &tmB, kb * G_BK, t * G_BN, &s.full[stage]);
+                    const bool la = !(a.debug & 4) || (i == 0 && kb < Cfg::STAGES), lb = !(a.debug & 2) || (i == 0 && kb < Cfg::STAGES);
+                    mbar_expect_tx(&s.full[stage], (la ? Cfg::A_BYTES : 0) + (lb ? G_B_BYTES : 0));
+                    if (la) tma_load_2d(s.a[stage], &tmA, kb * G_BK, qb * MT * G_BM, &s.full[stage]);
+                    if (lb) tma_load_2d(s.b[stage], &tmB, kb * G_BK, t * G_BN, &s.full[stage]);
                 }
                 __syncwarp();
-                if (++stage == G_STAGES) { stage = 0; phase ^= 1u; }
+                if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
             }
         }
     } else if (warp == 1) {
@@ -229,8 +272,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         int stage = 0;
         uint32_t phase = 0;
         for (int i = 0; i < my_tiles; ++i) {
-            const int buf = i & 1;
-            const uint32_t tphase = (uint32_t)(i >> 1) & 1u;
+            const int buf = i % Cfg::NBUF;
+            const uint32_t tphase = (uint32_t)(i / Cfg::NBUF) & 1u;
             mbar_wait(&s.tempty[buf], tphase ^ 1u);           // epilogue has drained this accumulator
             tc_fence_after();
             const uint32_t d_tmem = tmem + (uint32_t)(buf * G_BN);
@@ -240,55 +283,60 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (lane == 0) {
                     const u64 ad = umma_desc_k128(s.a[stage]), bd = umma_desc_k128(s.b[stage]);
 #pragma unroll
-                    for (int k = 0; k < G_BK / 8; ++k)        // +32 bytes along K inside the swizzle atom = +2 in the address field
-                        tc_mma_tf32(d_tmem, ad + (u64)(2 * k), bd + (u64)(2 * k), G_IDESC, (uint32_t)((kb | k) != 0));
+                    for (int k = 0; k < G_BK / 8; ++k) {      // +32 bytes along K inside the swizzle atom = +2 in the address field
+#pragma unroll
+                        for (int mt = 0; mt < MT; ++mt)       // query block mt: A rows 128*mt.. (16 KB further), accumulator columns 256*mt..
+                            if (!(a.debug & 8) || k == 0) tc_mma_tf32(d_tmem + (uint32_t)(mt * G_BN), ad + (u64)(2 * k) + (u64)(mt * (G_A_BYTES >> 4)),
+                                        bd + (u64)(2 * k), G_IDESC, (uint32_t)((kb | k) != 0));
+                    }
                     tc_commit(&s.empty[stage]);               // frees the smem stage when these MMAs retire
                     if (kb == KB - 1) tc_commit(&s.tfull[buf]);
                 }
                 __syncwarp();
-                if (++stage == G_STAGES) { stage = 0; phase ^= 1u; }
+                if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
             }
         }
     } else {
-        // ===== epilogue: 8 warps; a thread = one query (TMEM lane) x one half of the tile's 256 rows =====
+        // ===== epilogue: 8 warps per query block; a thread = one query (TMEM lane) x one half of the tile's 256 rows =====
         const int quarter = warp & 3;                          // a warp may only touch TMEM lanes 32*(warp%4)..+31
-        const int half = (warp - 2) >> 2;                      // columns [half*128, half*128+128)
+        const int egrp = (warp - 2) >> 2;                      // 0 .. 2*MT-1
+        const int mt = egrp >> 1, half = egrp & 1;             // query block within the CTA, columns [half*128, +128)
         const int m = quarter * 32 + lane;
-        const int qg = qb * G_BM + m;
+        const int qg = (qb * MT + mt) * G_BM + m;
         const bool qvalid = qg < a.nq;
         const float inq = qvalid ? a.inv_nq[qg] : 0.f;
         const float nq2f = qvalid ? (float)a.nq2[qg] : 0.f;
-        const int et = threadIdx.x - 64;                       // 0..255
+        const int et = threadIdx.x - 64;                       // 0 .. EPI_THREADS-1
         const int L = 2 * ngroups, li = 2 * group + half;      // one list per (CTA, query, half)
         u64 *mylist = a.lists + ((int64_t)(qvalid ? qg : 0) * L + li) * CAP;
         int cnt = 0;
-        u64 tau = ~0ull;                                       // keys below tau are kept
         float tau_f = qvalid ? CUDART_INF_F : -CUDART_INF_F;   // float image of tau: the common-case reject is one FSETP
         auto score = [&](float acc, float2 mm) -> float {
             if (METRIC == 0) return fmaf(-(acc * inq), mm.x, 1.0f) + mm.y;
             return sqrtf(fmaxf(nq2f + mm.x - 2.0f * acc, 0.f)) + mm.y;
         };
         for (int i = 0; i < my_tiles; ++i) {
-            const int t = group + i * ngroups, buf = i & 1;
-            const uint32_t tphase = (uint32_t)(i >> 1) & 1u;
+            const int t = group + i * ngroups, buf = i % Cfg::NBUF, mbuf = i & 1;
+            const uint32_t tphase = (uint32_t)(i / Cfg::NBUF) & 1u;
             const int64_t row0 = (int64_t)t * G_BN;
             const int rows_here = (int)min((int64_t)G_BN, a.n_rows - row0);
-            // per-row constants of this tile (meta[buf] was last read two tiles ago; the named barrier of the
+            // per-row constants of this tile (meta[mbuf] was last read two tiles ago; the named barrier of the
             // tile in between ordered those reads before these writes).  Rows past the table get +inf.
-            {
+            if (et < G_BN) {
                 const int r = et;
                 float m0 = 0.f, m1 = CUDART_INF_F;
                 if (r < rows_here) {
                     m0 = METRIC == 0 ? a.inv_ne[row0 + r] : (float)a.ne2[row0 + r];
                     m1 = a.penalty ? a.penalty[row0 + r] : 0.f;
                 }
-                s.meta[buf][r] = make_float2(m0, m1);
+                s.meta[mbuf][r] = make_float2(m0, m1);
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(Cfg::EPI_THREADS) : "memory");
             mbar_wait(&s.tfull[buf], tphase);
             tc_fence_after();
-            const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * G_BN + half * 128);
+            const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * G_BN + mt * G_BN + half * 128);
             const int cbase = half * 128;
+            if (a.debug & 1) { tc_fence_before(); mbar_arrive(&s.tempty[buf]); continue; }
             if (a.dump) {
                 for (int c = 0; c < 128; c += 32) {
                     uint32_t v[32];
@@ -298,7 +346,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     for (int j = 0; j < 32; ++j) {
                         const int r = cbase + c + j;
                         if (qvalid && r < rows_here)
-                            a.dump[(int64_t)qg * a.n_rows + row0 + r] = score(__uint_as_float(v[j]), s.meta[buf][r]);
+                            a.dump[(int64_t)qg * a.n_rows + row0 + r] = score(__uint_as_float(v[j]), s.meta[mbuf][r]);
                     }
                 }
                 tc_fence_before();
@@ -307,10 +355,9 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             if (i == 0 && a.boot_m > 0) {
                 // ---- bootstrap pass over the first tile: my m smallest keys, publish, wait, take the max ----
-                u64 best[G_BOOT_MAX];
-#pragma unroll
-                for (int b = 0; b < G_BOOT_MAX; ++b) best[b] = ~0ull;
-                float best_f = CUDART_NAN_F;                   // NaN: nothing is rejected until 8 keys are held
+                // four smallest keys in scalars (an indexed array ends up in local memory)
+                u64 b0 = ~0ull, b1 = ~0ull, b2 = ~0ull, b3 = ~0ull;
+                float best_f = CUDART_NAN_F;                   // NaN: nothing is rejected until 4 keys are held
                 for (int c = 0; c < 128; c += 32) {
                     uint32_t v[32];
                     tc_ld_32x32(taddr + (uint32_t)c, v);
@@ -318,57 +365,56 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const int r = cbase + c + j;
-                        const float sc = score(__uint_as_float(v[j]), s.meta[buf][r]);
+                        const float sc = score(__uint_as_float(v[j]), s.meta[mbuf][r]);
                         if (!(sc > best_f)) {
                             const u64 key = coarse_key(sc, (uint32_t)(row0 + r));
-                            if (r < rows_here && key < best[G_BOOT_MAX - 1]) {
-                                best[G_BOOT_MAX - 1] = key;
-#pragma unroll
-                                for (int b = G_BOOT_MAX - 1; b > 0; --b)
-                                    if (best[b] < best[b - 1]) { const u64 x = best[b]; best[b] = best[b - 1]; best[b - 1] = x; }
-                                best_f = ord_f32((uint32_t)(best[G_BOOT_MAX - 1] >> 32));
+                            if (r < rows_here && key < b3) {
+                                b3 = key;
+                                if (b3 < b2) { const u64 x = b3; b3 = b2; b2 = x; }
+                                if (b2 < b1) { const u64 x = b2; b2 = b1; b1 = x; }
+                                if (b1 < b0) { const u64 x = b1; b1 = b0; b0 = x; }
+                                best_f = ord_f32((uint32_t)(b3 >> 32));
                             }
                         }
                     }
                 }
-                u64 mine = best[0];
-#pragma unroll
-                for (int b = 1; b < G_BOOT_MAX; ++b) if (b == a.boot_m - 1) mine = best[b];
-                if (qvalid) a.pub[(int64_t)qg * L + li] = mine;
+                const u64 mine = a.boot_m == 1 ? b0 : a.boot_m == 2 ? b1 : a.boot_m == 3 ? b2 : b3;
+                // only the first boot_lists lists (CTAs with group < boot_lists/2) publish and are waited for:
+                // boot_lists * boot_m >= k' keys below the maximum is all the bound needs, and fewer lists -> lower maximum
+                if (qvalid && li < a.boot_lists) a.pub[(int64_t)qg * a.boot_lists + li] = mine;
                 __threadfence();
-                asm volatile("bar.sync 1, 256;" ::: "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(Cfg::EPI_THREADS) : "memory");
                 if (et == 0) {
-                    atomicAdd(&a.arrive[qb], 1u);
-                    while (*(volatile unsigned int *)&a.arrive[qb] < (unsigned int)ngroups) __nanosleep(64);
+                    const unsigned int want = (unsigned int)min(ngroups, (a.boot_lists + 1) / 2);
+                    if (2 * group < a.boot_lists) atomicAdd(&a.arrive[qb], 1u);
+                    while (*(volatile unsigned int *)&a.arrive[qb] < want) __nanosleep(32);
                     __threadfence();
                 }
-                asm volatile("bar.sync 1, 256;" ::: "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(Cfg::EPI_THREADS) : "memory");
                 if (qvalid) {
                     u64 t0 = 0;
-                    for (int l = 0; l < L; ++l) {
-                        const u64 x = __ldcg(&a.pub[(int64_t)qg * L + l]);
-                        t0 = x > t0 ? x : t0;
+                    const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(a.pub + (int64_t)qg * a.boot_lists);
+                    for (int l = 0; l < a.boot_lists / 2; ++l) {
+                        const ulonglong2 x = __ldcg(pp + l);
+                        t0 = x.x > t0 ? x.x : t0; t0 = x.y > t0 ? x.y : t0;
                     }
-                    tau = t0 == ~0ull ? t0 : t0 + 1ull;      // the filter is `key < tau`: keep the bounding key itself
-                    tau_f = t0 == ~0ull ? CUDART_INF_F : ord_f32((uint32_t)(t0 >> 32));
+                    tau_f = t0 == ~0ull ? CUDART_INF_F : ord_f32((uint32_t)(t0 >> 32));   // scores up to and including the bound pass
                 }
             }
-            // ---- filter pass: TMEM loads are issued one chunk ahead of the arithmetic ----
-            uint32_t va[32], vb[32];
-            tc_ld_32x32(taddr, va);
-#pragma unroll
-            for (int cc = 0; cc < 4; ++cc) {
-                uint32_t (&v)[32] = (cc & 1) ? vb : va;
-                uint32_t (&vn)[32] = (cc & 1) ? va : vb;
+            // ---- filter pass ----
+            // Lists hold raw (fp32 score bits, row) pairs: the ordered image is only built when a list is read
+            // (prune, select), so an append is a predicate, one store and one add.  With ~4 % of the scores
+            // passing per lane, some lane of the warp passes most of the time, so this path must stay short.
+            for (int c = 0; c < 128; c += 32) {
+                uint32_t v[32];
+                tc_ld_32x32(taddr + (uint32_t)c, v);
                 tc_ld_wait();
-                if (cc + 1 < 4) tc_ld_32x32(taddr + (uint32_t)((cc + 1) * 32), vn);
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const int r = cbase + cc * 32 + j;
-                    const float sc = score(__uint_as_float(v[j]), s.meta[buf][r]);
-                    if (!(sc > tau_f)) {                       // rare: at or below the threshold, or NaN
-                        const u64 key = coarse_key(sc, (uint32_t)(row0 + r));
-                        if (qvalid && r < rows_here && key < tau) mylist[cnt++] = key;
+                    const int r = cbase + c + j;
+                    const float sc = score(__uint_as_float(v[j]), s.meta[mbuf][r]);
+                    if (!(sc > tau_f)) {                       // at or below the threshold, or NaN
+                        if (qvalid && r < rows_here) mylist[cnt++] = ((u64)__float_as_uint(sc) << 32) | (u64)(uint32_t)(row0 + r);
                     }
                 }
                 // a list within 32 of its capacity is cut back to k' (every chunk appends at most 32)
@@ -379,8 +425,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     u64 *lp = (u64 *)__shfl_sync(MCP_FULL, (u64)(uintptr_t)mylist, src);
                     const int n = __shfl_sync(MCP_FULL, cnt, src);
                     __syncwarp();
-                    const u64 thr = warp_prune_list<KPL>(lp, n, a.kprime, lane);
-                    if (lane == src) { cnt = a.kprime; tau = thr + 1ull; tau_f = ord_f32((uint32_t)(thr >> 32)); }
+                    const u64 thr = warp_prune_list<KPL>(lp, n, a.kprime, lane);   // ordered key of the worst survivor
+                    if (lane == src) { cnt = a.kprime; tau_f = ord_f32((uint32_t)(thr >> 32)); }
                     __syncwarp();
                 }
             }
@@ -411,6 +457,9 @@ struct GemmPlan {
     PFN_encodeTiled encode = nullptr;
     int coop = -1;             // device supports cooperative launch (-1 = not asked yet)
     bool allow_boot = true;    // option "gemm_bootstrap"
+    bool l2_prefetch = false;  // option "gemm_l2_prefetch"
+    int debug = 0;             // option "gemm_debug" (timing experiments, wrong results)
+    bool allow_wide = false;    // option "gemm_wide": 256-query CTAs when there are more than 128 queries
     char err[256] = {0};
 };
 
@@ -461,9 +510,11 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
         p.rows = rows; p.n_rows = n_rows; p.ld = ld; p.dim = dim; p.valid = true;
     }
     CUtensorMap tmA;
-    int rc = gemm_encode_2d(p, &tmA, queries, nq, dim, dim, G_BM);
+    int rc = gemm_encode_2d(p, &tmA, queries, nq, dim, dim, ((nq > G_BM && p.allow_wide) ? 2 : 1) * G_BM);
     if (rc) return rc;
-    const int nqb = (nq + G_BM - 1) / G_BM;
+    // wide tiles (two query blocks per CTA) whenever there are more than 128 queries
+    const int MTsel = (nq > G_BM && p.allow_wide) ? 2 : 1;
+    const int nqb = (nq + MTsel * G_BM - 1) / (MTsel * G_BM);
     const int n_tiles = (int)((n_rows + G_BN - 1) / G_BN);
     int ngroups = std::max(1, std::min(n_sm / nqb, n_tiles));
     const int kpl = gemm_kpl_for(kprime), cap = kpl * 32;
@@ -471,7 +522,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     const size_t list_bytes = sizeof(u64) * (size_t)nq * L * cap;
     const size_t cnt_off = (list_bytes + 255) & ~(size_t)255;
     const size_t pub_off = (cnt_off + sizeof(int) * (size_t)nq * L + 255) & ~(size_t)255;
-    const size_t arr_off = (pub_off + sizeof(u64) * (size_t)nq * L + 255) & ~(size_t)255;
+    const size_t arr_off = (pub_off + sizeof(u64) * (size_t)nq * 32 + 255) & ~(size_t)255;
     if ((rc = ws.ensure(arr_off + 256))) { snprintf(p.err, sizeof p.err, "workspace allocation failed"); return rc; }
     unsigned char *wsb = reinterpret_cast<unsigned char *>(ws.p);
     GemmArgs a;
@@ -482,34 +533,40 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     a.pub = reinterpret_cast<u64 *>(wsb + pub_off);
     a.arrive = reinterpret_cast<unsigned int *>(wsb + arr_off);
     a.dump = dump;
+    a.rows = rows; a.ld = ld; a.l2_prefetch = p.l2_prefetch ? 1 : 0; a.debug = p.debug;
     // bootstrap needs every CTA of a query block resident at once: cooperative launch, grid <= #SMs (1 CTA / SM)
-    const int m = (kprime + L - 1) / L;
+    int boot_lists = std::min(L, 32) & ~1;                       // even: both halves of a CTA
+    const int m = boot_lists ? (kprime + boot_lists - 1) / boot_lists : G_BOOT_MAX + 1;
     if (p.coop < 0) {
         int dev = 0, v = 0;
         cudaGetDevice(&dev);
         p.coop = (cudaDeviceGetAttribute(&v, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && v) ? 1 : 0;
     }
-    a.boot_m = (!dump && p.coop == 1 && m <= G_BOOT_MAX && nqb * ngroups <= n_sm && p.allow_boot) ? m : 0;
-    const size_t smem = sizeof(GemmSmem) + 1024;
+    a.boot_m = (!dump && !(p.debug & 1) && p.coop == 1 && m <= G_BOOT_MAX && nqb * ngroups <= n_sm && p.allow_boot) ? m : 0;
+    a.boot_lists = boot_lists;
+    const size_t smem = (MTsel == 2 ? sizeof(GemmSmemT<2>) : sizeof(GemmSmemT<1>)) + 1024;
+    const int threads = MTsel == 2 ? GemmCfg<2>::THREADS : GemmCfg<1>::THREADS;
     cudaError_t e = cudaSuccess;
     if (a.boot_m) e = cudaMemsetAsync(a.arrive, 0, sizeof(unsigned int) * G_MAX_QBLOCKS, st);
     void *kargs[3] = {(void *)&tmA, (void *)&p.tmB, (void *)&a};
-#define G_LAUNCH(KPL, MET)                                                                                      \
+#define G_LAUNCH(MTV, KPL, MET)                                                                                 \
     do {                                                                                                        \
         if (e == cudaSuccess)                                                                                   \
-            e = cudaFuncSetAttribute(gemm_tf32_kernel<KPL, MET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+            e = cudaFuncSetAttribute(gemm_tf32_kernel<MTV, KPL, MET>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e == cudaSuccess) {                                                                                 \
             if (a.boot_m)                                                                                       \
-                e = cudaLaunchCooperativeKernel((const void *)gemm_tf32_kernel<KPL, MET>, dim3(nqb * ngroups),  \
-                                                dim3(G_THREADS), kargs, smem, st);                              \
+                e = cudaLaunchCooperativeKernel((const void *)gemm_tf32_kernel<MTV, KPL, MET>, dim3(nqb * ngroups), \
+                                                dim3(threads), kargs, smem, st);                                \
             else {                                                                                              \
-                gemm_tf32_kernel<KPL, MET><<<nqb * ngroups, G_THREADS, smem, st>>>(tmA, p.tmB, a);              \
+                gemm_tf32_kernel<MTV, KPL, MET><<<nqb * ngroups, threads, smem, st>>>(tmA, p.tmB, a);           \
                 e = cudaGetLastError();                                                                         \
             }                                                                                                   \
         }                                                                                                       \
     } while (0)
-    if (metric == 0) { if (kpl == 4) G_LAUNCH(4, 0); else if (kpl == 8) G_LAUNCH(8, 0); else G_LAUNCH(16, 0); }
-    else             { if (kpl == 4) G_LAUNCH(4, 1); else if (kpl == 8) G_LAUNCH(8, 1); else G_LAUNCH(16, 1); }
+#define G_LAUNCH_K(MTV, MET) do { if (kpl == 4) G_LAUNCH(MTV, 4, MET); else if (kpl == 8) G_LAUNCH(MTV, 8, MET); else G_LAUNCH(MTV, 16, MET); } while (0)
+    if (MTsel == 2) { if (metric == 0) G_LAUNCH_K(2, 0); else G_LAUNCH_K(2, 1); }
+    else            { if (metric == 0) G_LAUNCH_K(1, 0); else G_LAUNCH_K(1, 1); }
+#undef G_LAUNCH_K
 #undef G_LAUNCH
     if (e != cudaSuccess) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch: %s", cudaGetErrorString(e)); return -2; }
     *out_lists = a.lists; *out_cnt = a.list_cnt; *out_L = L; *out_cap = cap;

@@ -281,6 +281,12 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
     } else if (!strcmp(name, "max_fallback")) {
         if (value < 1 || value > 64) return fail(MCP_EINVAL, "max_fallback %lld outside [1, 64]", (long long)value);
         idx->opt_max_fallback = (int)value;
+    } else if (!strcmp(name, "gemm_debug")) {
+        idx->gemm.debug = (int)value;
+    } else if (!strcmp(name, "gemm_l2_prefetch")) {
+        idx->gemm.l2_prefetch = value != 0;
+    } else if (!strcmp(name, "gemm_wide")) {
+        idx->gemm.allow_wide = value != 0;
     } else if (!strcmp(name, "gemm_bootstrap")) {
         idx->gemm.allow_boot = value != 0;
     } else if (!strcmp(name, "time_coarse")) {
@@ -395,11 +401,11 @@ static int run_scan_pass(mcp_index *idx, cudaStream_t st, const float *q, int di
 
 // reduce [nq][L][cap] lists until one list per query is left; returns the final buffers
 static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64 *in, int *in_cnt, int L, int cap,
-                        bool in_is_A, u64 **out_keys, int **out_cnt, int *out_stride) {
+                        bool in_is_A, u64 **out_keys, int **out_cnt, int *out_stride, bool raw_in = false) {
     int rc;
     bool first = true;
     while (L > 1 || first) {
-        if (L == 1 && cap <= kprime) break;       // already one list of at most k' keys
+        if (L == 1 && cap <= kprime && !raw_in) break;   // already one list of at most k' ordered keys
         first = false;
         int G = std::max(1, std::min(SEL_MAX / cap, SEL_THREADS));
         int L_out = (L + G - 1) / G;
@@ -408,9 +414,9 @@ static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64
         if ((rc = ob.ensure(sizeof(u64) * (size_t)nq * L_out * kprime))) return rc;
         if ((rc = oc.ensure(sizeof(int) * (size_t)nq * L_out))) return rc;
         select_from_lists_kernel<<<dim3(L_out, nq), SEL_THREADS, 0, st>>>(in, in_cnt, L, cap, G, kprime, ob.as<u64>(),
-                                                                          oc.as<int>(), kprime);
+                                                                          oc.as<int>(), kprime, raw_in ? 1 : 0);
         KL();
-        in = ob.as<u64>(); in_cnt = oc.as<int>(); L = L_out; cap = kprime; in_is_A = !in_is_A;
+        in = ob.as<u64>(); in_cnt = oc.as<int>(); L = L_out; cap = kprime; in_is_A = !in_is_A; raw_in = false;
     }
     *out_keys = in; *out_cnt = in_cnt; *out_stride = cap;
     return MCP_OK;
@@ -541,8 +547,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             idx->stats.kernel_launches++;
             if ((rc = coarse_event(idx, st))) return rc;
             // the GEMM's lists live in gemm_ws; reductions ping-pong between listsA / listsB
-            if (L == 1 && cap <= kprime) { cand = lists; cand_cnt = cnts; cand_stride = cap; }
-            else if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride)))
+            // K2 lists are raw (fp32 bits, row) pairs: always pass them through one reduction, which builds the ordered keys
+            if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride, true)))
                 return rc;
         }
         rescore_kernel<<<dim3((cand_stride + RS_ROWS - 1) / RS_ROWS, cq), RESCORE_THREADS,

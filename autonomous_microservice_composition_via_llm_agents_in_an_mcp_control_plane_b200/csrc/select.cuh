@@ -105,7 +105,7 @@ select_from_scores_kernel(const float *__restrict__ scores, int64_t score_stride
 __global__ void __launch_bounds__(SEL_THREADS)
 select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_cnt, int L_in,
                          int cap_in, int G, int kprime, u64 *__restrict__ out,
-                         int *__restrict__ out_cnt, int cap_out) {
+                         int *__restrict__ out_cnt, int cap_out, int raw_in) {
     __shared__ SelectSmem s;
     __shared__ int base[SEL_THREADS + 1];      // exclusive prefix of the list lengths
     __shared__ int wsum[SEL_THREADS / 32];
@@ -140,7 +140,13 @@ select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_
     for (int l = l0 + warp; l < l1; l += SEL_THREADS / 32) {      // one warp per list
         const int b = base[l - lb] - off, c = base[l - lb + 1] - base[l - lb];
         const u64 *src = in + ((int64_t)q * L_in + l) * cap_in;
-        for (int i = lane; i < c; i += 32) s.keys[b + i] = src[i];
+        if (raw_in)   // K2 appends raw (fp32 bits, row) pairs: build the ordered key here
+            for (int i = lane; i < c; i += 32) {
+                const u64 raw = src[i];
+                s.keys[b + i] = ((u64)f32_ord(__uint_as_float((uint32_t)(raw >> 32))) << 32) | (raw & 0xFFFFFFFFull);
+            }
+        else
+            for (int i = lane; i < c; i += 32) s.keys[b + i] = src[i];
     }
     __syncthreads();
     const int64_t lo = (int64_t)q * L_out + g;

@@ -229,6 +229,7 @@ def main():
     ap.add_argument("--queries", type=int, default=0)
     ap.add_argument("--topk", type=int, default=0)
     ap.add_argument("--path", default="auto", choices=["auto", "stream_fp32", "gemm_tf32"])
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value (repeatable), e.g. gemm_wide=0")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--dag", type=int, default=0, help="also time the Kahn-level kernel on this many synthetic DAGs (extra)")
@@ -267,6 +268,9 @@ def main():
     sh.adopt_shard(rows, n).set_penalty(pen)
     if args.path != "auto":
         sh.local.set_option("path", args.path)
+    for o in args.opt:
+        name, val = o.split("=")
+        sh.local.set_option(name, int(val))
     sh.local.set_option("time_coarse", 1)
 
     def barrier():
