@@ -407,7 +407,7 @@ static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64
     while (L > 1 || first) {
         if (L == 1 && cap <= kprime && !raw_in) break;   // already one list of at most k' ordered keys
         first = false;
-        int G = std::max(1, std::min(SEL_MAX / cap, SEL_THREADS));
+        int G = std::min(L, SEL_THREADS);          // one CTA per query unless there are more than SEL_THREADS lists
         int L_out = (L + G - 1) / G;
         Buf &ob = in_is_A ? idx->listsB : idx->listsA;
         Buf &oc = in_is_A ? idx->cntB : idx->cntA;
@@ -436,7 +436,7 @@ static int choose_path(const mcp_index *idx, int nq) {
 
 // fp64 scan + exact select for flagged slots [slot0, slot0 + slots)
 static int run_exact(mcp_index *idx, cudaStream_t st, const float *d_q, const double *nq2, int k, int slots,
-                     int32_t *out_ids, float *out_scores, double *out_scores64) {
+                     int32_t *out_ids, float *out_scores, double *out_scores64, bool fold_status) {
     int rc;
     if ((rc = idx->exact_all.ensure(sizeof(u64) * (size_t)slots * (size_t)idx->n_rows))) return rc;
     int *flag_list = idx->flags.as<int>() + 8, *n_flag = idx->flags.as<int>();
@@ -448,7 +448,8 @@ static int run_exact(mcp_index *idx, cudaStream_t st, const float *d_q, const do
         idx->metric, flag_list, n_flag, 0, idx->exact_all.as<u64>());
     KL();
     exact_select_kernel<<<slots, EXSEL_THREADS, 0, st>>>(idx->exact_all.as<u64>(), idx->n_rows, k, idx->id_base,
-                                                         flag_list, n_flag, 0, out_ids, out_scores, out_scores64);
+                                                         flag_list, n_flag, 0, out_ids, out_scores, out_scores64,
+                                                         fold_status ? n_flag + 1 : nullptr);
     KL();
     return MCP_OK;
 }
@@ -481,7 +482,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             int c = std::min(slots, nq - q0);
             flag_all_kernel<<<(c + 127) / 128, 128, 0, st>>>(flag_list, n_flag, q0, c);
             KL();
-            if ((rc = run_exact(idx, st, d_q, idx->nq2.as<double>(), k, c, out_ids, out_scores, out_scores64))) return rc;
+            if ((rc = run_exact(idx, st, d_q, idx->nq2.as<double>(), k, c, out_ids, out_scores, out_scores64, false))) return rc;
         }
         clear_flag_kernel<<<1, 1, 0, st>>>(n_flag);
         KL();
@@ -564,10 +565,9 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
         KL();
         // certificate failures: fp64 scan on the device, flag_list holds chunk-local query numbers
         if ((rc = run_exact(idx, st, dq, idx->nq2.as<double>() + q0, k, idx->opt_max_fallback, out_ids + (int64_t)q0 * k, out_scores + (int64_t)q0 * k,
-                            out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr)))
+                            out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, true)))
             return rc;
-        status_accumulate_kernel<<<1, 1, 0, st>>>(n_flag, status, idx->opt_max_fallback);
-        KL();
+        (void)status;   // [1] failures, [2] unresolved, [3] ticket: folded by exact_select_kernel's last CTA
         idx->stats.rows_scanned += n;
         idx->stats.bytes_scanned += n * (int64_t)dim * 4;
         idx->stats.candidates_rescored += (int64_t)cq * kc;
@@ -883,7 +883,7 @@ extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float
                                                                        n_flag, 0, scores);   // writes scores[0 .. n_rows)
         KCHECK();
         exact_select_kernel<<<1, EXSEL_THREADS, 0, st>>>(scores, idx->n_rows, k, idx->id_base, flag_list, n_flag, 0,
-                                                          out_ids_device, out_scores_device, out_scores64_device);
+                                                          out_ids_device, out_scores_device, out_scores64_device, nullptr);
         KCHECK();
     }
     return MCP_OK;

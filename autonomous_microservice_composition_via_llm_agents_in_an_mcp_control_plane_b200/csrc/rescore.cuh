@@ -29,8 +29,9 @@ struct CertParams {
 
 // ---- K4a: exact rescoring ------------------------------------------------------------------------
 // One CTA = one query x 32 candidates.  The fp64 chain of a candidate (dim dependent FMAs, index order) is
-// the latency floor, and on B200 the fp32 -> fp64 conversion (F2F, ~12 cycles per warp instruction, measured
-// with tools/fp64_latency.cu) costs more than the FMA itself.  So: the query is converted to fp64 once per CTA
+// the latency floor.  On B200 the fp64 pipe is narrow (tools/fp64_latency.cu, tools/chain_bench.cu: a dependent DFMA
+// every ~8-16 cycles, F2F.F64.F32 ~12 cycles per warp instruction, both on the same pipe, ~0.4 warp instructions per
+// clock per SM), so the chain carries as little as possible: the query is converted to fp64 once per CTA
 // by all threads and kept in shared memory; all 128 threads stream the 32 candidate rows through a 3-stage
 // cp.async ring (64 floats per row per stage, 256 contiguous bytes per row); the 32 lanes of warp 0 each walk
 // their own row out of shared memory, converting only the row element.  grid (ceil(stride / 32), Q).
@@ -60,7 +61,15 @@ rescore_kernel(const float *__restrict__ rows, int dim, int64_t ld,
     const int cnt = min(cand_cnt[q], cand_stride);
     if (j0 >= cand_stride) return;
     const float *qv = queries + (int64_t)q * dim;
-    for (int i = threadIdx.x; i < dimp; i += blockDim.x) sq[i] = i < dim ? (double)qv[i] : 0.0;
+    {   // query -> fp64 in shared memory; the loads of a thread are issued together, not one per loop trip
+        float t[8];
+        for (int i0 = 0; i0 < dimp; i0 += 8 * RESCORE_THREADS) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { const int i = i0 + u * RESCORE_THREADS + threadIdx.x; t[u] = i < dim ? __ldg(qv + i) : 0.f; }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { const int i = i0 + u * RESCORE_THREADS + threadIdx.x; if (i < dimp) sq[i] = (double)(t[u]); }
+        }
+    }
     if (threadIdx.x < RS_ROWS) {
         int j = j0 + threadIdx.x;
         s_row[threadIdx.x] = (j < cnt) ? (int)(cand[(int64_t)q * cand_stride + j] & 0xFFFFFFFFull) : -1;
@@ -82,21 +91,25 @@ rescore_kernel(const float *__restrict__ rows, int dim, int64_t ld,
     };
     for (int c = 0; c < RS_STAGES - 1; ++c) issue(c);
     double acc = 0.0;
+    // The chain warp differs from CTA to CTA: warp w sits on scheduler w % 4, and the F2F pipe of one scheduler
+    // cannot feed the chains of every CTA resident on the SM.
+    const int cw = (blockIdx.x + blockIdx.y) & 3, cl = threadIdx.x & 31;
+    const bool chain = (threadIdx.x >> 5) == cw;
     for (int c = 0; c < nchunks; ++c) {
         cp_async_wait<RS_STAGES - 2>();
         __syncthreads();                                   // chunk c has landed; everyone is done with chunk c-1's stage
         issue(c + RS_STAGES - 1);
-        if (threadIdx.x < RS_ROWS) {
+        if (chain) {
             const int c0 = c * RS_COLS, w = min(RS_COLS, dimp - c0);
-            const float *e = tile + (size_t)(c % RS_STAGES) * RS_ROWS * RS_PITCH + threadIdx.x * RS_PITCH;
+            const float *e = tile + (size_t)(c % RS_STAGES) * RS_ROWS * RS_PITCH + cl * RS_PITCH;
             const double *qq = sq + c0;
             if (metric == 0) {
 #pragma unroll 4
                 for (int i = 0; i < w; i += 4) {
                     const float4 v = *reinterpret_cast<const float4 *>(e + i);
                     const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
-                    acc = fma(u0.x, (double)v.x, acc); acc = fma(u0.y, (double)v.y, acc);
-                    acc = fma(u1.x, (double)v.z, acc); acc = fma(u1.y, (double)v.w, acc);
+                    acc = fma(u0.x, (double)(v.x), acc); acc = fma(u0.y, (double)(v.y), acc);
+                    acc = fma(u1.x, (double)(v.z), acc); acc = fma(u1.y, (double)(v.w), acc);
                 }
             } else {
 #pragma unroll 4
@@ -104,17 +117,17 @@ rescore_kernel(const float *__restrict__ rows, int dim, int64_t ld,
                     const float4 v = *reinterpret_cast<const float4 *>(e + i);
                     const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
                     double d;
-                    d = __dsub_rn(u0.x, (double)v.x); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                    d = __dsub_rn(u0.y, (double)v.y); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                    d = __dsub_rn(u1.x, (double)v.z); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                    d = __dsub_rn(u1.y, (double)v.w); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                    d = __dsub_rn(u0.x, (double)(v.x)); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                    d = __dsub_rn(u0.y, (double)(v.y)); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                    d = __dsub_rn(u1.x, (double)(v.z)); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                    d = __dsub_rn(u1.y, (double)(v.w)); acc = __dadd_rn(acc, __dmul_rn(d, d));
                 }
             }
         }
     }
-    if (threadIdx.x < RS_ROWS && j0 + threadIdx.x < cand_stride) {
-        const int64_t o = (int64_t)q * cand_stride + j0 + threadIdx.x;
-        const int row = s_row[threadIdx.x];
+    if (chain && j0 + cl < cand_stride) {
+        const int64_t o = (int64_t)q * cand_stride + j0 + cl;
+        const int row = s_row[cl];
         if (row < 0) { exact_key[o] = ~0ull; exact_row[o] = MCP_PAD_ROW; }
         else {
             double s = exact_finish(acc, metric, nq2[q], ne2[row]);
@@ -234,16 +247,28 @@ exact_scan_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64
 // are taken in row order, which is the "ties -> lowest id" rule.
 __global__ void __launch_bounds__(EXSEL_THREADS)
 exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, int64_t id_base,
-                    const int *__restrict__ flag_list, const int *__restrict__ n_flag, int slot0,
+                    const int *__restrict__ flag_list, int *__restrict__ n_flag, int slot0,
                     int32_t *__restrict__ out_ids, float *__restrict__ out_scores,
-                    double *__restrict__ out_scores64) {
+                    double *__restrict__ out_scores64, int *__restrict__ status /* NULL, or [failures, unresolved, ticket] */) {
     __shared__ uint32_t hist[256];
     __shared__ int s_digit, s_cnt, s_warp_base[EXSEL_THREADS / 32 + 1], s_taken, s_nless;
     __shared__ long long s_need;
     __shared__ u64 sk[MCP_MAX_K_POW2];
     __shared__ int sv[MCP_MAX_K_POW2];
     int f = blockIdx.x;
-    if (slot0 + f >= *n_flag) return;
+    const int nf = *n_flag;
+    // the last CTA to get here folds this batch's flag count into the running status and clears it for the next batch
+    // (every CTA has read n_flag by then: the ticket is taken after the read)
+    if (status && threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&status[2], 1) == (int)gridDim.x - 1) {
+            status[0] += nf;
+            status[1] += nf > (int)gridDim.x ? nf - (int)gridDim.x : 0;
+            status[2] = 0;
+            *n_flag = 0;
+        }
+    }
+    if (slot0 + f >= nf) return;
     int q = flag_list[slot0 + f];
     const u64 *E = exact_all + (int64_t)f * n_rows;
     int kk = (int)min((int64_t)k, n_rows);

@@ -13,30 +13,54 @@
 #define SEL_THREADS 512
 #define SEL_MAX 4096   // keys one CTA selects from (32 KB of shared memory)
 
+#define SEL_HISTS 8    // private histograms (warp w uses copy w % 8): early digits are nearly constant, one copy would serialise
 struct SelectSmem {
     u64 keys[SEL_MAX];
-    uint32_t hist[256];
+    uint32_t hist[SEL_HISTS][256];
+    u64 kmin, kmax;
     int digit, need, cnt, out_count;
 };
 
 // Returns the largest key that belongs to the kk smallest of keys[0..n).  Block-uniform.
 __device__ inline u64 cta_radix_threshold(SelectSmem &s, int n, int kk) {
     if (kk >= n) return ~0ull;
-    u64 prefix = 0, mask = 0;
+    // bytes on which every key agrees need no pass: find them from the block-wide min and max
+    u64 mn = ~0ull, mx = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { const u64 key = s.keys[i]; mn = key < mn ? key : mn; mx = key > mx ? key : mx; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const u64 a = __shfl_xor_sync(MCP_FULL, mn, o), b = __shfl_xor_sync(MCP_FULL, mx, o);
+        mn = a < mn ? a : mn; mx = b > mx ? b : mx;
+    }
+    if (threadIdx.x == 0) { s.kmin = ~0ull; s.kmax = 0; }
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) { atomicMin(&s.kmin, mn); atomicMax(&s.kmax, mx); }
+    __syncthreads();
+    const u64 diff = s.kmin ^ s.kmax;
+    int shift0 = 56;
+    while (shift0 > 0 && (diff >> shift0) == 0) shift0 -= 8;
+    u64 prefix = shift0 == 56 ? 0ull : (s.kmin >> (shift0 + 8)) << (shift0 + 8);
+    u64 mask = shift0 == 56 ? 0ull : ~0ull << (shift0 + 8);
     int need = kk;
-    for (int shift = 56; shift >= 0; shift -= 8) {
-        for (int i = threadIdx.x; i < 256; i += blockDim.x) s.hist[i] = 0;
+    uint32_t *myhist = s.hist[(threadIdx.x >> 5) % SEL_HISTS];
+    for (int shift = shift0; shift >= 0; shift -= 8) {
+        for (int i = threadIdx.x; i < SEL_HISTS * 256; i += blockDim.x) (&s.hist[0][0])[i] = 0;
         __syncthreads();
         for (int i = threadIdx.x; i < n; i += blockDim.x) {
             u64 key = s.keys[i];
-            if ((key & mask) == prefix) atomicAdd(&s.hist[(uint32_t)(key >> shift) & 255u], 1u);
+            if ((key & mask) == prefix) atomicAdd(&myhist[(uint32_t)(key >> shift) & 255u], 1u);
         }
         __syncthreads();
         if (threadIdx.x < 32) {
             int lane = threadIdx.x;
             uint32_t c[8], sum = 0;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { c[j] = s.hist[lane * 8 + j]; sum += c[j]; }
+            for (int j = 0; j < 8; ++j) {
+                uint32_t t = 0;
+#pragma unroll
+                for (int h = 0; h < SEL_HISTS; ++h) t += s.hist[h][lane * 8 + j];
+                c[j] = t; sum += t;
+            }
             uint32_t incl = sum;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -98,10 +122,11 @@ select_from_scores_kernel(const float *__restrict__ scores, int64_t score_stride
     cta_select_write(s, n, min(kprime, n), lists + l * cap, list_cnt + l);
 }
 
-// Stage B: lists[q][L_in][cap_in] -> lists[q][L_out][cap_out]; group g reduces G consecutive
-// input lists (G * cap_in <= SEL_MAX, G <= SEL_THREADS).  grid (L_out, Q).
-// Lists are usually far from full: when all of a query's lists together fit one CTA, group 0 takes them all and
-// the other groups hand back empty lists (the launch shape stays static, the work does not).
+// Stage B: lists[q][L_in][cap_in] -> lists[q][L_out][cap_out]; CTA g reduces the G consecutive input lists
+// [g*G, g*G+G) (G <= SEL_THREADS) to their kprime smallest keys.  grid (L_out, Q).
+// Lists are usually far from full, so one CTA normally takes all of a query's lists at once; when their keys do
+// not fit the SEL_MAX-key buffer they are consumed in chunks, the best kprime so far riding along.
+// raw_in: the lists hold raw (fp32 score bits, row) pairs as the GEMM epilogue appends them.
 __global__ void __launch_bounds__(SEL_THREADS)
 select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_cnt, int L_in,
                          int cap_in, int G, int kprime, u64 *__restrict__ out,
@@ -109,14 +134,11 @@ select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_
     __shared__ SelectSmem s;
     __shared__ int base[SEL_THREADS + 1];      // exclusive prefix of the list lengths
     __shared__ int wsum[SEL_THREADS / 32];
+    __shared__ int s_lend;
     const int g = blockIdx.x, q = blockIdx.y, L_out = gridDim.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    // list lengths, one per thread, and their block-wide exclusive scan: all lists of the query when there are
-    // at most SEL_THREADS of them (lets group 0 take everything), else just this group's
-    int l0 = g * G, l1 = min(l0 + G, L_in);
-    const bool whole = L_in <= SEL_THREADS;
-    const int lb = whole ? 0 : l0, nl = whole ? L_in : l1 - l0;
-    const int mycnt = (int)threadIdx.x < nl ? min(in_cnt[(int64_t)q * L_in + lb + threadIdx.x], cap_in) : 0;
+    const int l0 = g * G, nl = min(G, L_in - l0);
+    const int mycnt = (int)threadIdx.x < nl ? min(in_cnt[(int64_t)q * L_in + l0 + threadIdx.x], cap_in) : 0;
     int incl = mycnt;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(MCP_FULL, incl, o); if (lane >= o) incl += t; }
@@ -129,26 +151,60 @@ select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_
         if (lane < SEL_THREADS / 32) wsum[lane] = wi - w;
     }
     __syncthreads();
-    base[threadIdx.x] = wsum[warp] + incl - mycnt;             // base[i] = keys before list lb + i
+    base[threadIdx.x] = wsum[warp] + incl - mycnt;             // base[i] = keys before list l0 + i
     if (threadIdx.x == SEL_THREADS - 1) base[SEL_THREADS] = wsum[warp] + incl;
     __syncthreads();
-    if (whole && base[SEL_THREADS] <= SEL_MAX) {
-        if (g != 0) { if (threadIdx.x == 0) out_cnt[(int64_t)q * L_out + g] = 0; return; }
-        l0 = 0; l1 = L_in;
-    }
-    const int off = base[l0 - lb], n = base[l1 - lb] - off;
-    for (int l = l0 + warp; l < l1; l += SEL_THREADS / 32) {      // one warp per list
-        const int b = base[l - lb] - off, c = base[l - lb + 1] - base[l - lb];
-        const u64 *src = in + ((int64_t)q * L_in + l) * cap_in;
-        if (raw_in)   // K2 appends raw (fp32 bits, row) pairs: build the ordered key here
-            for (int i = lane; i < c; i += 32) {
-                const u64 raw = src[i];
-                s.keys[b + i] = ((u64)f32_ord(__uint_as_float((uint32_t)(raw >> 32))) << 32) | (raw & 0xFFFFFFFFull);
-            }
-        else
-            for (int i = lane; i < c; i += 32) s.keys[b + i] = src[i];
-    }
-    __syncthreads();
+    const u64 *lists = in + ((int64_t)q * L_in + l0) * cap_in;
     const int64_t lo = (int64_t)q * L_out + g;
-    cta_select_write(s, n, min(kprime, n), out + lo * cap_out, out_cnt + lo);
+    u64 *dst = out + lo * cap_out;
+    int carry = 0, ls = 0;
+    for (;;) {
+        // lists [ls, le) are the longest run whose keys fit behind the carried ones (normally: all of them)
+        if (threadIdx.x == 0) {
+            int le = nl;
+            if (carry + base[nl] - base[ls] > SEL_MAX) {       // base[] is monotone: binary search for the last list that fits
+                int a = ls + 1, b = nl;                        // invariant: list run [ls, a) fits, [ls, b) does not
+                while (b - a > 1) { const int mid = (a + b) >> 1; if (carry + base[mid] - base[ls] <= SEL_MAX) a = mid; else b = mid; }
+                le = a;
+            }
+            s_lend = le;
+        }
+        __syncthreads();
+        const int le = s_lend, b0 = base[ls], m = base[le] - b0;
+        // flat gather, at most SEL_MAX / SEL_THREADS = 8 keys per thread: first every thread finds where its keys
+        // live (binary search over the prefix sums, shared memory only), then all its global loads go out together
+        {
+            const u64 *src[SEL_MAX / SEL_THREADS];
+#pragma unroll
+            for (int u = 0; u < SEL_MAX / SEL_THREADS; ++u) {
+                const int i = threadIdx.x + u * SEL_THREADS;
+                src[u] = nullptr;
+                if (i < m) {
+                    const int e = b0 + i;
+                    int a = ls, b = le;                        // list l with base[l] <= e < base[l+1]
+                    while (b - a > 1) { const int mid = (a + b) >> 1; if (base[mid] <= e) a = mid; else b = mid; }
+                    src[u] = lists + (int64_t)a * cap_in + (e - base[a]);
+                }
+            }
+            u64 x[SEL_MAX / SEL_THREADS];
+#pragma unroll
+            for (int u = 0; u < SEL_MAX / SEL_THREADS; ++u) x[u] = src[u] ? __ldg(src[u]) : 0ull;
+#pragma unroll
+            for (int u = 0; u < SEL_MAX / SEL_THREADS; ++u)
+                if (src[u]) {
+                    const u64 v = x[u];
+                    s.keys[carry + threadIdx.x + u * SEL_THREADS] =
+                        raw_in ? (((u64)f32_ord(__uint_as_float((uint32_t)(v >> 32))) << 32) | (v & 0xFFFFFFFFull)) : v;
+                }
+        }
+        __syncthreads();
+        const int n = carry + m;
+        cta_select_write(s, n, min(kprime, n), dst, out_cnt + lo);
+        if (le >= nl) break;
+        __syncthreads();
+        carry = min(kprime, n);
+        for (int i = threadIdx.x; i < carry; i += SEL_THREADS) s.keys[i] = dst[i];   // written by this CTA just above
+        ls = le;
+        __syncthreads();
+    }
 }
