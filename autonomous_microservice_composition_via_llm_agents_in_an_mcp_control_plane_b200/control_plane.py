@@ -67,6 +67,16 @@ class ServiceRegistry:
     def list_services(self) -> List[dict]:
         return [json.loads(self.redis.get(key)) for key in self.redis.scan_iter(f"{SERVICES_PREFIX}*")]
 
+    def get_services(self, names: Sequence[str]) -> List[dict]:
+        """The k candidates' records only: k GETs instead of SCAN + one GET per registered service (the
+        reference's :33-34 is O(N) round trips per request, unworkable at 1M services).  Unknown names are skipped."""
+        out = []
+        for n in names:
+            raw = self.redis.get(f"{SERVICES_PREFIX}{n}")
+            if raw:
+                out.append(json.loads(raw))
+        return out
+
 
 # ---- wire models (control_plane.py:39-43, :79-85) -----------------------------------------------
 class PlanRequest(BaseModel):
@@ -103,6 +113,66 @@ def _openai_chat(prompt: str) -> str:
     return resp.choices[0].message.content
 
 
+class MicroBatcher:
+    """Coalesces concurrent single-query searches into one kernel launch.
+
+    ``/plan`` runs on worker threads and ``/plan_and_execute`` on its own (control_plane.py:140-151), so several
+    requests are usually in flight at once, yet each carries one intent; one scan of the table answers a whole batch
+    in barely more time than a single query (the scan is memory-bound).  Callers block in ``search``; one worker
+    thread drains whatever has queued up while the previous launch was running -- no timer, so a lone request pays
+    no extra latency, and the batch size adapts to the load by itself.
+    """
+
+    def __init__(self, search_fn: Callable[[np.ndarray, int], tuple], max_batch: int = 1024):
+        self._search, self._max = search_fn, max_batch
+        self._cv = threading.Condition()
+        self._pending: List[tuple] = []
+        self._closed = False
+        self.launches = self.requests = 0
+        self._worker = threading.Thread(target=self._run, name="mcp-microbatch", daemon=True)
+        self._worker.start()
+
+    def search(self, query: np.ndarray, k: int):
+        """One query vector -> (ids [k], scores [k]); blocks until its batch has been answered."""
+        slot = {"q": np.asarray(query, np.float32), "k": int(k), "done": threading.Event(), "out": None, "err": None}
+        with self._cv:
+            if self._closed:
+                raise RuntimeError("MicroBatcher is closed")
+            self._pending.append(slot)
+            self._cv.notify()
+        slot["done"].wait()
+        if slot["err"] is not None:
+            raise slot["err"]
+        return slot["out"]
+
+    def _run(self):
+        while True:
+            with self._cv:
+                while not self._pending and not self._closed:
+                    self._cv.wait()
+                if self._closed and not self._pending:
+                    return
+                batch, self._pending = self._pending[:self._max], self._pending[self._max:]
+            try:
+                kmax = max(s["k"] for s in batch)
+                ids, scores, _ = self._search(np.stack([s["q"] for s in batch]), kmax)
+                for i, s in enumerate(batch):
+                    s["out"] = (ids[i, :s["k"]], scores[i, :s["k"]])     # a prefix of an exact top-kmax is the exact top-k
+            except Exception as e:  # noqa: BLE001 -- handed to every waiting caller
+                for s in batch:
+                    s["err"] = e
+            self.launches += 1
+            self.requests += len(batch)
+            for s in batch:
+                s["done"].set()
+
+    def close(self):
+        with self._cv:
+            self._closed = True
+            self._cv.notify()
+        self._worker.join(timeout=5)
+
+
 class GraphPlanner:
     """Same constructor and ``plan`` signature as the reference; three optional injection points.
 
@@ -116,7 +186,7 @@ class GraphPlanner:
                  embed: Optional[Callable[[str], np.ndarray]] = None,
                  llm: Optional[Callable[[str], str]] = None,
                  top_k: int = RETRIEVAL_TOP_K, metric: str = RETRIEVAL_METRIC, device: int = CUDA_DEVICE,
-                 telemetry_client=None):
+                 telemetry_client=None, micro_batch: bool = False):
         self.registry = registry
         self.pg_dsn = pg_dsn
         self.conn = None                       # opened lazily; the reference connects in __init__ (:48)
@@ -128,6 +198,8 @@ class GraphPlanner:
         self._index: Optional[ServiceIndex] = None
         self._names: List[str] = []
         self._lock = threading.Lock()
+        self._batcher: Optional[MicroBatcher] = None
+        self._micro_batch = micro_batch
 
     # the reference's only read of the embedding table
     def _fetch_embeddings_metadata(self):
@@ -163,9 +235,23 @@ class GraphPlanner:
             self._index.set_penalty(_telemetry.penalty_for_services(recs, self._telemetry_client))
         return self._index
 
+    def attach_index(self, index: ServiceIndex, names: Sequence[str]) -> None:
+        """Use an index that is already resident (e.g. adopted from device memory) instead of fetching the table."""
+        with self._lock:
+            self._index, self._names = index, list(names)
+
     def retrieve(self, intent: str, k: Optional[int] = None) -> List[tuple]:
-        """Top-k (service name, score) for one intent."""
-        return self.retrieve_batch([intent], k)[0]
+        """Top-k (service name, score) for one intent.  With ``micro_batch=True`` concurrent callers share launches."""
+        if not self._micro_batch:
+            return self.retrieve_batch([intent], k)[0]
+        if self._index is None:
+            self.refresh_index()
+        k = min(k or self.top_k, max(1, len(self._names)))
+        with self._lock:
+            if self._batcher is None:
+                self._batcher = MicroBatcher(lambda q, kk: self._index.search(q, kk))
+        ids, scores = self._batcher.search(self._embed(intent), k)
+        return [(self._names[i], float(s)) for i, s in zip(ids, scores) if i >= 0]
 
     def retrieve_batch(self, intents: Sequence[str], k: Optional[int] = None) -> List[List[tuple]]:
         if self._index is None:
@@ -178,11 +264,14 @@ class GraphPlanner:
 
     # ---- plan (same contract as control_plane.py:57-75) -----------------------------------
     def plan(self, intent: str) -> PlanResponse:
-        services = self.registry.list_services()
         if self._index is None:
-            self.refresh_index(services)
-        by_name = {s["name"]: s for s in services}
-        candidates = [by_name[n] for n, _ in self.retrieve(intent) if n in by_name]
+            self.refresh_index(self.registry.list_services())     # first request only: the reference scans every time (:58)
+        names = [n for n, _ in self.retrieve(intent)]
+        if hasattr(self.registry, "get_services"):
+            candidates = self.registry.get_services(names)        # k GETs
+        else:                                                     # a registry that only offers the reference's method
+            by_name = {s["name"]: s for s in self.registry.list_services()}
+            candidates = [by_name[n] for n in names if n in by_name]
         lines = ["You are an orchestration agent.  Given the user intent and available services,",
                  "output a JSON DAG specifying for each step: service_name, input_keys, next_steps, fallback.",
                  "", "Available services:"]

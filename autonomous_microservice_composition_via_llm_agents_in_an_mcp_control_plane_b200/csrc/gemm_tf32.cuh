@@ -46,7 +46,7 @@ struct GemmArgs {
     int64_t n_rows;
     int dim, nq, nqb, kprime, cap;
     const float *inv_nq;       // [nq]
-    const double *nq2;         // [nq]
+    const float *nq2f;         // [nq] fp32 squared norms (L2 metric)
     const float *inv_ne;       // [n_rows]
     const double *ne2;         // [n_rows]
     const float *penalty;      // [n_rows] or NULL
@@ -305,7 +305,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int qg = (qb * MT + mt) * G_BM + m;
         const bool qvalid = qg < a.nq;
         const float inq = qvalid ? a.inv_nq[qg] : 0.f;
-        const float nq2f = qvalid ? (float)a.nq2[qg] : 0.f;
+        const float nq2f = qvalid ? a.nq2f[qg] : 0.f;
         const int et = threadIdx.x - 64;                       // 0 .. EPI_THREADS-1
         const int L = 2 * ngroups, li = 2 * group + half;      // one list per (CTA, query, half)
         u64 *mylist = a.lists + ((int64_t)(qvalid ? qg : 0) * L + li) * CAP;
@@ -498,7 +498,7 @@ static inline int gemm_max_kprime() { return 256; }
 // Returns 0, or a negative MCP_E* code with the message in plan.err.
 template <class BufT>
 static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const float *rows, int64_t n_rows, int dim,
-                         int64_t ld, const float *queries, int nq, const float *inv_nq, const double *nq2,
+                         int64_t ld, const float *queries, int nq, const float *inv_nq, const float *nq2f,
                          const float *inv_ne, const double *ne2, const float *penalty, int metric, int kprime,
                          u64 **out_lists, int **out_cnt, int *out_L, int *out_cap, float *dump = nullptr) {
     if (!gemm_supported(dim, ld)) { snprintf(p.err, sizeof p.err, "gemm_tf32 needs dim %% 4 == 0 (dim %d, ld %lld)", dim, (long long)ld); return -1; }
@@ -527,7 +527,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     unsigned char *wsb = reinterpret_cast<unsigned char *>(ws.p);
     GemmArgs a;
     a.n_rows = n_rows; a.dim = dim; a.nq = nq; a.nqb = nqb; a.kprime = kprime; a.cap = cap;
-    a.inv_nq = inv_nq; a.nq2 = nq2; a.inv_ne = inv_ne; a.ne2 = ne2; a.penalty = penalty;
+    a.inv_nq = inv_nq; a.nq2f = nq2f; a.inv_ne = inv_ne; a.ne2 = ne2; a.penalty = penalty;
     a.lists = reinterpret_cast<u64 *>(wsb);
     a.list_cnt = reinterpret_cast<int *>(wsb + cnt_off);
     a.pub = reinterpret_cast<u64 *>(wsb + pub_off);

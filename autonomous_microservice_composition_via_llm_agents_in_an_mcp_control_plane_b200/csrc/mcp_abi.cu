@@ -100,9 +100,11 @@ struct mcp_index {
     int opt_path = MCP_PATH_AUTO, opt_kprime = 0, opt_max_fallback = 4, opt_time_coarse = 0;
     // workspace
     Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, exact_key, exact_row, flags,
-        exact_all, out_ids, out_scores, out_scores64, gemm_ws, q_pad;
+        exact_all, out_ids, out_scores, out_scores64, gemm_ws, q_pad, inv_nq_exact, nq2f;
     int *h_status = nullptr;   // pinned: [0] certificate failures, [1] unresolved
     cudaStream_t stream = nullptr;
+    cudaStream_t aux = nullptr;            // side stream: exact query norms run here, beside the coarse scan
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t done = nullptr;
     bool pending = false;
     cudaStream_t last_stream = nullptr;
@@ -133,6 +135,9 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     if (prop.major != 10) { delete idx; return fail(MCP_ECUDA, "device %d is sm_%d%d; this library holds sm_100a code only", device_id, prop.major, prop.minor); }
     CU(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&idx->done, cudaEventDisableTiming));
+    CU(cudaStreamCreateWithFlags(&idx->aux, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&idx->ev_fork, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&idx->ev_join, cudaEventDisableTiming));
     CU(cudaMallocHost(&idx->h_status, 4 * sizeof(int)));
     idx->h_status[0] = idx->h_status[1] = 0;
     CU(cudaFuncSetAttribute(rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SMEM_BYTES(8192)));
@@ -151,11 +156,14 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     Buf *bufs[] = {&idx->own_rows, &idx->norm2, &idx->inv_norm, &idx->penalty, &idx->consts, &idx->q_copy,
                    &idx->nq2, &idx->inv_nq, &idx->qflag, &idx->scores, &idx->listsA, &idx->listsB, &idx->cntA,
                    &idx->cntB, &idx->exact_key, &idx->exact_row, &idx->flags, &idx->exact_all, &idx->out_ids,
-                   &idx->out_scores, &idx->out_scores64, &idx->gemm_ws, &idx->q_pad};
+                   &idx->out_scores, &idx->out_scores64, &idx->gemm_ws, &idx->q_pad, &idx->inv_nq_exact, &idx->nq2f};
     for (Buf *b : bufs) b->release();
     for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
     if (idx->h_status) cudaFreeHost(idx->h_status);
     if (idx->done) cudaEventDestroy(idx->done);
+    if (idx->ev_fork) cudaEventDestroy(idx->ev_fork);
+    if (idx->ev_join) cudaEventDestroy(idx->ev_join);
+    if (idx->aux) cudaStreamDestroy(idx->aux);
     if (idx->stream) cudaStreamDestroy(idx->stream);
     delete idx;
     return MCP_OK;
@@ -470,9 +478,26 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     if ((size_t)(nq + 8) * sizeof(int) > idx->flags.cap) return fail(MCP_EINVAL, "n_queries %d exceeds the flag buffer", nq);
     // flags: [0] n_flag (zero between kernels) [1] certificate failures [2] unresolved (both since last sync_status) [8..] list
     int *n_flag = idx->flags.as<int>(), *status = n_flag + 1, *flag_list = n_flag + 8;
-    prep_queries_kernel<<<nq, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
-        d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>());
-    KL();
+    if ((rc = idx->inv_nq_exact.ensure(sizeof(float) * nq))) return rc;
+    if ((rc = idx->nq2f.ensure(sizeof(float) * nq))) return rc;
+    // coarse kernels only need fp32 inverse norms; the exact fp64 norms (a dim-long dependent chain per query) and
+    // the query flags are consumed by the rescoring stage, so they are computed on a side stream meanwhile
+    bool forked = false;
+    if (path == MCP_PATH_EXACT_FP64) {
+        prep_queries_kernel<<<nq, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
+            d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>());
+        KL();
+    } else {
+        prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>());
+        KL();
+        CU(cudaEventRecord(idx->ev_fork, st));
+        CU(cudaStreamWaitEvent(idx->aux, idx->ev_fork, 0));
+        prep_queries_kernel<<<nq, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), idx->aux>>>(
+            d_q, dim, idx->nq2.as<double>(), idx->inv_nq_exact.as<float>(), idx->qflag.as<unsigned char>());
+        KL();
+        CU(cudaEventRecord(idx->ev_join, idx->aux));
+        forked = true;
+    }
 
     idx->stats.searches++; idx->stats.queries += nq; idx->stats.last_path = path; idx->stats.last_kprime = kprime;
 
@@ -501,7 +526,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     CertParams cp;
     cp.metric = idx->metric; cp.path = path; cp.complete = (n <= kprime);
     const double u = 5.9604644775390625e-08;   // 2^-24
-    if (path == MCP_PATH_STREAM_FP32) cp.rel = 2.0 * (dim / 32.0 + 16.0) * u;
+    if (path == MCP_PATH_STREAM_FP32) cp.rel = 2.0 * (dim / 32.0 + 32.0) * u;   // + the fp32 tree-summed query norm
     else cp.rel = 1.02 * 0.001953125 + dim * 4.0 * u;      // TF32 truncation of both operands (2^-9) + fp32 accumulation
     cp.abs_pen = 8.0 * u;
 
@@ -542,7 +567,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
         } else {
             int L, cap; u64 *lists; int *cnts;
             if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, idx->d_rows, n, dim, idx->ld, dq, cq,
-                                    idx->inv_nq.as<float>() + q0, idx->nq2.as<double>() + q0, idx->inv_norm.as<float>(),
+                                    idx->inv_nq.as<float>() + q0, idx->nq2f.as<float>() + q0, idx->inv_norm.as<float>(),
                                     idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap)))
                 return fail(rc, "%s", idx->gemm.err);
             idx->stats.kernel_launches++;
@@ -552,6 +577,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride, true)))
                 return rc;
         }
+        if (forked) { CU(cudaStreamWaitEvent(st, idx->ev_join, 0)); forked = false; }   // exact norms + flags are ready
         rescore_kernel<<<dim3((cand_stride + RS_ROWS - 1) / RS_ROWS, cq), RESCORE_THREADS,
                          RS_SMEM_BYTES(dim), st>>>(idx->d_rows, dim, idx->ld, dq, idx->nq2.as<double>() + q0,
                                                     idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt,
@@ -683,8 +709,9 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     if ((rc = idx->nq2.ensure(sizeof(double) * n_queries))) return rc;
     if ((rc = idx->inv_nq.ensure(sizeof(float) * n_queries))) return rc;
     if ((rc = idx->qflag.ensure(n_queries))) return rc;
-    prep_queries_kernel<<<n_queries, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
-        queries_device, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>());
+    if ((rc = idx->nq2f.ensure(sizeof(float) * n_queries))) return rc;
+    prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
+                                                                 idx->nq2f.as<float>());   // what a search feeds its coarse kernel
     KCHECK();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     if (path == MCP_PATH_STREAM_FP32) {
@@ -698,7 +725,7 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     } else if (path == MCP_PATH_GEMM_TF32) {
         u64 *l; int *c; int L, cap;
         if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, idx->d_rows, idx->n_rows, dim, idx->ld, queries_device,
-                                n_queries, idx->inv_nq.as<float>(), idx->nq2.as<double>(), idx->inv_norm.as<float>(),
+                                n_queries, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), idx->inv_norm.as<float>(),
                                 idx->norm2.as<double>(), pen, idx->metric, 64, &l, &c, &L, &cap, out_scores_device)))
             return fail(rc, "%s", idx->gemm.err);
     } else

@@ -103,6 +103,21 @@ prep_queries_kernel(const float *__restrict__ queries, int dim, double *__restri
     }
 }
 
+// fp32 inverse norms of a query batch, one warp per query: all the coarse kernels need.  The exact fp64 norm
+// (prep_queries_kernel: a dim-long dependent chain) is only needed by the rescoring stage, so it runs on a side
+// stream while the coarse scan is under way.
+__global__ void __launch_bounds__(128)
+prep_queries_fast_kernel(const float *__restrict__ queries, int n_queries, int dim, float *__restrict__ inv_norm,
+                         float *__restrict__ norm2f) {
+    const int q = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (q >= n_queries) return;
+    const float *src = queries + (int64_t)q * dim;
+    float acc = 0.f;
+    for (int i = lane; i < dim; i += 32) { const float v = src[i]; acc = fmaf(v, v, acc); }
+    acc = warp_sum(acc);
+    if (lane == 0) { inv_norm[q] = 1.0f / sqrtf(acc); norm2f[q] = acc; }   // zero query -> inf -> NaN scores, like the exact path
+}
+
 __global__ void penalty_stats_kernel(const float *__restrict__ pen, int64_t n, TableConsts *consts) {
     float mx = -CUDART_INF_F, amx = 0.f;
     bool bad = false;

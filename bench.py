@@ -59,7 +59,7 @@ class ClockSampler:
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                                           "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -73,7 +73,7 @@ class ClockSampler:
 
     def __exit__(self, *exc):
         if self.proc:
-            time.sleep(0.12)
+            time.sleep(0.05)
             self.proc.terminate()
             try:
                 self.proc.wait(2)

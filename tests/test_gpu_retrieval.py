@@ -221,7 +221,7 @@ def test_coarse_scores_within_certified_bounds(mcp, oracle, metric, path):
             got = idx.coarse_scores_device(torch.from_numpy(qs).to(dev), path)
             torch.cuda.synchronize()
             got = got.cpu().numpy().astype(np.float64)
-        rel = 2.0 * (d / 32.0 + 16.0) * u if path == "stream_fp32" else 1.02 * 2.0 ** -9 + d * 4.0 * u
+        rel = 2.0 * (d / 32.0 + 32.0) * u if path == "stream_fp32" else 1.02 * 2.0 ** -9 + d * 4.0 * u
         qn = np.linalg.norm(qs.astype(np.float64), axis=1)[:, None]
         en = np.linalg.norm(rows.astype(np.float64), axis=1)[None, :]
         if metric == 0:

@@ -147,3 +147,45 @@ def test_control_plane_surface(mcp):
 
     reg = cp.ServiceRegistry(client=FakeRedis({"mcp:service:a": '{"name": "a", "endpoint": "http://a"}', "other": "1"}))
     assert reg.list_services() == [{"name": "a", "endpoint": "http://a"}]
+
+
+def test_micro_batcher_coalesces_and_answers_each_caller(mcp):
+    """Host logic only (a numpy stand-in for the index): concurrent single queries share launches, every caller gets
+    the answer to *its* query, a shorter k is a prefix, and an error reaches every waiting caller."""
+    import threading
+    import time
+
+    from autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 import control_plane as cp
+
+    table = np.random.default_rng(0).standard_normal((500, 16)).astype(np.float32)
+    calls = []
+
+    def fake_search(q, k):
+        calls.append(q.shape[0])
+        time.sleep(0.01)                                   # a launch in flight: later requests pile up behind it
+        d = ((q[:, None, :] - table[None]) ** 2).sum(-1)
+        ids = np.argsort(d, axis=1, kind="stable")[:, :k].astype(np.int32)
+        return ids, np.take_along_axis(d, ids, 1).astype(np.float32), None
+
+    mb = cp.MicroBatcher(fake_search, max_batch=64)
+    qs = np.random.default_rng(1).standard_normal((200, 16)).astype(np.float32)
+    out = [None] * 200
+
+    def client(i):
+        out[i] = mb.search(qs[i], 3 + i % 4)
+
+    th = [threading.Thread(target=client, args=(i,)) for i in range(200)]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    for i in range(200):
+        want = np.argsort(((qs[i] - table) ** 2).sum(-1), kind="stable")[:3 + i % 4]
+        assert out[i][0].tolist() == want.tolist()
+    assert sum(calls) == 200 and len(calls) < 60 and max(calls) <= 64     # coalesced, capped
+    assert mb.requests == 200 and mb.launches == len(calls)
+    mb.close()
+    boom = cp.MicroBatcher(lambda q, k: (_ for _ in ()).throw(ValueError("no device")))
+    with pytest.raises(ValueError):
+        boom.search(qs[0], 3)
+    boom.close()
