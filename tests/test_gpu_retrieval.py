@@ -235,3 +235,53 @@ def test_coarse_scores_within_certified_bounds(mcp, oracle, metric, path):
         err = np.abs(got - exact)
         worst = np.unravel_index(np.argmax(err - eps), err.shape)
         assert (err <= eps).all(), f"{path} metric {metric} n={n} d={d}: |coarse-exact|={err[worst]:.3e} at (q,row)={worst}, bound {np.broadcast_to(eps, err.shape)[worst]:.3e}"
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+def test_gemm_list_prune_path(mcp, oracle, metric):
+    """Without the cross-CTA bootstrap every (CTA, query) list starts empty and fills up, so the register-only warp
+    radix select that cuts a full list back to k' runs many times; with it, almost never.  Both must give the oracle's
+    answer -- this is the only test that drives the prune path hard (one query block, 30K rows per... list)."""
+    rng = np.random.default_rng(31 + metric)
+    n, d, q, k = 60_000, 128, 40, 24
+    rows = rng.standard_normal((n, d), dtype=np.float32)
+    qs = rng.standard_normal((q, d), dtype=np.float32)
+    pen = (rng.random(n) * 0.02).astype(np.float32)
+    want_ids, want_s64, _ = oracle.topk(rows, qs, k, metric, pen)
+    for boot in (0, 1):
+        with mcp.ServiceIndex(d, "cosine" if metric == 0 else "l2") as idx:
+            idx.load(rows).set_penalty(pen)
+            idx.set_option("path", "gemm_tf32").set_option("gemm_bootstrap", boot).set_option("kprime", 32)
+            _assert_parity(idx.search(qs, k), want_ids, want_s64)
+            assert idx.stats()["last_kprime"] == 32
+
+
+def test_micro_batched_planner_matches_direct_search(mcp, oracle):
+    import threading
+
+    from autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 import control_plane as cp
+
+    rows = cases.unit_rows(20_000, 1536, 77)
+    names = [f"s{i}" for i in range(len(rows))]
+
+    class Reg:
+        def list_services(self):
+            return []
+
+    planner = cp.GraphPlanner(Reg(), fetch_embeddings=lambda: list(zip(names, rows)), top_k=6, micro_batch=True)
+    planner.refresh_index([])
+    intents = [f"intent {i}" for i in range(96)]
+    got = [None] * len(intents)
+
+    def client(i):
+        got[i] = planner.retrieve(intents[i])
+
+    th = [threading.Thread(target=client, args=(i,)) for i in range(len(intents))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    qs = np.stack([cp.hash_embedding(t) for t in intents])
+    want_ids, want_s64, _ = oracle.topk(rows, qs, 6, 0, np.zeros(len(rows), np.float32))
+    assert [[n for n, _ in r] for r in got] == [[names[i] for i in row] for row in want_ids]
+    assert planner._batcher.requests == 96 and planner._batcher.launches <= 96
