@@ -289,6 +289,9 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
     } else if (!strcmp(name, "max_fallback")) {
         if (value < 1 || value > 64) return fail(MCP_EINVAL, "max_fallback %lld outside [1, 64]", (long long)value);
         idx->opt_max_fallback = (int)value;
+    } else if (!strcmp(name, "gemm_cluster")) {
+        if (value != 0 && value != 1 && value != 2 && value != 4) return fail(MCP_EINVAL, "gemm_cluster must be 0, 1, 2 or 4");
+        idx->gemm.cluster_opt = (int)value;
     } else if (!strcmp(name, "gemm_debug")) {
         idx->gemm.debug = (int)value;
     } else if (!strcmp(name, "gemm_l2_prefetch")) {
