@@ -485,22 +485,31 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     if ((rc = idx->nq2f.ensure(sizeof(float) * nq))) return rc;
     // coarse kernels only need fp32 inverse norms; the exact fp64 norms (a dim-long dependent chain per query) and
     // the query flags are consumed by the rescoring stage, so they are computed on a side stream meanwhile
-    bool forked = false;
-    if (path == MCP_PATH_EXACT_FP64) {
+    bool forked = false, joined = false;
+    if (path != MCP_PATH_STREAM_FP32) {
+        // the tensor-core scan wants every SM to itself (measured: co-running the exact-norm CTAs slows it by more than they
+        // take), so here the exact norms simply come first; the fork below is for the small-batch streaming path
         prep_queries_kernel<<<nq, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
-            d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>());
+            d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), idx->nq2f.as<float>());
         KL();
+        forked = joined = true;
     } else {
         prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>());
         KL();
-        CU(cudaEventRecord(idx->ev_fork, st));
+        CU(cudaEventRecord(idx->ev_fork, st));      // the side stream may start once the queries are in place ...
         CU(cudaStreamWaitEvent(idx->aux, idx->ev_fork, 0));
+    }
+    // ... but its kernel is enqueued right after the first coarse launch, so that the coarse kernel gets the SMs first
+    // and the small exact-norm CTAs fill in beside it
+    auto launch_exact_prep = [&]() -> int {
+        if (forked) return MCP_OK;
         prep_queries_kernel<<<nq, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), idx->aux>>>(
-            d_q, dim, idx->nq2.as<double>(), idx->inv_nq_exact.as<float>(), idx->qflag.as<unsigned char>());
+            d_q, dim, idx->nq2.as<double>(), idx->inv_nq_exact.as<float>(), idx->qflag.as<unsigned char>(), nullptr);
         KL();
         CU(cudaEventRecord(idx->ev_join, idx->aux));
         forked = true;
-    }
+        return MCP_OK;
+    };
 
     idx->stats.searches++; idx->stats.queries += nq; idx->stats.last_path = path; idx->stats.last_kprime = kprime;
 
@@ -556,6 +565,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
                 if ((rc = run_scan_pass(idx, st, dqs + (int64_t)p * dimp, dimp, idx->inv_nq.as<float>() + q0 + p, nv,
                                         idx->scores.as<float>() + (int64_t)p * n, n)))
                     return rc;
+                if ((rc = launch_exact_prep())) return rc;
             }
             if ((rc = coarse_event(idx, st))) return rc;
             int P = (int)((n + SEL_MAX - 1) / SEL_MAX);
@@ -574,13 +584,15 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
                                     idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap)))
                 return fail(rc, "%s", idx->gemm.err);
             idx->stats.kernel_launches++;
+            if ((rc = launch_exact_prep())) return rc;
             if ((rc = coarse_event(idx, st))) return rc;
             // the GEMM's lists live in gemm_ws; reductions ping-pong between listsA / listsB
             // K2 lists are raw (fp32 bits, row) pairs: always pass them through one reduction, which builds the ordered keys
             if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride, true)))
                 return rc;
         }
-        if (forked) { CU(cudaStreamWaitEvent(st, idx->ev_join, 0)); forked = false; }   // exact norms + flags are ready
+        if ((rc = launch_exact_prep())) return rc;
+        if (!joined) { CU(cudaStreamWaitEvent(st, idx->ev_join, 0)); joined = true; }   // exact norms + flags are ready
         rescore_kernel<<<dim3((cand_stride + RS_ROWS - 1) / RS_ROWS, cq), RESCORE_THREADS,
                          RS_SMEM_BYTES(dim), st>>>(idx->d_rows, dim, idx->ld, dq, idx->nq2.as<double>() + q0,
                                                     idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt,
@@ -713,8 +725,13 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     if ((rc = idx->inv_nq.ensure(sizeof(float) * n_queries))) return rc;
     if ((rc = idx->qflag.ensure(n_queries))) return rc;
     if ((rc = idx->nq2f.ensure(sizeof(float) * n_queries))) return rc;
-    prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
-                                                                 idx->nq2f.as<float>());   // what a search feeds its coarse kernel
+    // the same query norms a search would feed this coarse kernel
+    if (path == MCP_PATH_STREAM_FP32)
+        prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
+                                                                     idx->nq2f.as<float>());
+    else
+        prep_queries_kernel<<<n_queries, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
+            queries_device, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), idx->nq2f.as<float>());
     KCHECK();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     if (path == MCP_PATH_STREAM_FP32) {

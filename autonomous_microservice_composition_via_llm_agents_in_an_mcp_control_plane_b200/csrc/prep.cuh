@@ -72,7 +72,7 @@ prep_rows_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64_
 #define PREPQ_THREADS 128
 __global__ void __launch_bounds__(PREPQ_THREADS)
 prep_queries_kernel(const float *__restrict__ queries, int dim, double *__restrict__ norm2,
-                    float *__restrict__ inv_norm, unsigned char *__restrict__ qflag) {
+                    float *__restrict__ inv_norm, unsigned char *__restrict__ qflag, float *__restrict__ norm2f) {
     extern __shared__ __align__(16) float sq_prep[];
     __shared__ int s_bad;
     const int q = blockIdx.x;
@@ -98,6 +98,7 @@ prep_queries_kernel(const float *__restrict__ queries, int dim, double *__restri
         for (int i = d4; i < dim; ++i) acc = fma((double)sq_prep[i], (double)sq_prep[i], acc);
         norm2[q] = acc;
         inv_norm[q] = (float)(1.0 / sqrt(acc));
+        if (norm2f) norm2f[q] = (float)acc;
         bool odd = (acc != 0.0) && (acc < 1e-30 || acc > 1e30);
         qflag[q] = (unsigned char)((s_bad ? 2 : 0) | ((odd || acc == 0.0 || s_bad) ? 1 : 0));
     }

@@ -232,7 +232,8 @@ def main():
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (repeatable), e.g. gemm_wide=0")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
-    ap.add_argument("--dag", type=int, default=0, help="also time the Kahn-level kernel on this many synthetic DAGs (extra)")
+    ap.add_argument("--dag", type=int, default=100_000, help="also time the Kahn-level kernel on this many synthetic DAGs (extra; 0 = skip)")
+    ap.add_argument("--no-config3-ref", action="store_true", help="skip the single-GPU run of the multi-GPU workload (extra)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -405,6 +406,36 @@ def main():
             byts = enc.n_nodes.size * (1 + 4 + 128 + 2) + enc.edges.size
             extra["dag_levels"] = {"dags": args.dag, "ms": round(ms, 4), "dags_per_s": round(args.dag / ms * 1e3),
                                    "GBps": round(byts / (ms * 1e-3) / 1e9, 1), "with_order": True}
+        if wl == "config2" and not args.no_config3_ref and not args.no_extras and not (args.rows or args.queries or args.topk):
+            # the multi-GPU workload (config 3) on this one GPU, so that the N = 2, 4, 8 lines (strong scaling over a fixed
+            # 10M-row table) have an N = 1 point; the headline N = 1 line above is config 2 as BASELINE.json quotes it
+            try:
+                c3 = CONFIGS["config3"]
+                sh.close()
+                del rows, pen
+                torch.cuda.empty_cache()
+                rows3 = make_shard(torch, dev, 0, c3["n"], dim, c3["seeds"][0])
+                pen3 = make_penalty(torch, dev, c3["n"], c3["seeds"][2])
+                q3 = make_queries(torch, dev, c3["q"], dim, c3["seeds"][1])
+                sh = sharded.ShardedIndex(dim, c3["metric"], local)
+                sh.adopt_shard(rows3, c3["n"]).set_penalty(pen3)
+                for _ in range(2):
+                    sh.search_device(q3, c3["k"])
+                torch.cuda.synchronize()
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record()
+                for _ in range(5):
+                    sh.search_device(q3, c3["k"])
+                a1.record()
+                torch.cuda.synchronize()
+                ms3 = a0.elapsed_time(a1) / 5
+                f3, u3 = sh.sync_status()
+                extra["config3_on_1_gpu"] = {"workload": c3["label"], "ms_per_step": round(ms3, 3), "queries_per_s": round(c3["q"] / ms3 * 1e3, 1),
+                                             "TFLOPs": round(2.0 * c3["q"] * c3["n"] * dim / (ms3 * 1e-3) / 1e12, 1),
+                                             "certificate_failures": f3, "unresolved": u3}
+                rows, pen, qs = rows3[:n], pen3[:n].contiguous(), make_queries(torch, dev, q, dim, cfg["seeds"][1])   # for the CPU baseline below
+            except Exception as ex:  # noqa: BLE001 -- an extra must never take the headline line down
+                extra["config3_on_1_gpu"] = {"error": str(ex)[:200]}
         if not args.no_cpu_baseline:
             import oracle
 
