@@ -102,6 +102,8 @@ struct mcp_index {
     Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, exact_key, exact_row, flags,
         exact_all, out_ids, out_scores, out_scores64, gemm_ws, q_pad, inv_nq_exact, nq2f;
     int *h_status = nullptr;   // pinned: [0] certificate failures, [1] unresolved
+    unsigned char *h_stage = nullptr;   // pinned staging for the host-buffer search: results + status in one copy
+    size_t h_stage_cap = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t aux = nullptr;            // side stream: exact query norms run here, beside the coarse scan
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -160,6 +162,7 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     for (Buf *b : bufs) b->release();
     for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
     if (idx->h_status) cudaFreeHost(idx->h_status);
+    if (idx->h_stage) cudaFreeHost(idx->h_stage);
     if (idx->done) cudaEventDestroy(idx->done);
     if (idx->ev_fork) cudaEventDestroy(idx->ev_fork);
     if (idx->ev_join) cudaEventDestroy(idx->ev_join);
@@ -679,32 +682,44 @@ extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n
     }
     CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
     idx->last_stream = st;
+    // Results and status come back in ONE device->host copy into a pinned staging buffer, after ONE synchronisation:
+    // device layout [scores64 f64 nk | ids i32 nk | scores f32 nk | status 2 x i32]
     const size_t nk = (size_t)n_queries * k;
+    const size_t off_ids = sizeof(double) * nk, off_sc = off_ids + sizeof(int32_t) * nk, off_st = off_sc + sizeof(float) * nk;
+    const size_t total = off_st + 2 * sizeof(int);
     if ((rc = idx->q_copy.ensure(sizeof(float) * (size_t)n_queries * idx->dim))) return rc;
-    if ((rc = idx->out_ids.ensure(sizeof(int32_t) * nk))) return rc;
-    if ((rc = idx->out_scores.ensure(sizeof(float) * nk))) return rc;
-    if ((rc = idx->out_scores64.ensure(sizeof(double) * nk))) return rc;
+    if ((rc = idx->out_ids.ensure(total))) return rc;                 // one buffer holds all three outputs
+    if (total > idx->h_stage_cap) {
+        if (idx->h_stage) cudaFreeHost(idx->h_stage);
+        idx->h_stage = nullptr; idx->h_stage_cap = 0;
+        CU(cudaMallocHost(&idx->h_stage, total + total / 4));
+        idx->h_stage_cap = total + total / 4;
+    }
+    unsigned char *dbase = idx->out_ids.as<unsigned char>();
+    double *d_s64 = reinterpret_cast<double *>(dbase);
+    int32_t *d_ids = reinterpret_cast<int32_t *>(dbase + off_ids);
+    float *d_sc = reinterpret_cast<float *>(dbase + off_sc);
     CU(cudaMemcpyAsync(idx->q_copy.p, queries_host, sizeof(float) * (size_t)n_queries * idx->dim, cudaMemcpyHostToDevice, st));
     for (int attempt = 0; attempt < 2; ++attempt) {
         int saved = idx->opt_path;
-        if (attempt == 1) idx->opt_path = MCP_PATH_EXACT_FP64;      // leftovers beyond the device-side fallback slots
-        rc = search_locked(idx, idx->q_copy.as<float>(), n_queries, k, idx->out_ids.as<int32_t>(),
-                           idx->out_scores.as<float>(), idx->out_scores64.as<double>(), st);
+        if (attempt == 1) idx->opt_path = MCP_PATH_EXACT_FP64;      // leftovers beyond the device-side fallback slots (rare)
+        rc = search_locked(idx, idx->q_copy.as<float>(), n_queries, k, d_ids, d_sc, d_s64, st);
         idx->opt_path = saved;
         if (rc) return rc;
-        CU(cudaMemcpyAsync(idx->h_status, idx->flags.as<int>() + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
-        if (attempt == 0) {
-            idx->stats.certificate_failures += idx->h_status[0];
-            idx->stats.exact_scans += idx->h_status[0] - idx->h_status[1];
-        }
+        CU(cudaMemcpyAsync(dbase + off_st, idx->flags.as<int>() + 1, 2 * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        CU(cudaMemcpyAsync(idx->h_stage, dbase, total, cudaMemcpyDeviceToHost, st));
         CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
-        if (idx->h_status[1] == 0) break;
+        CU(cudaStreamSynchronize(st));
+        const int *hs = reinterpret_cast<const int *>(idx->h_stage + off_st);
+        if (attempt == 0) {
+            idx->stats.certificate_failures += hs[0];
+            idx->stats.exact_scans += hs[0] - hs[1];
+        }
+        if (hs[1] == 0) break;
     }
-    CU(cudaMemcpyAsync(out_ids, idx->out_ids.p, sizeof(int32_t) * nk, cudaMemcpyDeviceToHost, st));
-    CU(cudaMemcpyAsync(out_scores, idx->out_scores.p, sizeof(float) * nk, cudaMemcpyDeviceToHost, st));
-    if (out_scores64) CU(cudaMemcpyAsync(out_scores64, idx->out_scores64.p, sizeof(double) * nk, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    memcpy(out_ids, idx->h_stage + off_ids, sizeof(int32_t) * nk);
+    memcpy(out_scores, idx->h_stage + off_sc, sizeof(float) * nk);
+    if (out_scores64) memcpy(out_scores64, idx->h_stage, sizeof(double) * nk);
     return MCP_OK;
 }
 
