@@ -43,6 +43,7 @@ SIGNATURES = {
     "mcp_index_destroy": (_i32, [_vp]),
     "mcp_index_load": (_i32, [_vp, _vp, _i64, _i64]),
     "mcp_index_adopt_device": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp]),
+    "mcp_index_update_rows": (_i32, [_vp, _i64, _vp, _i64]),
     "mcp_index_set_penalty": (_i32, [_vp, _vp]),
     "mcp_index_set_penalty_device": (_i32, [_vp, _vp, _vp]),
     "mcp_index_search": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),

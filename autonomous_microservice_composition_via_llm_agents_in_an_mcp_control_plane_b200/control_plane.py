@@ -283,7 +283,16 @@ class GraphPlanner:
 
 # ---- orchestrator (control_plane.py:87-131) ----------------------------------------------------
 class Orchestrator:
-    def __init__(self, client=None, device: int = CUDA_DEVICE):
+    """``execute`` keeps the reference's order and semantics.  Two opt-in extras from SURVEY.md section 8f item 3:
+    ``parallel_levels=True`` awaits every node of a generation together (the kernel hands back the generations; the
+    reference awaits nodes one by one, :109), ``retries=n`` re-POSTs a failing service n more times before the
+    fallback (README.md:49 promises retries, the reference has none)."""
+
+    def __init__(self, client=None, device: int = CUDA_DEVICE, parallel_levels: bool = False, retries: int = 0):
+        self.parallel_levels, self.retries = parallel_levels, retries
+        self._init(client, device)
+
+    def _init(self, client=None, device: int = CUDA_DEVICE):
         if client is None:
             import httpx
 
@@ -314,28 +323,40 @@ class Orchestrator:
         _, order, status = _dag.decode(enc, res, 0)
 
         results, errors = {}, {}
-        for name in order:                                # == list(nx.topological_sort(G)), from the kernel
+
+        async def run_node(name):
             node = nodes[name]
             service_url = node["endpoint"]                # KeyError for an undeclared node, as in the reference (:106)
             inputs = {k: results.get(v, payload.get(v)) for k, v in node["inputs"].items()}
-            try:
-                resp = await self.client.post(service_url, json=inputs, timeout=5.0)
-                resp.raise_for_status()
-                results[name] = resp.json()
-            except Exception as e:  # noqa: BLE001 -- same breadth as the reference (:112)
-                self.logger.error(f"Service {name} failed: {e}")
-                errors[name] = str(e)
-                fallback = (first_in_edge.get(name) or {}).get("fallback")
-                if not fallback:
-                    raise HTTPException(status_code=502, detail=f"{name} failed and no fallback available")
-                self.logger.info(f"Attempting fallback {fallback} for {name}")
+            last = None
+            for _ in range(1 + self.retries):
                 try:
-                    resp = await self.client.post(fallback, json=inputs, timeout=5.0)
+                    resp = await self.client.post(service_url, json=inputs, timeout=5.0)
                     resp.raise_for_status()
                     results[name] = resp.json()
-                except Exception as e2:  # noqa: BLE001
-                    self.logger.error(f"Fallback {fallback} failed: {e2}")
-                    errors[name] += f"; fallback failed: {e2}"
+                    return
+                except Exception as e:  # noqa: BLE001 -- same breadth as the reference (:112)
+                    last = e
+            self.logger.error(f"Service {name} failed: {last}")
+            errors[name] = str(last)
+            fallback = (first_in_edge.get(name) or {}).get("fallback")
+            if not fallback:
+                raise HTTPException(status_code=502, detail=f"{name} failed and no fallback available")
+            self.logger.info(f"Attempting fallback {fallback} for {name}")
+            try:
+                resp = await self.client.post(fallback, json=inputs, timeout=5.0)
+                resp.raise_for_status()
+                results[name] = resp.json()
+            except Exception as e2:  # noqa: BLE001
+                self.logger.error(f"Fallback {fallback} failed: {e2}")
+                errors[name] += f"; fallback failed: {e2}"
+
+        if self.parallel_levels:
+            for gen in _dag.generations(enc, res, 0):     # nodes of one generation have no edges between them
+                await asyncio.gather(*(run_node(n) for n in gen))
+        else:
+            for name in order:                            # == list(nx.topological_sort(G)), from the kernel
+                await run_node(name)
         if status:
             # the reference raises only after the acyclic prefix has been POSTed
             raise nx.NetworkXUnfeasible("Graph contains a cycle or graph changed during iteration")

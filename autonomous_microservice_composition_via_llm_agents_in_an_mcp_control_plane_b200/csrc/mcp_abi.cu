@@ -225,6 +225,35 @@ extern "C" int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, 
     return prepare_table(idx, (cudaStream_t)stream);
 }
 
+// Registry refresh without a reload: rows [first_row, first_row + n_rows) changed.
+extern "C" int mcp_index_update_rows(mcp_index *idx, int64_t first_row, const float *rows_host, int64_t n_rows) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!idx->n_rows) return fail(MCP_ESTATE, "update_rows before load");
+    if (first_row < 0 || n_rows < 1 || first_row + n_rows > idx->n_rows) return fail(MCP_EINVAL, "row range [%lld, %lld) outside the table", (long long)first_row, (long long)(first_row + n_rows));
+    CU(cudaSetDevice(idx->device));
+    if (idx->pending) { CU(cudaEventSynchronize(idx->done)); }      // searches in flight read the rows
+    cudaStream_t st = idx->stream;
+    idx->last_stream = st;
+    if (rows_host) {
+        if (idx->d_rows != idx->own_rows.as<float>()) return fail(MCP_ESTATE, "the table is adopted device memory: change it in place and pass rows_host = NULL");
+        CU(cudaMemcpy2DAsync(idx->own_rows.as<float>() + first_row * idx->ld, sizeof(float) * idx->ld, rows_host, sizeof(float) * idx->dim,
+                             sizeof(float) * idx->dim, (size_t)n_rows, cudaMemcpyHostToDevice, st));
+    }
+    // norms of the changed rows; bad_rows is counted afresh, the maximum norm only ever grows (a larger bound stays valid)
+    TableConsts *c = idx->consts.as<TableConsts>();
+    CU(cudaMemsetAsync(&c->bad_rows, 0, sizeof(unsigned int), st));
+    unsigned blocks = (unsigned)((n_rows + PREP_ROWS - 1) / PREP_ROWS);
+    prep_rows_kernel<false><<<blocks, PREP_ROWS, 0, st>>>(idx->d_rows + first_row * idx->ld, n_rows, idx->dim, idx->ld,
+                                                          idx->norm2.as<double>() + first_row, idx->inv_norm.as<float>() + first_row,
+                                                          nullptr, c);
+    KCHECK();
+    CU(cudaMemcpyAsync(&idx->h_consts, c, sizeof(TableConsts), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (idx->h_consts.bad_rows) return fail(MCP_EINVAL, "%u updated rows hold NaN/Inf elements; the table now contains them -- update again", idx->h_consts.bad_rows);
+    return MCP_OK;
+}
+
 static int penalty_stats(mcp_index *idx, cudaStream_t st) {
     TableConsts *c = idx->consts.as<TableConsts>();
     CU(cudaMemsetAsync(&c->pen_max, 0, 3 * sizeof(unsigned int), st));   // pen_max, pen_absmax, bad_pen

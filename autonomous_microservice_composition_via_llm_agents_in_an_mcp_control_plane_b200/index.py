@@ -88,6 +88,59 @@ class ServiceIndex:
         self._keep = [rows]
         return self
 
+    def update_rows(self, first_row: int, rows: Optional[np.ndarray] = None, n_rows: Optional[int] = None) -> "ServiceIndex":
+        """Replace rows [first_row, first_row + len(rows)) of a loaded table, or (rows=None) tell the index that the owner
+        of an adopted table changed n_rows rows in place; norms are recomputed, nothing else is reloaded."""
+        if rows is not None:
+            rows = np.ascontiguousarray(rows, dtype=np.float32)
+            if rows.ndim != 2 or rows.shape[1] != self.dim:
+                raise ValueError(f"rows must be [n, {self.dim}] float32")
+            nat.check(self._lib.mcp_index_update_rows(self._h, int(first_row), _np_ptr(rows), rows.shape[0]))
+        else:
+            nat.check(self._lib.mcp_index_update_rows(self._h, int(first_row), None, int(n_rows)))
+        return self
+
+    # ---- flat-file table format (SURVEY.md section 8f item 4) ------------------------------------------------
+    # <path>: 64-byte header (magic "MCPTBL01", dim, n_rows, id_base, metric as little-endian int64) + N x dim fp32 rows,
+    # row-major -- mmap-able, so a registry loads at file-system speed instead of through Postgres rows (control_plane.py:54).
+    # <path>.names: one service name per line (optional sidecar).
+    @staticmethod
+    def save_table(path, rows: np.ndarray, names=None, id_base: int = 0, metric: int = 0) -> None:
+        rows = np.ascontiguousarray(rows, dtype=np.float32)
+        hdr = np.zeros(8, np.int64)
+        hdr[0] = int.from_bytes(b"MCPTBL01", "little")
+        hdr[1:5] = (rows.shape[1], rows.shape[0], id_base, metric)
+        with open(path, "wb") as f:
+            f.write(hdr.tobytes())
+            f.write(rows.tobytes())
+        if names is not None:
+            with open(str(path) + ".names", "w", encoding="utf-8") as f:
+                f.write("\n".join(names))
+
+    @staticmethod
+    def open_table(path):
+        """-> (rows memmap [N, dim] float32, names or None, id_base, metric) without reading the rows."""
+        hdr = np.fromfile(path, dtype=np.int64, count=8)
+        if hdr.size != 8 or hdr[0] != int.from_bytes(b"MCPTBL01", "little"):
+            raise ValueError(f"{path}: not an MCPTBL01 table file")
+        dim, n, id_base, metric = (int(x) for x in hdr[1:5])
+        rows = np.memmap(path, dtype=np.float32, mode="r", offset=64, shape=(n, dim))
+        names = None
+        try:
+            with open(str(path) + ".names", encoding="utf-8") as f:
+                names = f.read().split("\n")
+        except FileNotFoundError:
+            pass
+        return rows, names, id_base, metric
+
+    def load_file(self, path) -> list:
+        """Load a table written by ``save_table``; returns the names sidecar (or None)."""
+        rows, names, id_base, _ = self.open_table(path)
+        if rows.shape[1] != self.dim:
+            raise ValueError(f"{path} holds dim {rows.shape[1]}, index has dim {self.dim}")
+        self.load(rows, id_base)
+        return names
+
     def set_penalty(self, penalty) -> "ServiceIndex":
         if penalty is None:
             nat.check(self._lib.mcp_index_set_penalty(self._h, None))

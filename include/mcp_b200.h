@@ -83,6 +83,11 @@ int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_rows, int64
 int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, int64_t n_rows, int64_t ld,
                            int64_t id_base, void *stream);
 
+/* Registry refresh without a reload: rows [first_row, first_row + n_rows) are replaced by
+ * rows_host (tables made by mcp_index_load), or -- rows_host = NULL -- were changed in place by the owner of an adopted
+ * table; their norms are recomputed.  Blocks until searches in flight have finished.                                  */
+int mcp_index_update_rows(mcp_index *idx, int64_t first_row, const float *rows_host, int64_t n_rows);
+
 /* ---- telemetry fold --------------------------------------------------------------------------
  * One fp32 penalty per service, added to the distance before ranking.  The reference names the
  * fields (cost_profile: control_plane.py:31, README.md:93; latency / error rate: README.md:43-48)

@@ -122,3 +122,30 @@ def test_schedule_batch(mcp, oracle):
     for i in (0, 1, 500, 1999):
         assert mcp.dag.decode(enc, res, i) == oracle.nx_levels(graphs[i])
     asyncio.run(orch.client.aclose())
+
+
+def test_parallel_levels_and_retries(mcp, oracle):
+    """Opt-in extras: a generation's nodes are awaited together (same results, calls grouped by generation), and a
+    flaky service is retried before its fallback."""
+    import httpx
+
+    calls, fail_once = [], {"http://w/api": 1}
+
+    def handler(request):
+        url = str(request.url)
+        calls.append(url)
+        if fail_once.get(url, 0) > 0:
+            fail_once[url] -= 1
+            return httpx.Response(503)
+        return httpx.Response(200, json={"from": url})
+
+    from autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 import control_plane as cp
+
+    orch = cp.Orchestrator(client=httpx.AsyncClient(transport=httpx.MockTransport(handler)), parallel_levels=True, retries=1)
+    graph = {"nodes": [{"name": n, "endpoint": f"http://{n}/api", "inputs": {}} for n in "zyxwv"],
+             "edges": [{"from": a, "to": b} for a, b in [("y", "v"), ("z", "w"), ("z", "x"), ("y", "x"), ("z", "v")]]}
+    resp = asyncio.run(orch.execute(graph, {}))
+    assert resp.errors == {} and set(resp.results) == set("zyxwv")     # w failed once, the retry succeeded
+    assert calls.count("http://w/api") == 2
+    first_gen = {"http://z/api", "http://y/api"}
+    assert set(calls[:2]) == first_gen and not (set(calls[2:]) & first_gen)   # generation 0 completes before generation 1 starts

@@ -285,3 +285,46 @@ def test_micro_batched_planner_matches_direct_search(mcp, oracle):
     want_ids, want_s64, _ = oracle.topk(rows, qs, 6, 0, np.zeros(len(rows), np.float32))
     assert [[n for n, _ in r] for r in got] == [[names[i] for i in row] for row in want_ids]
     assert planner._batcher.requests == 96 and planner._batcher.launches <= 96
+
+
+def test_update_rows_and_table_file(mcp, oracle, tmp_path):
+    """Registry refresh without a reload: replaced rows are found (or no longer found) at once, on a loaded table
+    and on an adopted one; and a table written to the flat file format searches the same after load_file."""
+    import torch
+
+    rng = np.random.default_rng(55)
+    rows = rng.standard_normal((5000, 256), dtype=np.float32)
+    qs = rng.standard_normal((12, 256), dtype=np.float32)
+    with mcp.ServiceIndex(256) as idx:
+        idx.load(rows)
+        before, _, _ = idx.search(qs, 4)
+        new = rows.copy()
+        new[1000:1012] = qs * 3.0                                      # each query now has a parallel row
+        new[int(before[0, 0])] = -qs[0]                                # and query 0's old best becomes its worst
+        lo, hi = min(1000, int(before[0, 0])), max(1012, int(before[0, 0]) + 1)
+        idx.update_rows(lo, new[lo:hi])
+        want_ids, want_s64, _ = oracle.topk(new, qs, 4, 0, None)
+        _assert_parity(idx.search(qs, 4), want_ids, want_s64)
+        assert want_ids[:, 0].tolist() == list(range(1000, 1012))
+        bad = new[:3].copy()
+        bad[1, 1] = np.inf
+        with pytest.raises(mcp.McpError):
+            idx.update_rows(0, bad)
+        idx.update_rows(0, new[:3])
+    dev = torch.device("cuda:0")
+    t = torch.from_numpy(rows).to(dev)
+    with mcp.ServiceIndex(256) as idx:
+        idx.adopt(t)
+        t[1000:1012] = torch.from_numpy(qs * 3.0).to(dev)
+        torch.cuda.synchronize()
+        idx.update_rows(1000, None, 12)
+        got = idx.search(qs, 1)[0]
+        assert got[:, 0].tolist() == list(range(1000, 1012))
+        with pytest.raises(mcp.McpError):
+            idx.update_rows(0, rows[:2])                               # adopted memory belongs to the caller
+    p = tmp_path / "t.mcp"
+    mcp.ServiceIndex.save_table(p, new, [f"n{i}" for i in range(len(new))])
+    with mcp.ServiceIndex(256) as idx:
+        names = idx.load_file(p)
+        assert names[7] == "n7"
+        _assert_parity(idx.search(qs, 4), want_ids, want_s64)

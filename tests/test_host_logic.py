@@ -189,3 +189,17 @@ def test_micro_batcher_coalesces_and_answers_each_caller(mcp):
     with pytest.raises(ValueError):
         boom.search(qs[0], 3)
     boom.close()
+
+
+def test_table_file_format_round_trip(mcp, tmp_path):
+    rows = np.random.default_rng(3).standard_normal((37, 24)).astype(np.float32)
+    names = [f"svc-{i}" for i in range(37)]
+    p = tmp_path / "table.mcp"
+    mcp.ServiceIndex.save_table(p, rows, names, id_base=100, metric=1)
+    assert p.stat().st_size == 64 + rows.nbytes
+    got, got_names, id_base, metric = mcp.ServiceIndex.open_table(p)
+    assert isinstance(got, np.memmap) and np.array_equal(got, rows)
+    assert got_names == names and id_base == 100 and metric == 1
+    (tmp_path / "junk").write_bytes(b"x" * 100)
+    with pytest.raises(ValueError):
+        mcp.ServiceIndex.open_table(tmp_path / "junk")
