@@ -350,12 +350,6 @@ extern "C" int mcp_index_get_stats(mcp_index *idx, mcp_stats *out) {
 // ---------------------------------------------------------------------------------------------
 // search
 // ---------------------------------------------------------------------------------------------
-__global__ void status_accumulate_kernel(int *n_flag, int *status, int max_fallback) {
-    int f = *n_flag;
-    status[0] += f;
-    status[1] += f > max_fallback ? f - max_fallback : 0;
-    *n_flag = 0;
-}
 __global__ void flag_all_kernel(int *flag_list, int *n_flag, int q0, int n) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) flag_list[i] = q0 + i;
@@ -512,7 +506,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     if ((rc = idx->qflag.ensure(nq))) return rc;
     if ((size_t)(nq + 8) * sizeof(int) > idx->flags.cap) return fail(MCP_EINVAL, "n_queries %d exceeds the flag buffer", nq);
     // flags: [0] n_flag (zero between kernels) [1] certificate failures [2] unresolved (both since last sync_status) [8..] list
-    int *n_flag = idx->flags.as<int>(), *status = n_flag + 1, *flag_list = n_flag + 8;
+    int *n_flag = idx->flags.as<int>(), *flag_list = n_flag + 8;
     if ((rc = idx->inv_nq_exact.ensure(sizeof(float) * nq))) return rc;
     if ((rc = idx->nq2f.ensure(sizeof(float) * nq))) return rc;
     // coarse kernels only need fp32 inverse norms; the exact fp64 norms (a dim-long dependent chain per query) and
@@ -640,7 +634,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
         if ((rc = run_exact(idx, st, dq, idx->nq2.as<double>() + q0, k, idx->opt_max_fallback, out_ids + (int64_t)q0 * k, out_scores + (int64_t)q0 * k,
                             out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, true)))
             return rc;
-        (void)status;   // [1] failures, [2] unresolved, [3] ticket: folded by exact_select_kernel's last CTA
+        // flags[1] failures, [2] unresolved, [3] ticket: folded by exact_select_kernel's last CTA
         idx->stats.rows_scanned += n;
         idx->stats.bytes_scanned += n * (int64_t)dim * 4;
         idx->stats.candidates_rescored += (int64_t)cq * kc;

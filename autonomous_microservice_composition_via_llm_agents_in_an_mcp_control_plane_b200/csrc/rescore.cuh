@@ -38,7 +38,7 @@ struct CertParams {
 #define RS_ROWS 32
 #define RS_COLS 64
 #define RS_PITCH (RS_COLS + 4)        // fp32 ring row pitch (floats): 16-byte aligned rows, conflict-free LDS.128
-#define RS_STAGES 3
+#define RS_STAGES 5                   // 4 chunks (~2.4 us of chain time) of row gathers in flight per CTA; 55.5 KB smem at dim 1536 -> 4 CTAs / SM
 #define RS_SMEM_BYTES(dim) (sizeof(double) * (((dim) + 3) & ~3) + sizeof(float) * RS_STAGES * RS_ROWS * RS_PITCH + 16)
 __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
