@@ -60,6 +60,7 @@ struct GemmArgs {
     const float *rows;         // table base + row pitch, for the L2 row prefetch
     int64_t ld;
     int l2_prefetch;
+    int bn;                    // rows per tile (<= 256, a multiple of the cluster size): chosen so that every CTA gets the same number of tiles
     int cluster;               // CTAs per cluster (1, 2 or 4): the query-block CTAs that share a row tile load a slice each and multicast it
     int debug;                 // timing experiments only (results are wrong): 1 skip epilogue math, 2 skip row-tile loads, 4 skip query-tile loads, 8 skip MMAs
 };
@@ -224,7 +225,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     GemmSmemT<MT> &s = *reinterpret_cast<GemmSmemT<MT> *>(g_smem_raw + ((1024u - (smem_u32(g_smem_raw) & 1023u)) & 1023u));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qb = blockIdx.x % a.nqb, group = blockIdx.x / a.nqb, ngroups = gridDim.x / a.nqb;
-    const int n_tiles = (int)((a.n_rows + G_BN - 1) / G_BN);
+    const int BN = a.bn;                                       // rows per tile; the MMA is always N = 256, columns >= BN are ignored
+    const int n_tiles = (int)((a.n_rows + BN - 1) / BN);
     const int my_tiles = group < n_tiles ? (n_tiles - group + ngroups - 1) / ngroups : 0;
     const int KB = (a.dim + G_BK - 1) / G_BK;
     constexpr int CAP = KPL * 32;
@@ -270,7 +272,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     if (pk >= KB) { pt = t + ngroups; pk = 0; }
                     if (pt < n_tiles) {
                         const int bytes = min(8 * G_BK, a.dim - pk * G_BK) * 4;
-                        const int64_t prow0 = (int64_t)pt * G_BN;
+                        const int64_t prow0 = (int64_t)pt * BN;
 #pragma unroll
                         for (int u = 0; u < G_BN / 32; ++u) {
                             const int64_t r = prow0 + u * 32 + lane;
@@ -282,13 +284,13 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 mbar_wait(&s.empty[stage], phase ^ 1u);
                 if (lane == 0) {
                     const bool la = !(a.debug & 4) || (i == 0 && kb < Cfg::STAGES), lb = !(a.debug & 2) || (i == 0 && kb < Cfg::STAGES);
-                    mbar_expect_tx(&s.full[stage], (la ? Cfg::A_BYTES : 0) + (lb ? G_B_BYTES : 0));
+                    mbar_expect_tx(&s.full[stage], (la ? Cfg::A_BYTES : 0) + (lb ? BN * G_BK * 4 : 0));
                     if (la) tma_load_2d(s.a[stage], &tmA, kb * G_BK, qb * MT * G_BM, &s.full[stage]);
                     if (lb) {
-                        if (C == 1) tma_load_2d(s.b[stage], &tmB, kb * G_BK, t * G_BN, &s.full[stage]);
+                        if (C == 1) tma_load_2d(s.b[stage], &tmB, kb * G_BK, t * BN, &s.full[stage]);
                         else {                                 // my slice of the tile, to everyone in the cluster
-                            const int srows = G_BN / C;
-                            tma_load_2d_mc(s.b[stage] + (size_t)crank * srows * G_BK, &tmB, kb * G_BK, t * G_BN + (int)crank * srows,
+                            const int srows = BN / C;
+                            tma_load_2d_mc(s.b[stage] + (size_t)crank * srows * G_BK, &tmB, kb * G_BK, t * BN + (int)crank * srows,
                                            &s.full[stage], cmask);
                         }
                     }
@@ -349,8 +351,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int i = 0; i < my_tiles; ++i) {
             const int t = group + i * ngroups, buf = i % Cfg::NBUF, mbuf = i & 1;
             const uint32_t tphase = (uint32_t)(i / Cfg::NBUF) & 1u;
-            const int64_t row0 = (int64_t)t * G_BN;
-            const int rows_here = (int)min((int64_t)G_BN, a.n_rows - row0);
+            const int64_t row0 = (int64_t)t * BN;
+            const int rows_here = (int)min((int64_t)BN, a.n_rows - row0);
             // per-row constants of this tile (meta[mbuf] was last read two tiles ago; the named barrier of the
             // tile in between ordered those reads before these writes).  Rows past the table get +inf.
             if (et < G_BN) {
@@ -369,7 +371,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int cbase = half * 128;
             if (a.debug & 1) { tc_fence_before(); mbar_arrive(&s.tempty[buf]); continue; }
             if (a.dump) {
-                for (int c = 0; c < 128; c += 32) {
+                for (int c = 0; c < 128 && cbase + c < rows_here; c += 32) {
                     uint32_t v[32];
                     tc_ld_32x32(taddr + (uint32_t)c, v);
                     tc_ld_wait();
@@ -389,7 +391,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 // four smallest keys in scalars (an indexed array ends up in local memory)
                 u64 b0 = ~0ull, b1 = ~0ull, b2 = ~0ull, b3 = ~0ull;
                 float best_f = CUDART_NAN_F;                   // NaN: nothing is rejected until 4 keys are held
-                for (int c = 0; c < 128; c += 32) {
+                for (int c = 0; c < 128 && cbase + c < rows_here; c += 32) {
                     uint32_t v[32];
                     tc_ld_32x32(taddr + (uint32_t)c, v);
                     tc_ld_wait();
@@ -436,7 +438,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // Lists hold raw (fp32 score bits, row) pairs: the ordered image is only built when a list is read
             // (prune, select), so an append is a predicate, one store and one add.  With ~4 % of the scores
             // passing per lane, some lane of the warp passes most of the time, so this path must stay short.
-            for (int c = 0; c < 128; c += 32) {
+            for (int c = 0; c < 128 && cbase + c < rows_here; c += 32) {   // chunks past the tile's rows hold nothing
                 uint32_t v[32];
                 tc_ld_32x32(taddr + (uint32_t)c, v);
                 tc_ld_wait();
@@ -483,7 +485,8 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32
 struct GemmPlan {
     bool valid = false;
     CUtensorMap tmB;           // box = 256 / tmB_cluster rows
-    int tmB_cluster = 0;
+    int tmB_cluster = 0, tmB_bn = 0;
+    bool balance_tiles = false; // option "gemm_balance" (measured: no gain -- at Q = 256 the tensor pipe is a co-bottleneck and shorter tiles waste MMA columns)
     int cluster_opt = 0;       // option "gemm_cluster": 0 = automatic, else force 1 / 2 / 4
     const float *rows = nullptr;
     int64_t n_rows = 0, ld = 0;
@@ -551,7 +554,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     int rc = gemm_encode_2d(p, &tmA, queries, nq, dim, dim, MTsel * G_BM);
     if (rc) return rc;
     const int nqb = (nq + MTsel * G_BM - 1) / (MTsel * G_BM);
-    const int n_tiles = (int)((n_rows + G_BN - 1) / G_BN);
+    int n_tiles = (int)((n_rows + G_BN - 1) / G_BN);
     int ngroups = std::max(1, std::min(n_sm / nqb, n_tiles));
     const int kpl = gemm_kpl_for(kprime), cap = kpl * 32;
     const void *func = gemm_kernel_ptr(MTsel, kpl, metric);
@@ -577,9 +580,19 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
         } else (void)cudaGetLastError();
         if (ngroups < 1) { C = 1; ngroups = std::max(1, std::min(n_sm / nqb, n_tiles)); }
     }
-    if (!p.valid || p.rows != rows || p.n_rows != n_rows || p.ld != ld || p.dim != dim || p.tmB_cluster != C) {
-        if ((rc = gemm_encode_2d(p, &p.tmB, rows, n_rows, dim, ld, G_BN / C))) return rc;
-        p.rows = rows; p.n_rows = n_rows; p.ld = ld; p.dim = dim; p.tmB_cluster = C; p.valid = true;
+    // Balanced tiles (option gemm_balance, off by default): shrink the tile height until every group runs the same number of
+    // rounds, BN = ceil(N / (rounds * groups)).  Measured on config 2: 155.8 vs 154.1 us -- no gain: the MMA is N = 256 either
+    // way, and at 256 queries the tensor pipe (a TF32 M128 N256 K8 MMA retires every ~171 cycles here, not 128) is as much the
+    // bound as HBM is, so shorter tiles only add tensor work.
+    const int rounds = (n_tiles + ngroups - 1) / ngroups;
+    int bn = (int)((n_rows + (int64_t)rounds * ngroups - 1) / ((int64_t)rounds * ngroups));
+    bn = std::min(G_BN, std::max(2 * C, (bn + 2 * C - 1) / (2 * C) * (2 * C)));
+    if (!p.balance_tiles) bn = G_BN;
+    n_tiles = (int)((n_rows + bn - 1) / bn);
+    ngroups = std::max(1, std::min(ngroups, n_tiles));
+    if (!p.valid || p.rows != rows || p.n_rows != n_rows || p.ld != ld || p.dim != dim || p.tmB_cluster != C || p.tmB_bn != bn) {
+        if ((rc = gemm_encode_2d(p, &p.tmB, rows, n_rows, dim, ld, bn / C))) return rc;
+        p.rows = rows; p.n_rows = n_rows; p.ld = ld; p.dim = dim; p.tmB_cluster = C; p.tmB_bn = bn; p.valid = true;
     }
     const int L = 2 * ngroups;                       // one list per (CTA, query, half tile)
     const size_t list_bytes = sizeof(u64) * (size_t)nq * L * cap;
@@ -596,7 +609,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     a.pub = reinterpret_cast<u64 *>(wsb + pub_off);
     a.arrive = reinterpret_cast<unsigned int *>(wsb + arr_off);
     a.dump = dump;
-    a.rows = rows; a.ld = ld; a.l2_prefetch = p.l2_prefetch ? 1 : 0; a.debug = p.debug; a.cluster = C;
+    a.rows = rows; a.ld = ld; a.l2_prefetch = p.l2_prefetch ? 1 : 0; a.debug = p.debug; a.cluster = C; a.bn = bn;
     // bootstrap needs every CTA of a query block resident at once: cooperative launch, grid <= #SMs (1 CTA / SM)
     int boot_lists = std::min(L, 32) & ~1;                       // even: both halves of a CTA
     const int m = boot_lists ? (kprime + boot_lists - 1) / boot_lists : G_BOOT_MAX + 1;

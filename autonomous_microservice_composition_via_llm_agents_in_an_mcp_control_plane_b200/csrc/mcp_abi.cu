@@ -321,6 +321,8 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
     } else if (!strcmp(name, "max_fallback")) {
         if (value < 1 || value > 64) return fail(MCP_EINVAL, "max_fallback %lld outside [1, 64]", (long long)value);
         idx->opt_max_fallback = (int)value;
+    } else if (!strcmp(name, "gemm_balance")) {
+        idx->gemm.balance_tiles = value != 0;
     } else if (!strcmp(name, "gemm_cluster")) {
         if (value != 0 && value != 1 && value != 2 && value != 4) return fail(MCP_EINVAL, "gemm_cluster must be 0, 1, 2 or 4");
         idx->gemm.cluster_opt = (int)value;
@@ -417,19 +419,28 @@ static int run_scan_pass(mcp_index *idx, cudaStream_t st, const float *q, int di
     int grid = (int)std::min<int64_t>((int64_t)idx->n_sm * per_sm, want);
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     const float *inv_ne = idx->inv_norm.as<float>();
-    bool nj12 = dim == 1536;
+    // rows of 512 / 768 / 1024 / 1536 / 2048 / 3072 floats get all their loads issued up front (NJ float4 per lane);
+    // any other dim % 4 == 0 takes the generic loop (4 loads in flight per lane)
+    const int nj = (dim % 128 == 0) ? dim / 128 : 0;
     cudaError_t e;
-#define SCAN_CASE(QT)                                                                                               \
-    e = nj12 ? launch_scan<QT, 12>(idx->metric, grid, smem, st, idx->d_rows, idx->n_rows, dim, idx->ld, q, inv_nq, \
-                                   inv_ne, pen, scores, stride, nvalid)                                             \
-             : launch_scan<QT, 0>(idx->metric, grid, smem, st, idx->d_rows, idx->n_rows, dim, idx->ld, q, inv_nq, \
-                                  inv_ne, pen, scores, stride, nvalid)
+#define SCAN_ARGS idx->metric, grid, smem, st, idx->d_rows, idx->n_rows, dim, idx->ld, q, inv_nq, inv_ne, pen, scores, stride, nvalid
+#define SCAN_CASE(QT)                                                     \
+    switch (nj) {                                                         \
+        case 4:  e = launch_scan<QT, 4>(SCAN_ARGS); break;                \
+        case 6:  e = launch_scan<QT, 6>(SCAN_ARGS); break;                \
+        case 8:  e = launch_scan<QT, 8>(SCAN_ARGS); break;                \
+        case 12: e = launch_scan<QT, 12>(SCAN_ARGS); break;               \
+        case 16: e = launch_scan<QT, 16>(SCAN_ARGS); break;               \
+        case 24: e = launch_scan<QT, 24>(SCAN_ARGS); break;               \
+        default: e = launch_scan<QT, 0>(SCAN_ARGS); break;                \
+    }
     switch (qt) {
         case 1: SCAN_CASE(1); break;
         case 2: SCAN_CASE(2); break;
         case 4: SCAN_CASE(4); break;
         default: SCAN_CASE(8); break;
     }
+#undef SCAN_ARGS
 #undef SCAN_CASE
     if (e != cudaSuccess) return fail(MCP_ECUDA, "scan_fp32 launch: %s", cudaGetErrorString(e));
     idx->stats.kernel_launches++;

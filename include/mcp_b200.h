@@ -148,6 +148,7 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
  * query before exact rescoring, >= k), "max_fallback" (device-side fp64 re-scans per batch),
  * "gemm_wide" (1 = K2 with 256-query CTAs above 128 queries; default 0 = 128-query CTAs, measured faster),
  * "gemm_l2_prefetch" (1 = K2 with a per-row 1 KB L2 bulk prefetch; default 0, measured slower),
+ * "gemm_balance" (1 = K2 tile height shrunk so that every CTA gets the same number of tiles; default 0 = 256-row tiles, measured equal),
  * "gemm_cluster" (CTAs per cluster that multicast the row tile to each other: 0 = automatic, or 1 / 2 / 4),
  * "gemm_debug" (bit mask for timing experiments that switch off parts of K2 -- results are WRONG; default 0),
  * "gemm_bootstrap" (0 = K2 without the cross-CTA threshold bootstrap; default 1),
