@@ -253,7 +253,13 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a GPU: the product path has no CPU fallback"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    saved_stdout = None
     if world > 1:
+        # NCCL prints its version banner (and everything NCCL_DEBUG asks for) on stdout while the communicator comes up;
+        # stdout must carry exactly one JSON line, so fd 1 points at stderr until the first collectives are through
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     wl = "config2" if (args.workload == "auto" and world == 1) or args.workload == "config2" else "config3"
@@ -283,6 +289,13 @@ def main():
         out = sh.search_device(qs, k)
     barrier()
     sh.sync_status()
+    if saved_stdout is not None:
+        t_ = torch.zeros(1, device=dev)
+        dist.all_reduce(t_)                      # every kind of collective used later has run once by now
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
     st0 = sh.local.stats()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clocks:
