@@ -328,3 +328,28 @@ def test_update_rows_and_table_file(mcp, oracle, tmp_path):
         names = idx.load_file(p)
         assert names[7] == "n7"
         _assert_parity(idx.search(qs, 4), want_ids, want_s64)
+
+
+def test_query_chunking_paths_agree(mcp, oracle):
+    """Batches larger than one launch takes: the GEMM path splits at 1024 queries, the streaming path at whatever keeps
+    its score matrix within budget.  Every chunked answer must equal the fp64 scan's (oracle-checked on a sample)."""
+    import torch
+
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(99)
+    n, d, q, k = 150_000, 512, 1300, 16
+    rows = torch.randn((n, d), generator=g, device=dev)
+    qs = torch.randn((q, d), generator=g, device=dev)
+    idx = mcp.ServiceIndex(d).adopt(rows)
+    idx.set_option("path", "exact_fp64").set_option("max_fallback", 16)
+    want_i, _, want_s = (t.clone() for t in idx.search_device(qs, k))
+    idx.sync_status()
+    for path in ("gemm_tf32", "stream_fp32"):
+        idx.set_option("path", path)
+        ids, _, s64 = idx.search_device(qs, k)
+        assert idx.sync_status()[1] == 0
+        assert torch.equal(ids, want_i) and torch.equal(s64, want_s), path
+    sample = [0, 1023, 1024, 1299]
+    oi, os64, _ = oracle.topk(rows.cpu().numpy(), qs.cpu().numpy()[sample], k, 0, None)
+    assert np.array_equal(want_i.cpu().numpy()[sample], oi) and np.array_equal(want_s.cpu().numpy()[sample], os64)
+    idx.close()
