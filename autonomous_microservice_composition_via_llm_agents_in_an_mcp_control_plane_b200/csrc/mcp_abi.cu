@@ -105,8 +105,6 @@ struct mcp_index {
     unsigned char *h_stage = nullptr;   // pinned staging for the host-buffer search: results + status in one copy
     size_t h_stage_cap = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t aux = nullptr;            // side stream: exact query norms run here, beside the coarse scan
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t done = nullptr;
     bool pending = false;
     cudaStream_t last_stream = nullptr;
@@ -137,12 +135,10 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     if (prop.major != 10) { delete idx; return fail(MCP_ECUDA, "device %d is sm_%d%d; this library holds sm_100a code only", device_id, prop.major, prop.minor); }
     CU(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&idx->done, cudaEventDisableTiming));
-    CU(cudaStreamCreateWithFlags(&idx->aux, cudaStreamNonBlocking));
-    CU(cudaEventCreateWithFlags(&idx->ev_fork, cudaEventDisableTiming));
-    CU(cudaEventCreateWithFlags(&idx->ev_join, cudaEventDisableTiming));
     CU(cudaMallocHost(&idx->h_status, 4 * sizeof(int)));
     idx->h_status[0] = idx->h_status[1] = 0;
     CU(cudaFuncSetAttribute(rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SMEM_BYTES(8192)));
+    CU(cudaFuncSetAttribute(rescore_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_BYTES(8192, RF_MAXG)));
     int rc = idx->consts.ensure(sizeof(TableConsts));
     if (!rc) rc = idx->flags.ensure(sizeof(int) * 4096);
     if (rc) { delete idx; return rc; }
@@ -164,9 +160,6 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     if (idx->h_status) cudaFreeHost(idx->h_status);
     if (idx->h_stage) cudaFreeHost(idx->h_stage);
     if (idx->done) cudaEventDestroy(idx->done);
-    if (idx->ev_fork) cudaEventDestroy(idx->ev_fork);
-    if (idx->ev_join) cudaEventDestroy(idx->ev_join);
-    if (idx->aux) cudaStreamDestroy(idx->aux);
     if (idx->stream) cudaStreamDestroy(idx->stream);
     delete idx;
     return MCP_OK;
@@ -520,33 +513,16 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     int *n_flag = idx->flags.as<int>(), *flag_list = n_flag + 8;
     if ((rc = idx->inv_nq_exact.ensure(sizeof(float) * nq))) return rc;
     if ((rc = idx->nq2f.ensure(sizeof(float) * nq))) return rc;
-    // coarse kernels only need fp32 inverse norms; the exact fp64 norms (a dim-long dependent chain per query) and
-    // the query flags are consumed by the rescoring stage, so they are computed on a side stream meanwhile
-    bool forked = false, joined = false;
-    if (path != MCP_PATH_STREAM_FP32) {
-        // the tensor-core scan wants every SM to itself (measured: co-running the exact-norm CTAs slows it by more than they
-        // take), so here the exact norms simply come first; the fork below is for the small-batch streaming path
+    // coarse kernels only need fp32 norms; the exact fp64 norm of each query is computed inside the fused rescoring
+    // kernel (as one more chain), so nothing serial sits in front of the scan
+    if (path == MCP_PATH_EXACT_FP64) {
         prep_queries_kernel<<<nq, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
             d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), idx->nq2f.as<float>());
         KL();
-        forked = joined = true;
     } else {
         prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>());
         KL();
-        CU(cudaEventRecord(idx->ev_fork, st));      // the side stream may start once the queries are in place ...
-        CU(cudaStreamWaitEvent(idx->aux, idx->ev_fork, 0));
     }
-    // ... but its kernel is enqueued right after the first coarse launch, so that the coarse kernel gets the SMs first
-    // and the small exact-norm CTAs fill in beside it
-    auto launch_exact_prep = [&]() -> int {
-        if (forked) return MCP_OK;
-        prep_queries_kernel<<<nq, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), idx->aux>>>(
-            d_q, dim, idx->nq2.as<double>(), idx->inv_nq_exact.as<float>(), idx->qflag.as<unsigned char>(), nullptr);
-        KL();
-        CU(cudaEventRecord(idx->ev_join, idx->aux));
-        forked = true;
-        return MCP_OK;
-    };
 
     idx->stats.searches++; idx->stats.queries += nq; idx->stats.last_path = path; idx->stats.last_kprime = kprime;
 
@@ -569,8 +545,6 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     if (path == MCP_PATH_STREAM_FP32)
         chunk = (int)std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(SCORE_BUDGET_BYTES / (4ull * (size_t)n))));
     const int kc = (int)std::min<int64_t>(kprime, n);
-    if ((rc = idx->exact_key.ensure(sizeof(u64) * (size_t)chunk * kprime))) return rc;
-    if ((rc = idx->exact_row.ensure(sizeof(int) * (size_t)chunk * kprime))) return rc;
 
     CertParams cp;
     cp.metric = idx->metric; cp.path = path; cp.complete = (n <= kprime);
@@ -602,7 +576,6 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
                 if ((rc = run_scan_pass(idx, st, dqs + (int64_t)p * dimp, dimp, idx->inv_nq.as<float>() + q0 + p, nv,
                                         idx->scores.as<float>() + (int64_t)p * n, n)))
                     return rc;
-                if ((rc = launch_exact_prep())) return rc;
             }
             if ((rc = coarse_event(idx, st))) return rc;
             int P = (int)((n + SEL_MAX - 1) / SEL_MAX);
@@ -621,26 +594,22 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
                                     idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap)))
                 return fail(rc, "%s", idx->gemm.err);
             idx->stats.kernel_launches++;
-            if ((rc = launch_exact_prep())) return rc;
             if ((rc = coarse_event(idx, st))) return rc;
             // the GEMM's lists live in gemm_ws; reductions ping-pong between listsA / listsB
             // K2 lists are raw (fp32 bits, row) pairs: always pass them through one reduction, which builds the ordered keys
             if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride, true)))
                 return rc;
         }
-        if ((rc = launch_exact_prep())) return rc;
-        if (!joined) { CU(cudaStreamWaitEvent(st, idx->ev_join, 0)); joined = true; }   // exact norms + flags are ready
-        rescore_kernel<<<dim3((cand_stride + RS_ROWS - 1) / RS_ROWS, cq), RESCORE_THREADS,
-                         RS_SMEM_BYTES(dim), st>>>(idx->d_rows, dim, idx->ld, dq, idx->nq2.as<double>() + q0,
-                                                    idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt,
-                                                    cand_stride, idx->exact_key.as<u64>(), idx->exact_row.as<int>());
-        KL();
-        finalize_kernel<<<cq, FINAL_THREADS, 0, st>>>(
-            idx->exact_key.as<u64>(), idx->exact_row.as<int>(), cand, cand_cnt, cand_stride,
-            pow2_at_least(std::max(std::min(cand_stride, kprime), 2)), k, idx->id_base, idx->nq2.as<double>() + q0,
-            idx->qflag.as<unsigned char>() + q0, idx->consts.as<TableConsts>(), cp, out_ids + (int64_t)q0 * k,
-            out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag);
-        KL();
+        {
+            const int G = (std::min(cand_stride, kprime) + RS_ROWS - 1) / RS_ROWS;
+            const int GP = std::max(1, cq <= idx->n_sm ? std::min(G, RF_MAXG) : std::min(G, 2));   // few queries: one pass; many: more CTAs per SM
+            rescore_finalize_kernel<<<cq, 32 * (GP + 1), RF_SMEM_BYTES(dim, GP), st>>>(
+                idx->d_rows, dim, idx->ld, dq, idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt, cand_stride,
+                pow2_at_least(std::max(std::min(cand_stride, kprime), 2)), k, idx->id_base, idx->consts.as<TableConsts>(), cp,
+                idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
+                out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag);
+            KL();
+        }
         // certificate failures: fp64 scan on the device, flag_list holds chunk-local query numbers
         if ((rc = run_exact(idx, st, dq, idx->nq2.as<double>() + q0, k, idx->opt_max_fallback, out_ids + (int64_t)q0 * k, out_scores + (int64_t)q0 * k,
                             out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, true)))
@@ -774,13 +743,9 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     if ((rc = idx->inv_nq.ensure(sizeof(float) * n_queries))) return rc;
     if ((rc = idx->qflag.ensure(n_queries))) return rc;
     if ((rc = idx->nq2f.ensure(sizeof(float) * n_queries))) return rc;
-    // the same query norms a search would feed this coarse kernel
-    if (path == MCP_PATH_STREAM_FP32)
-        prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
-                                                                     idx->nq2f.as<float>());
-    else
-        prep_queries_kernel<<<n_queries, PREPQ_THREADS, sizeof(float) * ((dim + 3) & ~3), st>>>(
-            queries_device, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), idx->nq2f.as<float>());
+    // the same query norms a search feeds its coarse kernel
+    prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
+                                                                 idx->nq2f.as<float>());
     KCHECK();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     if (path == MCP_PATH_STREAM_FP32) {

@@ -200,6 +200,174 @@ finalize_kernel(const u64 *__restrict__ exact_key, const int *__restrict__ exact
     }
 }
 
+// ---- K4 fused: exact rescoring + query norm + final sort + certificate; one CTA per query ------------------------
+// Replaces prep_queries_kernel + rescore_kernel + finalize_kernel on the search path (three launches, two global round
+// trips).  The CTA has GP candidate warps (32 candidates each; more than RF_MAXG * 32 candidates take several passes)
+// and one extra warp whose lane 0 walks the query against itself: that chain *is* the exact fp64 squared norm of the
+// query, in index order, and it is exactly as long as a candidate's chain, so it costs nothing on the critical path.
+// All threads stream the candidate rows through the cp.async ring; then the CTA sorts, writes the top k and checks
+// the certificate.  nq2 / qflag are also written out for the fp64 fallback scan that may follow.
+#define RF_MAXG 4
+#define RF_STAGES 4
+#define RF_SMEM_BYTES(dim, gp) (sizeof(double) * (((dim) + 3) & ~3) + sizeof(float) * RF_STAGES * (gp) * RS_ROWS * RS_PITCH + 16)
+
+__global__ void __launch_bounds__(32 * (RF_MAXG + 1))
+rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, const float *__restrict__ queries,
+                        const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
+                        const u64 *__restrict__ cand, const int *__restrict__ cand_cnt, int cand_stride,
+                        int npow2, int k, int64_t id_base, const TableConsts *__restrict__ consts, CertParams cp,
+                        double *__restrict__ nq2_out, unsigned char *__restrict__ qflag_out,
+                        int32_t *__restrict__ out_ids, float *__restrict__ out_scores, double *__restrict__ out_scores64,
+                        int *__restrict__ flag_list, int *__restrict__ n_flag) {
+    extern __shared__ __align__(16) unsigned char rf_raw[];
+    __shared__ u64 sk[FINAL_MAX];
+    __shared__ int sv[FINAL_MAX];
+    __shared__ int s_row[RF_MAXG * RS_ROWS];
+    __shared__ unsigned int s_tmax;
+    __shared__ int s_bad;
+    __shared__ double s_nq2;
+    const int nthreads = blockDim.x, GP = nthreads / 32 - 1;       // candidate warps per pass
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int dimp = (dim + 3) & ~3;
+    double *sq = reinterpret_cast<double *>(rf_raw);                // [dimp] the query in fp64
+    float *tile = reinterpret_cast<float *>(sq + dimp);             // [RF_STAGES][GP * RS_ROWS][RS_PITCH]
+    const int q = blockIdx.x;
+    const int cnt = min(cand_cnt[q], cand_stride);
+    const float *qv = queries + (int64_t)q * dim;
+    if (threadIdx.x == 0) { s_tmax = 0; s_bad = 0; }
+    __syncthreads();
+    {   // query -> fp64 in shared memory (loads batched), non-finite detection
+        bool bad = false;
+        float t[8];
+        for (int i0 = 0; i0 < dimp; i0 += 8 * nthreads) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { const int i = i0 + u * nthreads + threadIdx.x; t[u] = i < dim ? __ldg(qv + i) : 0.f; }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { const int i = i0 + u * nthreads + threadIdx.x; if (i < dimp) { sq[i] = (double)t[u]; bad |= !isfinite(t[u]); } }
+        }
+        if (bad) s_bad = 1;
+    }
+    unsigned int tmax = 0;
+    for (int i = threadIdx.x; i < npow2; i += nthreads) {
+        sk[i] = ~0ull; sv[i] = MCP_PAD_ROW;
+        if (i < cnt) tmax = max(tmax, (unsigned int)(cand[(int64_t)q * cand_stride + i] >> 32));
+    }
+    atomicMax(&s_tmax, tmax);
+    const int nchunks = (dimp + RS_COLS - 1) / RS_COLS;
+    const int n_groups = (cnt + RS_ROWS - 1) / RS_ROWS;
+    double nq2_acc = 0.0;                                           // lane 0 of the extra warp
+    for (int g0 = 0; g0 < max(n_groups, 1); g0 += GP) {
+        __syncthreads();                                            // previous pass has left the ring and s_row
+        if (warp < GP) {
+            const int j = (g0 + warp) * RS_ROWS + lane;
+            s_row[warp * RS_ROWS + lane] = (j < cnt) ? (int)(cand[(int64_t)q * cand_stride + j] & 0xFFFFFFFFull) : -1;
+        }
+        __syncthreads();
+        auto issue = [&](int c) {
+            if (c < nchunks) {
+                const int c0 = c * RS_COLS, w4 = min(RS_COLS, dimp - c0) >> 2;
+                float *dst = tile + (size_t)(c % RF_STAGES) * GP * RS_ROWS * RS_PITCH;
+                for (int f = threadIdx.x; f < GP * RS_ROWS * (RS_COLS / 4); f += nthreads) {
+                    const int rr = f / (RS_COLS / 4), c4 = f % (RS_COLS / 4);
+                    const int row = s_row[rr];
+                    if (row >= 0 && c4 < w4) cp_async16(dst + rr * RS_PITCH + c4 * 4, rows + (int64_t)row * ld + c0 + c4 * 4);
+                }
+            }
+            cp_async_commit();
+        };
+        for (int c = 0; c < RF_STAGES - 1; ++c) issue(c);
+        double acc = 0.0;
+        for (int c = 0; c < nchunks; ++c) {
+            cp_async_wait<RF_STAGES - 2>();
+            __syncthreads();                                        // chunk c has landed; everyone is done with chunk c-1's stage
+            issue(c + RF_STAGES - 1);
+            const int c0 = c * RS_COLS, w = min(RS_COLS, dimp - c0);
+            const double *qq = sq + c0;
+            if (warp < GP) {
+                const float *e = tile + (size_t)(c % RF_STAGES) * GP * RS_ROWS * RS_PITCH + (warp * RS_ROWS + lane) * RS_PITCH;
+                if (metric == 0) {
+#pragma unroll 4
+                    for (int i = 0; i < w; i += 4) {
+                        const float4 v = *reinterpret_cast<const float4 *>(e + i);
+                        const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
+                        acc = fma(u0.x, (double)v.x, acc); acc = fma(u0.y, (double)v.y, acc);
+                        acc = fma(u1.x, (double)v.z, acc); acc = fma(u1.y, (double)v.w, acc);
+                    }
+                } else {
+#pragma unroll 4
+                    for (int i = 0; i < w; i += 4) {
+                        const float4 v = *reinterpret_cast<const float4 *>(e + i);
+                        const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
+                        double d;
+                        d = __dsub_rn(u0.x, (double)v.x); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                        d = __dsub_rn(u0.y, (double)v.y); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                        d = __dsub_rn(u1.x, (double)v.z); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                        d = __dsub_rn(u1.y, (double)v.w); acc = __dadd_rn(acc, __dmul_rn(d, d));
+                    }
+                }
+            } else if (g0 == 0 && lane == 0) {
+                // the query against itself: sum q_i^2 in index order == the oracle's nq2 (exact products)
+#pragma unroll 4
+                for (int i = 0; i < w; i += 2) {
+                    const double2 u = *reinterpret_cast<const double2 *>(qq + i);
+                    nq2_acc = fma(u.x, u.x, nq2_acc); nq2_acc = fma(u.y, u.y, nq2_acc);
+                }
+            }
+        }
+        if (g0 == 0 && warp == GP && lane == 0) s_nq2 = nq2_acc;
+        __syncthreads();
+        if (warp < GP) {
+            const int j = (g0 + warp) * RS_ROWS + lane;
+            const int row = s_row[warp * RS_ROWS + lane];
+            if (j < npow2 && row >= 0) {
+                double sc = exact_finish(acc, metric, s_nq2, ne2[row]);
+                if (penalty) sc = sc + (double)penalty[row];
+                sk[j] = f64_ord(sc); sv[j] = row;
+            }
+        }
+    }
+    cta_bitonic_sort_pairs(sk, sv, npow2);
+    for (int i = threadIdx.x; i < k; i += nthreads) {
+        const int64_t o = (int64_t)q * k + i;
+        const bool real = (i < cnt) && sv[i] != MCP_PAD_ROW;
+        const double s = real ? ord_f64(sk[i]) : CUDART_INF;
+        out_ids[o] = real ? (int32_t)(id_base + sv[i]) : -1;
+        out_scores[o] = (float)s;
+        if (out_scores64) out_scores64[o] = s;
+    }
+    if (threadIdx.x == 0) {
+        const double nq2 = s_nq2;
+        const bool odd = (nq2 != 0.0) && (nq2 < 1e-30 || nq2 > 1e30);
+        const unsigned char flag = (unsigned char)((s_bad ? 2 : 0) | ((odd || nq2 == 0.0 || s_bad) ? 1 : 0));
+        nq2_out[q] = nq2;
+        qflag_out[q] = flag;
+        bool pass;
+        if (flag) pass = false;                              // degenerate query: always the fp64 scan
+        else if (cp.complete) pass = true;
+        else if (s_tmax == 0xFFFFFFFFu) pass = true;         // worst survivor is NaN: every dropped row is NaN with a larger id
+        else if (cnt < k) pass = false;                      // cannot happen when !complete; be safe
+        else {
+            const double T = (double)ord_f32(s_tmax);
+            const double sk_k = ord_f64(sk[k - 1]);          // NaN if fewer than k numeric scores
+            const double qn = sqrt(nq2);
+            const double en = sqrt(__longlong_as_double((long long)consts->max_norm2_bits));
+            const double pen_abs = (double)consts->pen_absmax, pen_max = (double)consts->pen_max;
+            double eps;
+            if (cp.metric == 0) {
+                eps = cp.rel + cp.abs_pen * (2.0 + pen_abs);
+            } else if (cp.path == 2) {
+                const double delta = 2.0 * cp.rel * qn * en + 4.0 * 5.96e-8 * (qn + en) * (qn + en);
+                double x0 = T - pen_max; x0 = x0 > 0.0 ? x0 * x0 : 0.0;
+                eps = sqrt(x0) - sqrt(fmax(x0 - delta, 0.0)) + cp.abs_pen * (sqrt(x0) + pen_abs);
+            } else {
+                eps = cp.rel * (qn + en) + cp.abs_pen * ((qn + en) + pen_abs);
+            }
+            pass = (sk_k == sk_k) && (sk_k < T - eps);
+        }
+        if (!pass) flag_list[atomicAdd(n_flag, 1)] = q;
+    }
+}
+
 // ---- K4c: fp64 scan of every row for the flagged queries ---------------------------------------
 // grid (blocks, max_fallback); slot f serves query flag_list[slot0 + f]; slots past *n_flag exit.
 __global__ void __launch_bounds__(256)
