@@ -55,7 +55,8 @@ struct GemmArgs {
     float *dump;               // debug: [nq][n_rows] coarse scores instead of lists, or NULL
     // cross-CTA bootstrap of the per-query threshold (cooperative launch only; boot_m == 0 disables it)
     u64 *pub;                  // [nq][L]  each (CTA, query)'s boot_m-th smallest key of its first tile
-    unsigned int *arrive;      // [nqb]    CTAs of a query block that have published
+    unsigned int *arrive;      // [nqb]    CTAs of a query block that have published (zero when the launch starts)
+    unsigned int *arrive_next; // [G_MAX_QBLOCKS] the other slot of the pair: this launch clears it for the next one
     int boot_m, boot_lists;    // lists 0 .. boot_lists-1 publish their boot_m-th smallest key (boot_lists even)
     const float *rows;         // table base + row pitch, for the L2 row prefetch
     int64_t ld;
@@ -68,25 +69,6 @@ struct GemmArgs {
 
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(u64 *b, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(u64 *b, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(u64 *b) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(u64 *b, uint32_t parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
-}
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tm, int c0, int c1, u64 *bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
@@ -254,6 +236,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     if (warp == 0) {
         // ===== TMA producer (whole warp walks the loop, lane 0 issues) =====
+        if (blockIdx.x == 0 && lane < G_MAX_QBLOCKS && a.arrive_next) a.arrive_next[lane] = 0;
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
             asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
@@ -493,6 +476,9 @@ struct GemmPlan {
     int dim = 0;
     PFN_encodeTiled encode = nullptr;
     int coop = -1;             // device supports cooperative launch (-1 = not asked yet)
+    const void *arrive_ws = nullptr;   // workspace (pointer, capacity) whose arrive-counter pair is known to be initialised
+    size_t arrive_ws_cap = 0;
+    int arrive_slot = 0;       // which counter set the next bootstrap launch uses (it clears the other one)
     bool allow_boot = true;    // option "gemm_bootstrap"
     bool l2_prefetch = false;  // option "gemm_l2_prefetch"
     int debug = 0;             // option "gemm_debug" (timing experiments, wrong results)
@@ -595,19 +581,24 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
         p.rows = rows; p.n_rows = n_rows; p.ld = ld; p.dim = dim; p.tmB_cluster = C; p.tmB_bn = bn; p.valid = true;
     }
     const int L = 2 * ngroups;                       // one list per (CTA, query, half tile)
+    // workspace: [arrive counters, two sets][lists][list counts][published bounds].  The counters sit first so that their
+    // place does not move with the launch shape: a bootstrap launch uses one set (zero on entry) and clears the other for
+    // the launch after it, which saves a memset node per search; only a new workspace is cleared from the host.
+    const size_t hdr = 256;
+    static_assert(2 * G_MAX_QBLOCKS * sizeof(unsigned int) <= 256, "arrive counter pair");
     const size_t list_bytes = sizeof(u64) * (size_t)nq * L * cap;
-    const size_t cnt_off = (list_bytes + 255) & ~(size_t)255;
+    const size_t cnt_off = (hdr + list_bytes + 255) & ~(size_t)255;
     const size_t pub_off = (cnt_off + sizeof(int) * (size_t)nq * L + 255) & ~(size_t)255;
-    const size_t arr_off = (pub_off + sizeof(u64) * (size_t)nq * 32 + 255) & ~(size_t)255;
-    if ((rc = ws.ensure(arr_off + 256))) { snprintf(p.err, sizeof p.err, "workspace allocation failed"); return rc; }
+    const size_t end_off = (pub_off + sizeof(u64) * (size_t)nq * 32 + 255) & ~(size_t)255;
+    if ((rc = ws.ensure(end_off))) { snprintf(p.err, sizeof p.err, "workspace allocation failed"); return rc; }
     unsigned char *wsb = reinterpret_cast<unsigned char *>(ws.p);
     GemmArgs a;
     a.n_rows = n_rows; a.dim = dim; a.nq = nq; a.nqb = nqb; a.kprime = kprime; a.cap = cap;
     a.inv_nq = inv_nq; a.nq2f = nq2f; a.inv_ne = inv_ne; a.ne2 = ne2; a.penalty = penalty;
-    a.lists = reinterpret_cast<u64 *>(wsb);
+    a.lists = reinterpret_cast<u64 *>(wsb + hdr);
     a.list_cnt = reinterpret_cast<int *>(wsb + cnt_off);
     a.pub = reinterpret_cast<u64 *>(wsb + pub_off);
-    a.arrive = reinterpret_cast<unsigned int *>(wsb + arr_off);
+    a.arrive = nullptr; a.arrive_next = nullptr;
     a.dump = dump;
     a.rows = rows; a.ld = ld; a.l2_prefetch = p.l2_prefetch ? 1 : 0; a.debug = p.debug; a.cluster = C; a.bn = bn;
     // bootstrap needs every CTA of a query block resident at once: cooperative launch, grid <= #SMs (1 CTA / SM)
@@ -620,7 +611,16 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     }
     a.boot_m = (!dump && !(p.debug & 1) && p.coop == 1 && m <= G_BOOT_MAX && nqb * ngroups <= n_sm && p.allow_boot) ? m : 0;
     a.boot_lists = boot_lists;
-    if (a.boot_m) e = cudaMemsetAsync(a.arrive, 0, sizeof(unsigned int) * G_MAX_QBLOCKS, st);
+    if (a.boot_m) {
+        if (p.arrive_ws != (const void *)wsb || p.arrive_ws_cap != (size_t)ws.cap) {
+            e = cudaMemsetAsync(wsb, 0, hdr, st);
+            p.arrive_ws = wsb; p.arrive_ws_cap = (size_t)ws.cap; p.arrive_slot = 0;
+        }
+        unsigned int *pair = reinterpret_cast<unsigned int *>(wsb);
+        a.arrive = pair + p.arrive_slot * G_MAX_QBLOCKS;
+        a.arrive_next = pair + (1 - p.arrive_slot) * G_MAX_QBLOCKS;
+        p.arrive_slot ^= 1;
+    }
     int nattr = C > 1 ? 1 : 0;
     if (a.boot_m) { attrs[nattr].id = cudaLaunchAttributeCooperative; attrs[nattr].val.cooperative = 1; ++nattr; }
     cfg.numAttrs = nattr; cfg.gridDim = dim3(nqb * ngroups);

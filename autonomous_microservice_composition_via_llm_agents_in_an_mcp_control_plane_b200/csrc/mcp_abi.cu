@@ -101,7 +101,9 @@ struct mcp_index {
     // workspace
     Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, exact_key, exact_row, flags,
         exact_all, out_ids, out_scores, out_scores64, gemm_ws, q_pad, inv_nq_exact, nq2f;
-    int *h_status = nullptr;   // pinned: [0] certificate failures, [1] unresolved
+    int *h_status = nullptr;   // pinned + mapped: [0] certificate failures, [1] unresolved; written by the fallback kernel's status fold
+    int *h_status_dev = nullptr;   // the same words as the device addresses them
+    Buf slot_ticket;           // one ticket per fallback slot (zero between launches)
     unsigned char *h_stage = nullptr;   // pinned staging for the host-buffer search: results + status in one copy
     size_t h_stage_cap = 0;
     cudaStream_t stream = nullptr;
@@ -135,10 +137,11 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     if (prop.major != 10) { delete idx; return fail(MCP_ECUDA, "device %d is sm_%d%d; this library holds sm_100a code only", device_id, prop.major, prop.minor); }
     CU(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&idx->done, cudaEventDisableTiming));
-    CU(cudaMallocHost(&idx->h_status, 4 * sizeof(int)));
+    CU(cudaHostAlloc(&idx->h_status, 4 * sizeof(int), cudaHostAllocMapped));
     idx->h_status[0] = idx->h_status[1] = 0;
+    CU(cudaHostGetDevicePointer(&idx->h_status_dev, idx->h_status, 0));
     CU(cudaFuncSetAttribute(rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SMEM_BYTES(8192)));
-    CU(cudaFuncSetAttribute(rescore_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_BYTES(8192, RF_MAXG)));
+    CU(cudaFuncSetAttribute(rescore_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_LIMIT));
     int rc = idx->consts.ensure(sizeof(TableConsts));
     if (!rc) rc = idx->flags.ensure(sizeof(int) * 4096);
     if (rc) { delete idx; return rc; }
@@ -154,7 +157,7 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     Buf *bufs[] = {&idx->own_rows, &idx->norm2, &idx->inv_norm, &idx->penalty, &idx->consts, &idx->q_copy,
                    &idx->nq2, &idx->inv_nq, &idx->qflag, &idx->scores, &idx->listsA, &idx->listsB, &idx->cntA,
                    &idx->cntB, &idx->exact_key, &idx->exact_row, &idx->flags, &idx->exact_all, &idx->out_ids,
-                   &idx->out_scores, &idx->out_scores64, &idx->gemm_ws, &idx->q_pad, &idx->inv_nq_exact, &idx->nq2f};
+                   &idx->out_scores, &idx->out_scores64, &idx->gemm_ws, &idx->q_pad, &idx->inv_nq_exact, &idx->nq2f, &idx->slot_ticket};
     for (Buf *b : bufs) b->release();
     for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
     if (idx->h_status) cudaFreeHost(idx->h_status);
@@ -475,22 +478,23 @@ static int choose_path(const mcp_index *idx, int nq) {
     return (nq >= 8 && gemm_supported(idx->dim, idx->ld)) ? MCP_PATH_GEMM_TF32 : MCP_PATH_STREAM_FP32;
 }
 
-// fp64 scan + exact select for flagged slots [slot0, slot0 + slots)
+// fp64 scan + exact select for the flagged queries, slots at a time, in one launch (exact_fallback_kernel)
 static int run_exact(mcp_index *idx, cudaStream_t st, const float *d_q, const double *nq2, int k, int slots,
                      int32_t *out_ids, float *out_scores, double *out_scores64, bool fold_status) {
     int rc;
     if ((rc = idx->exact_all.ensure(sizeof(u64) * (size_t)slots * (size_t)idx->n_rows))) return rc;
+    if (sizeof(int) * (size_t)slots > idx->slot_ticket.cap) {
+        if ((rc = idx->slot_ticket.ensure(sizeof(int) * (size_t)std::max(slots, 64)))) return rc;
+        CU(cudaMemsetAsync(idx->slot_ticket.p, 0, idx->slot_ticket.cap, st));
+    }
     int *flag_list = idx->flags.as<int>() + 8, *n_flag = idx->flags.as<int>();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
-    int64_t want = (idx->n_rows + 255) / 256;
-    int gx = (int)std::min<int64_t>((int64_t)idx->n_sm * 8, want);
-    exact_scan_kernel<<<dim3(gx, slots), 256, sizeof(float) * idx->dim, st>>>(
-        idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen,
-        idx->metric, flag_list, n_flag, 0, idx->exact_all.as<u64>());
-    KL();
-    exact_select_kernel<<<slots, EXSEL_THREADS, 0, st>>>(idx->exact_all.as<u64>(), idx->n_rows, k, idx->id_base,
-                                                         flag_list, n_flag, 0, out_ids, out_scores, out_scores64,
-                                                         fold_status ? n_flag + 1 : nullptr);
+    const int64_t want = (idx->n_rows + EXSEL_THREADS - 1) / EXSEL_THREADS;
+    const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)idx->n_sm * 2, want));
+    exact_fallback_kernel<<<dim3(gx, slots), EXSEL_THREADS, sizeof(float) * idx->dim, st>>>(
+        idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag,
+        k, idx->id_base, idx->exact_all.as<u64>(), idx->slot_ticket.as<int>(), out_ids, out_scores, out_scores64,
+        fold_status ? n_flag + 1 : nullptr, fold_status ? idx->h_status_dev : nullptr);
     KL();
     return MCP_OK;
 }
@@ -520,7 +524,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), idx->nq2f.as<float>());
         KL();
     } else {
-        prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>());
+        prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), n_flag);
         KL();
     }
 
@@ -552,11 +556,13 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     if (path == MCP_PATH_STREAM_FP32) cp.rel = 2.0 * (dim / 32.0 + 32.0) * u;   // + the fp32 tree-summed query norm
     else cp.rel = 1.02 * 0.001953125 + dim * 4.0 * u;      // TF32 truncation of both operands (2^-9) + fp32 accumulation
     cp.abs_pen = 8.0 * u;
+    cp.debug = idx->gemm.debug >> 8;
 
     for (int q0 = 0; q0 < nq; q0 += chunk) {
         const int cq = std::min(chunk, nq - q0);
         const float *dq = d_q + (int64_t)q0 * dim;
         u64 *cand; int *cand_cnt; int cand_stride;
+        if (q0 > 0) { clear_flag_kernel<<<1, 1, 0, st>>>(n_flag); KL(); }   // the previous chunk's flags have been served
         if ((rc = coarse_event(idx, st))) return rc;
         if (path == MCP_PATH_STREAM_FP32) {
             // the scan reads 128-bit words: rows are padded to ld by load(); queries get the same zero padding
@@ -602,8 +608,9 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
         }
         {
             const int G = (std::min(cand_stride, kprime) + RS_ROWS - 1) / RS_ROWS;
-            const int GP = std::max(1, cq <= idx->n_sm ? std::min(G, RF_MAXG) : std::min(G, 2));   // few queries: one pass; many: more CTAs per SM
-            rescore_finalize_kernel<<<cq, 32 * (GP + 1), RF_SMEM_BYTES(dim, GP), st>>>(
+            int GP = std::max(1, cq <= idx->n_sm ? std::min(G, RF_MAXG) : std::min(G, 2));   // few queries: one pass; many: more CTAs per SM
+            while (GP > 1 && RF_SMEM_BYTES(dim, GP) > RF_SMEM_LIMIT) --GP;
+            rescore_finalize_kernel<<<cq, 32 * (GP + RF_NPROD + 1), RF_SMEM_BYTES(dim, GP), st>>>(
                 idx->d_rows, dim, idx->ld, dq, idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt, cand_stride,
                 pow2_at_least(std::max(std::min(cand_stride, kprime), 2)), k, idx->id_base, idx->consts.as<TableConsts>(), cp,
                 idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
@@ -614,7 +621,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
         if ((rc = run_exact(idx, st, dq, idx->nq2.as<double>() + q0, k, idx->opt_max_fallback, out_ids + (int64_t)q0 * k, out_scores + (int64_t)q0 * k,
                             out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, true)))
             return rc;
-        // flags[1] failures, [2] unresolved, [3] ticket: folded by exact_select_kernel's last CTA
+        // flags[1] failures, [2] unresolved, [3] ticket: folded by exact_fallback_kernel's last CTA
         idx->stats.rows_scanned += n;
         idx->stats.bytes_scanned += n * (int64_t)dim * 4;
         idx->stats.candidates_rescored += (int64_t)cq * kc;
@@ -642,7 +649,7 @@ extern "C" int mcp_index_search_device(mcp_index *idx, const float *queries_devi
     if ((rc = order_after_previous(idx, st))) return rc;
     rc = search_locked(idx, queries_device, n_queries, k, out_ids_device, out_scores_device, out_scores64_device, st);
     if (rc) return rc;
-    CU(cudaMemcpyAsync(idx->h_status, idx->flags.as<int>() + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    // the status words reach idx->h_status through the fallback kernel's fold (host-mapped memory): no copy node
     CU(cudaEventRecord(idx->done, st));
     idx->pending = true;
     return MCP_OK;
@@ -657,6 +664,7 @@ extern "C" int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_fail
         CU(cudaEventSynchronize(idx->done));
         idx->pending = false;
         fails = idx->h_status[0]; unresolved = idx->h_status[1];
+        idx->h_status[0] = idx->h_status[1] = 0;      // the device rewrites them from its own (now cleared) counters
         idx->stats.certificate_failures += fails;
         idx->stats.exact_scans += fails - unresolved;
         CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), idx->last_stream));
@@ -682,14 +690,15 @@ extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n
         idx->pending = false;
         idx->stats.certificate_failures += idx->h_status[0];
         idx->stats.exact_scans += idx->h_status[0] - idx->h_status[1];
+        CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
     }
-    CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
+    idx->h_status[0] = idx->h_status[1] = 0;      // device counters are zero here (cleared after every host-buffer search)
     idx->last_stream = st;
-    // Results and status come back in ONE device->host copy into a pinned staging buffer, after ONE synchronisation:
-    // device layout [scores64 f64 nk | ids i32 nk | scores f32 nk | status 2 x i32]
+    // Results come back in ONE device->host copy into a pinned staging buffer, after ONE synchronisation
+    // (device layout [scores64 f64 nk | ids i32 nk | scores f32 nk]); the status words arrive in host-mapped memory.
     const size_t nk = (size_t)n_queries * k;
-    const size_t off_ids = sizeof(double) * nk, off_sc = off_ids + sizeof(int32_t) * nk, off_st = off_sc + sizeof(float) * nk;
-    const size_t total = off_st + 2 * sizeof(int);
+    const size_t off_ids = sizeof(double) * nk, off_sc = off_ids + sizeof(int32_t) * nk;
+    const size_t total = off_sc + sizeof(float) * nk;
     if ((rc = idx->q_copy.ensure(sizeof(float) * (size_t)n_queries * idx->dim))) return rc;
     if ((rc = idx->out_ids.ensure(total))) return rc;                 // one buffer holds all three outputs
     if (total > idx->h_stage_cap) {
@@ -709,11 +718,11 @@ extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n
         rc = search_locked(idx, idx->q_copy.as<float>(), n_queries, k, d_ids, d_sc, d_s64, st);
         idx->opt_path = saved;
         if (rc) return rc;
-        CU(cudaMemcpyAsync(dbase + off_st, idx->flags.as<int>() + 1, 2 * sizeof(int), cudaMemcpyDeviceToDevice, st));
         CU(cudaMemcpyAsync(idx->h_stage, dbase, total, cudaMemcpyDeviceToHost, st));
         CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
         CU(cudaStreamSynchronize(st));
-        const int *hs = reinterpret_cast<const int *>(idx->h_stage + off_st);
+        const int hs[2] = {idx->h_status[0], idx->h_status[1]};
+        idx->h_status[0] = idx->h_status[1] = 0;
         if (attempt == 0) {
             idx->stats.certificate_failures += hs[0];
             idx->stats.exact_scans += hs[0] - hs[1];
@@ -745,7 +754,7 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     if ((rc = idx->nq2f.ensure(sizeof(float) * n_queries))) return rc;
     // the same query norms a search feeds its coarse kernel
     prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
-                                                                 idx->nq2f.as<float>());
+                                                                 idx->nq2f.as<float>(), nullptr);
     KCHECK();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     if (path == MCP_PATH_STREAM_FP32) {
@@ -944,7 +953,7 @@ extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float
                                                                        n_flag, 0, scores);   // writes scores[0 .. n_rows)
         KCHECK();
         exact_select_kernel<<<1, EXSEL_THREADS, 0, st>>>(scores, idx->n_rows, k, idx->id_base, flag_list, n_flag, 0,
-                                                          out_ids_device, out_scores_device, out_scores64_device, nullptr);
+                                                          out_ids_device, out_scores_device, out_scores64_device);
         KCHECK();
     }
     return MCP_OK;

@@ -109,7 +109,8 @@ prep_queries_kernel(const float *__restrict__ queries, int dim, double *__restri
 // stream while the coarse scan is under way.
 __global__ void __launch_bounds__(128)
 prep_queries_fast_kernel(const float *__restrict__ queries, int n_queries, int dim, float *__restrict__ inv_norm,
-                         float *__restrict__ norm2f) {
+                         float *__restrict__ norm2f, int *__restrict__ n_flag /* NULL, or the certificate's flag count to clear */) {
+    if (n_flag && blockIdx.x == 0 && threadIdx.x == 0) *n_flag = 0;     // first kernel of a search: nothing is flagged yet
     const int q = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (q >= n_queries) return;
     const float *src = queries + (int64_t)q * dim;

@@ -25,6 +25,7 @@ struct CertParams {
     int complete;          // candidate set == all rows: nothing was dropped
     double rel;            // relative coarse error bound of the dot product / squared distance
     double abs_pen;        // multiplier of pen_absmax for fp32 rounding of the final add
+    int debug;             // option gemm_debug >> 8 (timing experiments, wrong results): 1 no chain, 2 no gathers
 };
 
 // ---- K4a: exact rescoring ------------------------------------------------------------------------
@@ -202,16 +203,65 @@ finalize_kernel(const u64 *__restrict__ exact_key, const int *__restrict__ exact
 
 // ---- K4 fused: exact rescoring + query norm + final sort + certificate; one CTA per query ------------------------
 // Replaces prep_queries_kernel + rescore_kernel + finalize_kernel on the search path (three launches, two global round
-// trips).  The CTA has GP candidate warps (32 candidates each; more than RF_MAXG * 32 candidates take several passes)
-// and one extra warp whose lane 0 walks the query against itself: that chain *is* the exact fp64 squared norm of the
-// query, in index order, and it is exactly as long as a candidate's chain, so it costs nothing on the critical path.
-// All threads stream the candidate rows through the cp.async ring; then the CTA sorts, writes the top k and checks
-// the certificate.  nq2 / qflag are also written out for the fp64 fallback scan that may follow.
+// trips).  Warp roles (GP + 2 warps):
+//   * GP candidate warps, lane = candidate (more than GP * 32 candidates take several passes): wait for a chunk of
+//     64 columns on the stage's `full` mbarrier, walk it in index order, release the stage on `empty`.  They issue
+//     nothing but their chain -- an ncu capture of the version where all threads shared the copy loop showed that
+//     loop costing as much as the chains, and the chain (about 15 cycles per element) is the kernel's floor.
+//   * one producer warp: 16 lanes per row issue cp.async (16 bytes each, 256 contiguous bytes per row and chunk) into
+//     a ring of RF_STAGES chunk tiles and hand completion to `full` (cp.async.mbarrier.arrive).  256-byte
+//     cp.async.bulk copies were tried here and ran at about one copy per 44 cycles per SM -- 1.5x slower overall.
+//   * one warp whose lane 0 walks the query against itself: that chain *is* the exact fp64 squared norm of the
+//     query, in index order, and it is as long as a candidate's chain, so it costs nothing on the critical path.
+// Then the CTA sorts, writes the top k and checks the certificate.  nq2 / qflag are also written out for the fp64
+// fallback scan that may follow.
 #define RF_MAXG 4
-#define RF_STAGES 4
-#define RF_SMEM_BYTES(dim, gp) (sizeof(double) * (((dim) + 3) & ~3) + sizeof(float) * RF_STAGES * (gp) * RS_ROWS * RS_PITCH + 16)
+#define RF_COLS 64                    // columns per chunk: 256 contiguous bytes of a row per gather
+#define RF_PITCH (RF_COLS + 4)
+#define RF_STAGES 5
+#define RF_NPROD 2                     // producer warps (each keeps its own copies in flight)
+#define RF_DEPTH 3                     // chunks of gathers in flight behind the one being handed over
+#define RF_SMEM_BYTES(dim, gp) (sizeof(double) * (((dim) + 3) & ~3) + sizeof(float) * RF_STAGES * (gp) * RS_ROWS * RF_PITCH + 64)
+#define RF_SMEM_LIMIT (216 * 1024)    // dynamic shared memory the kernel may ask for (227 KB per CTA less its static arrays)
 
-__global__ void __launch_bounds__(32 * (RF_MAXG + 1))
+// One candidate's walk over one chunk (w columns, a multiple of 4), in index order.  The compiler left to itself puts
+// each LDS right before the conversion that needs it, and each conversion right before its FMA, so every group of four
+// columns pays the shared-memory and conversion latencies on top of the four dependent FMAs (29 cycles per column
+// measured in the kernel).  Here the loads run two groups ahead of the chain and the conversions one group ahead, in
+// registers, so the chain sees only the FMA -> FMA dependency.  The look-ahead reads up to 11 floats / doubles past
+// the chunk: still inside the CTA's shared memory (next row of the tile, the tile behind the query), never used.
+template <int METRIC>
+__device__ __forceinline__ double rf_chain(const float *__restrict__ e, const double *__restrict__ qq, int w, double acc) {
+    float4 v2 = *reinterpret_cast<const float4 *>(e + 4);
+    double2 a2 = *reinterpret_cast<const double2 *>(qq + 4), b2 = *reinterpret_cast<const double2 *>(qq + 6);
+    double2 a1 = *reinterpret_cast<const double2 *>(qq), b1 = *reinterpret_cast<const double2 *>(qq + 2);
+    double d0, d1, d2, d3;
+    { const float4 v1 = *reinterpret_cast<const float4 *>(e); d0 = (double)v1.x; d1 = (double)v1.y; d2 = (double)v1.z; d3 = (double)v1.w; }
+#pragma unroll 2
+    for (int i = 0; i < w; i += 4) {
+        const float4 v3 = *reinterpret_cast<const float4 *>(e + i + 8);
+        const double2 a3 = *reinterpret_cast<const double2 *>(qq + i + 8), b3 = *reinterpret_cast<const double2 *>(qq + i + 10);
+        double n0, n1, n2, n3;     // volatile: keeps the conversions here, a whole group ahead of their FMAs (nvcc sinks plain casts to their use)
+        asm volatile("cvt.f64.f32 %0, %1;" : "=d"(n0) : "f"(v2.x));
+        asm volatile("cvt.f64.f32 %0, %1;" : "=d"(n1) : "f"(v2.y));
+        asm volatile("cvt.f64.f32 %0, %1;" : "=d"(n2) : "f"(v2.z));
+        asm volatile("cvt.f64.f32 %0, %1;" : "=d"(n3) : "f"(v2.w));
+        if (METRIC == 0) {
+            acc = fma(a1.x, d0, acc); acc = fma(a1.y, d1, acc); acc = fma(b1.x, d2, acc); acc = fma(b1.y, d3, acc);
+        } else {
+            double t;
+            t = __dsub_rn(a1.x, d0); acc = __dadd_rn(acc, __dmul_rn(t, t));
+            t = __dsub_rn(a1.y, d1); acc = __dadd_rn(acc, __dmul_rn(t, t));
+            t = __dsub_rn(b1.x, d2); acc = __dadd_rn(acc, __dmul_rn(t, t));
+            t = __dsub_rn(b1.y, d3); acc = __dadd_rn(acc, __dmul_rn(t, t));
+        }
+        d0 = n0; d1 = n1; d2 = n2; d3 = n3;
+        a1 = a2; b1 = b2; a2 = a3; b2 = b3; v2 = v3;
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(32 * (RF_MAXG + RF_NPROD + 1))
 rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, const float *__restrict__ queries,
                         const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
                         const u64 *__restrict__ cand, const int *__restrict__ cand_cnt, int cand_stride,
@@ -223,110 +273,158 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
     __shared__ u64 sk[FINAL_MAX];
     __shared__ int sv[FINAL_MAX];
     __shared__ int s_row[RF_MAXG * RS_ROWS];
+    __shared__ const float *s_rowptr[RF_MAXG * RS_ROWS];
+    __shared__ __align__(8) u64 s_full[RF_STAGES], s_empty[RF_STAGES];
     __shared__ unsigned int s_tmax;
     __shared__ int s_bad;
     __shared__ double s_nq2;
-    const int nthreads = blockDim.x, GP = nthreads / 32 - 1;       // candidate warps per pass
+    const int nthreads = blockDim.x, GP = nthreads / 32 - RF_NPROD - 1;   // candidate warps per pass
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int dimp = (dim + 3) & ~3;
     double *sq = reinterpret_cast<double *>(rf_raw);                // [dimp] the query in fp64
-    float *tile = reinterpret_cast<float *>(sq + dimp);             // [RF_STAGES][GP * RS_ROWS][RS_PITCH]
+    float *tile = reinterpret_cast<float *>(sq + dimp);             // [RF_STAGES][GP * RS_ROWS][RF_PITCH]
+    const size_t stage_floats = (size_t)GP * RS_ROWS * RF_PITCH;
     const int q = blockIdx.x;
     const int cnt = min(cand_cnt[q], cand_stride);
     const float *qv = queries + (int64_t)q * dim;
-    if (threadIdx.x == 0) { s_tmax = 0; s_bad = 0; }
-    __syncthreads();
-    {   // query -> fp64 in shared memory (loads batched), non-finite detection
-        bool bad = false;
-        float t[8];
-        for (int i0 = 0; i0 < dimp; i0 += 8 * nthreads) {
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { const int i = i0 + u * nthreads + threadIdx.x; t[u] = i < dim ? __ldg(qv + i) : 0.f; }
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { const int i = i0 + u * nthreads + threadIdx.x; if (i < dimp) { sq[i] = (double)t[u]; bad |= !isfinite(t[u]); } }
-        }
-        if (bad) s_bad = 1;
+    if (threadIdx.x == 0) {
+        s_tmax = 0; s_bad = 0;
+        for (int s = 0; s < RF_STAGES; ++s) { mbar_init(&s_full[s], 32 * RF_NPROD); mbar_init(&s_empty[s], GP); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    unsigned int tmax = 0;
-    for (int i = threadIdx.x; i < npow2; i += nthreads) {
-        sk[i] = ~0ull; sv[i] = MCP_PAD_ROW;
-        if (i < cnt) tmax = max(tmax, (unsigned int)(cand[(int64_t)q * cand_stride + i] >> 32));
-    }
-    atomicMax(&s_tmax, tmax);
-    const int nchunks = (dimp + RS_COLS - 1) / RS_COLS;
+    const int nchunks = (dimp + RF_COLS - 1) / RF_COLS;
     const int n_groups = (cnt + RS_ROWS - 1) / RS_ROWS;
-    double nq2_acc = 0.0;                                           // lane 0 of the extra warp
-    for (int g0 = 0; g0 < max(n_groups, 1); g0 += GP) {
-        __syncthreads();                                            // previous pass has left the ring and s_row
+    auto load_rows = [&](int g0) {                                  // candidate warps: this pass's rows
         if (warp < GP) {
             const int j = (g0 + warp) * RS_ROWS + lane;
-            s_row[warp * RS_ROWS + lane] = (j < cnt) ? (int)(cand[(int64_t)q * cand_stride + j] & 0xFFFFFFFFull) : -1;
+            const int row = (j < cnt) ? (int)(cand[(int64_t)q * cand_stride + j] & 0xFFFFFFFFull) : -1;
+            s_row[warp * RS_ROWS + lane] = row;
+            s_rowptr[warp * RS_ROWS + lane] = rows + (int64_t)max(row, 0) * ld;
         }
-        __syncthreads();
-        auto issue = [&](int c) {
-            if (c < nchunks) {
-                const int c0 = c * RS_COLS, w4 = min(RS_COLS, dimp - c0) >> 2;
-                float *dst = tile + (size_t)(c % RF_STAGES) * GP * RS_ROWS * RS_PITCH;
-                for (int f = threadIdx.x; f < GP * RS_ROWS * (RS_COLS / 4); f += nthreads) {
-                    const int rr = f / (RS_COLS / 4), c4 = f % (RS_COLS / 4);
-                    const int row = s_row[rr];
-                    if (row >= 0 && c4 < w4) cp_async16(dst + rr * RS_PITCH + c4 * 4, rows + (int64_t)row * ld + c0 + c4 * 4);
+    };
+    load_rows(0);
+    __syncthreads();                                                // barriers initialised, first pass's rows known
+    const bool producer = warp >= GP && warp < GP + RF_NPROD;
+    if (!producer) {
+        // Everyone but the producer (which is already gathering rows) brings the query in: fp64 in shared memory
+        // (loads batched), non-finite detection, and the worst surviving coarse score for the certificate.
+        const int nt = nthreads - 32 * RF_NPROD, t = threadIdx.x - (warp > GP ? 32 * RF_NPROD : 0);
+        bool bad = false;
+        float f[8];
+        for (int i0 = 0; i0 < dimp; i0 += 8 * nt) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { const int i = i0 + u * nt + t; f[u] = i < dim ? __ldg(qv + i) : 0.f; }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { const int i = i0 + u * nt + t; if (i < dimp) { sq[i] = (double)f[u]; bad |= !isfinite(f[u]); } }
+        }
+        if (bad) s_bad = 1;
+        unsigned int tmax = 0;
+        for (int i = t; i < npow2; i += nt) {
+            sk[i] = ~0ull; sv[i] = MCP_PAD_ROW;
+            if (i < cnt) tmax = max(tmax, (unsigned int)(cand[(int64_t)q * cand_stride + i] >> 32));
+        }
+        atomicMax(&s_tmax, tmax);
+        asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");       // the query is complete for its readers
+    }
+    double nq2_acc = 0.0;                                           // lane 0 of the last warp
+    int it0 = 0;                                                    // chunks issued by earlier passes: the ring's phases run on
+    for (int g0 = 0; g0 < max(n_groups, 1); g0 += GP, it0 += nchunks) {
+        if (g0 > 0) {
+            __syncthreads();                                        // previous pass has left s_row
+            load_rows(g0);
+            __syncthreads();
+        }
+        double acc = 0.0, ne2_row = 0.0, pen_row = 0.0;
+        if (producer) {
+            // ---- producer: lanes 0-15 take even rows, 16-31 odd rows; lane & 15 = which 16 bytes of the 256
+            const int n_valid = max(0, min(cnt - g0 * RS_ROWS, GP * RS_ROWS));     // valid rows are a prefix of s_row
+            constexpr int LPR = RF_COLS / 4, RPI = 32 / LPR;               // lanes per row, rows per iteration
+            const int half = lane / LPR, c4 = (lane % LPR) * 4;
+            auto issue = [&](int c) {
+                if (c >= nchunks) return;
+                const int it = it0 + c, s = it % RF_STAGES, n = it / RF_STAGES;
+                const int c0 = c * RF_COLS, w = min(RF_COLS, dimp - c0);
+                if (n > 0) mbar_wait(&s_empty[s], (n - 1) & 1);
+                float *dst = tile + (size_t)s * stage_floats + c4;
+                if (c4 < w && !(cp.debug & 2)) {
+#pragma unroll 4
+                    for (int rr = half + RPI * (warp - GP); rr < n_valid; rr += RPI * RF_NPROD) cp_async16(dst + rr * RF_PITCH, s_rowptr[rr] + c0 + c4);
+                }
+                cp_async_commit();
+            };
+            // Completion is relayed by hand: cp.async.mbarrier.arrive was measured to fire only when *all* of the
+            // thread's copies (later chunks included) had landed, which serialises the ring.  wait_group has a
+            // watermark, so: keep RF_DEPTH chunks in flight, and once chunk c - RF_DEPTH is known complete every
+            // producer lane arrives on its `full` barrier (release; the candidate warps' try_wait acquires).
+            for (int c = 0; c < nchunks + RF_DEPTH; ++c) {
+                if (c < nchunks) issue(c); else cp_async_commit();
+                if (c >= RF_DEPTH) {
+                    cp_async_wait<RF_DEPTH>();
+                    mbar_arrive(&s_full[(it0 + c - RF_DEPTH) % RF_STAGES]);
                 }
             }
-            cp_async_commit();
-        };
-        for (int c = 0; c < RF_STAGES - 1; ++c) issue(c);
-        double acc = 0.0;
-        for (int c = 0; c < nchunks; ++c) {
-            cp_async_wait<RF_STAGES - 2>();
-            __syncthreads();                                        // chunk c has landed; everyone is done with chunk c-1's stage
-            issue(c + RF_STAGES - 1);
-            const int c0 = c * RS_COLS, w = min(RS_COLS, dimp - c0);
-            const double *qq = sq + c0;
-            if (warp < GP) {
-                const float *e = tile + (size_t)(c % RF_STAGES) * GP * RS_ROWS * RS_PITCH + (warp * RS_ROWS + lane) * RS_PITCH;
-                if (metric == 0) {
-#pragma unroll 4
-                    for (int i = 0; i < w; i += 4) {
-                        const float4 v = *reinterpret_cast<const float4 *>(e + i);
-                        const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
-                        acc = fma(u0.x, (double)v.x, acc); acc = fma(u0.y, (double)v.y, acc);
-                        acc = fma(u1.x, (double)v.z, acc); acc = fma(u1.y, (double)v.w, acc);
-                    }
-                } else {
-#pragma unroll 4
-                    for (int i = 0; i < w; i += 4) {
-                        const float4 v = *reinterpret_cast<const float4 *>(e + i);
-                        const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
-                        double d;
-                        d = __dsub_rn(u0.x, (double)v.x); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                        d = __dsub_rn(u0.y, (double)v.y); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                        d = __dsub_rn(u1.x, (double)v.z); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                        d = __dsub_rn(u1.y, (double)v.w); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                    }
-                }
-            } else if (g0 == 0 && lane == 0) {
+        } else if (warp == GP + RF_NPROD) {
+            if (g0 == 0 && lane == 0) {
                 // the query against itself: sum q_i^2 in index order == the oracle's nq2 (exact products)
-#pragma unroll 4
-                for (int i = 0; i < w; i += 2) {
-                    const double2 u = *reinterpret_cast<const double2 *>(qq + i);
+#pragma unroll 8
+                for (int i = 0; i < dimp; i += 2) {
+                    const double2 u = *reinterpret_cast<const double2 *>(sq + i);
                     nq2_acc = fma(u.x, u.x, nq2_acc); nq2_acc = fma(u.y, u.y, nq2_acc);
                 }
+                s_nq2 = nq2_acc;
+            }
+        } else {
+            // ---- candidate warps: lane = candidate, columns in index order
+            const int my_row = s_row[warp * RS_ROWS + lane];
+            const bool live = my_row >= 0;
+            if (live) { ne2_row = ne2[my_row]; pen_row = penalty ? (double)penalty[my_row] : 0.0; }   // in flight under the first chunk
+            for (int c = 0; c < nchunks; ++c) {
+                const int it = it0 + c, s = it % RF_STAGES, n = it / RF_STAGES;
+                mbar_wait(&s_full[s], n & 1);
+                const int c0 = c * RF_COLS, w = min(RF_COLS, dimp - c0);
+                const double *qq = sq + c0;
+                const float *e = tile + (size_t)s * stage_floats + (warp * RS_ROWS + lane) * RF_PITCH;
+                if (live && !(cp.debug & 1)) acc = (metric == 0) ? rf_chain<0>(e, qq, w, acc) : rf_chain<1>(e, qq, w, acc);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&s_empty[s]);
             }
         }
-        if (g0 == 0 && warp == GP && lane == 0) s_nq2 = nq2_acc;
         __syncthreads();
         if (warp < GP) {
             const int j = (g0 + warp) * RS_ROWS + lane;
             const int row = s_row[warp * RS_ROWS + lane];
             if (j < npow2 && row >= 0) {
-                double sc = exact_finish(acc, metric, s_nq2, ne2[row]);
-                if (penalty) sc = sc + (double)penalty[row];
+                double sc = exact_finish(acc, metric, s_nq2, ne2_row);
+                if (penalty) sc = sc + pen_row;
                 sk[j] = f64_ord(sc); sv[j] = row;
             }
         }
     }
-    cta_bitonic_sort_pairs(sk, sv, npow2);
+    if (npow2 <= 2 * 32 * 3) {
+        // small lists: rank sort (every thread counts the entries ahead of its own; no barrier per stage, where the
+        // bitonic network below takes 21 barriers for 64 entries).  Pads are identical, so the index breaks ties.
+        __syncthreads();
+        u64 mk[2]; int mv[2], rank[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int i = threadIdx.x + u * nthreads;
+            rank[u] = 0;
+            if (i < npow2) {
+                mk[u] = sk[i]; mv[u] = sv[i];
+                for (int j = 0; j < npow2; ++j) {
+                    const u64 kj = sk[j]; const int vj = sv[j];
+                    rank[u] += (kj < mk[u] || (kj == mk[u] && (vj < mv[u] || (vj == mv[u] && j < i)))) ? 1 : 0;
+                }
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+            if (threadIdx.x + u * nthreads < npow2) { sk[rank[u]] = mk[u]; sv[rank[u]] = mv[u]; }
+        __syncthreads();
+    } else {
+        cta_bitonic_sort_pairs(sk, sv, npow2);
+    }
     for (int i = threadIdx.x; i < k; i += nthreads) {
         const int64_t o = (int64_t)q * k + i;
         const bool real = (i < cnt) && sv[i] != MCP_PAD_ROW;
@@ -412,33 +510,15 @@ exact_scan_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64
 
 // ---- K4d: exact top-k of one fp64 score vector; one CTA per slot ---------------------------------
 // Radix select on the 64-bit score image (values may repeat), then rows with the boundary value
-// are taken in row order, which is the "ties -> lowest id" rule.
-__global__ void __launch_bounds__(EXSEL_THREADS)
-exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, int64_t id_base,
-                    const int *__restrict__ flag_list, int *__restrict__ n_flag, int slot0,
-                    int32_t *__restrict__ out_ids, float *__restrict__ out_scores,
-                    double *__restrict__ out_scores64, int *__restrict__ status /* NULL, or [failures, unresolved, ticket] */) {
+// are taken in row order, which is the "ties -> lowest id" rule.  Every thread of an EXSEL_THREADS-wide CTA calls it.
+__device__ __forceinline__ void exact_select_body(const u64 *E /* may have been written by other CTAs of this launch: read through L2 */, int64_t n_rows, int k, int64_t id_base, int q,
+                                                  int32_t *__restrict__ out_ids, float *__restrict__ out_scores,
+                                                  double *__restrict__ out_scores64) {
     __shared__ uint32_t hist[256];
     __shared__ int s_digit, s_cnt, s_warp_base[EXSEL_THREADS / 32 + 1], s_taken, s_nless;
     __shared__ long long s_need;
     __shared__ u64 sk[MCP_MAX_K_POW2];
     __shared__ int sv[MCP_MAX_K_POW2];
-    int f = blockIdx.x;
-    const int nf = *n_flag;
-    // the last CTA to get here folds this batch's flag count into the running status and clears it for the next batch
-    // (every CTA has read n_flag by then: the ticket is taken after the read)
-    if (status && threadIdx.x == 0) {
-        __threadfence();
-        if (atomicAdd(&status[2], 1) == (int)gridDim.x - 1) {
-            status[0] += nf;
-            status[1] += nf > (int)gridDim.x ? nf - (int)gridDim.x : 0;
-            status[2] = 0;
-            *n_flag = 0;
-        }
-    }
-    if (slot0 + f >= nf) return;
-    int q = flag_list[slot0 + f];
-    const u64 *E = exact_all + (int64_t)f * n_rows;
     int kk = (int)min((int64_t)k, n_rows);
     u64 prefix = 0, mask = 0, thr = ~0ull;
     long long need = kk;
@@ -448,7 +528,7 @@ exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, in
             for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
             __syncthreads();
             for (int64_t i = threadIdx.x; i < n_rows; i += blockDim.x) {
-                u64 key = E[i];
+                u64 key = __ldcg(E + i);
                 if ((key & mask) == prefix) atomicAdd(&hist[(uint32_t)(key >> shift) & 255u], 1u);
             }
             __syncthreads();
@@ -473,7 +553,7 @@ exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, in
     __syncthreads();
     // pass 1: everything strictly better than the boundary (or <= when the whole bin is taken)
     for (int64_t i = threadIdx.x; i < n_rows; i += blockDim.x) {
-        u64 key = E[i];
+        u64 key = __ldcg(E + i);
         if (whole_bin ? (key <= thr) : (key < thr)) {
             int p = atomicAdd(&s_nless, 1);
             sk[p] = key; sv[p] = (int)i;
@@ -486,7 +566,7 @@ exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, in
         int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
         for (int64_t c0 = 0; c0 < n_rows; c0 += blockDim.x) {
             int64_t i = c0 + threadIdx.x;
-            bool hit = (i < n_rows) && (E[i] == thr);
+            bool hit = (i < n_rows) && (__ldcg(E + i) == thr);
             unsigned int b = __ballot_sync(MCP_FULL, hit);
             if (lane == 0) s_warp_base[warp] = __popc(b);
             __syncthreads();
@@ -514,4 +594,80 @@ exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, in
         out_scores[o] = (float)s;
         if (out_scores64) out_scores64[o] = s;
     }
+}
+
+__global__ void __launch_bounds__(EXSEL_THREADS)
+exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, int64_t id_base,
+                    const int *__restrict__ flag_list, int *__restrict__ n_flag, int slot0,
+                    int32_t *__restrict__ out_ids, float *__restrict__ out_scores,
+                    double *__restrict__ out_scores64) {
+    const int f = blockIdx.x;
+    if (slot0 + f >= *n_flag) return;
+    exact_select_body(exact_all + (int64_t)f * n_rows, n_rows, k, id_base, flag_list[slot0 + f], out_ids, out_scores, out_scores64);
+}
+
+// ---- K4c + K4d in one launch: the certificate's fallback ------------------------------------------------------------
+// grid (blocks, slots) x EXSEL_THREADS.  Slot f serves query flag_list[f]; slots past *n_flag exit at once, which is
+// the common case (no certificate failed), so the search pays one empty launch here instead of two.  The CTAs of a
+// live slot scan the table in fp64, and the last of them to finish (per-slot ticket) selects the slot's top k.
+__global__ void __launch_bounds__(EXSEL_THREADS)
+exact_fallback_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64_t ld,
+                      const float *__restrict__ queries, const double *__restrict__ nq2,
+                      const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
+                      const int *__restrict__ flag_list, const int *__restrict__ n_flag, int k, int64_t id_base,
+                      u64 *__restrict__ exact_all /* [slots][n_rows] */, int *__restrict__ slot_ticket /* [slots], zero */,
+                      int32_t *__restrict__ out_ids, float *__restrict__ out_scores, double *__restrict__ out_scores64,
+                      int *__restrict__ status /* NULL, or [failures, unresolved] */, volatile int *host_status) {
+    extern __shared__ float sqv[];
+    __shared__ int s_last;
+    const int f = blockIdx.y;
+    const int nf = *n_flag;
+    if (status && blockIdx.x == 0 && f == 0 && threadIdx.x == 0) {
+        // one thread folds this batch's flag count into the running status and mirrors it into host-mapped memory, so
+        // the host needs no copy node to read it.  The count itself is left alone (other CTAs may not have read it
+        // yet): the first kernel of the next search, or clear_flag_kernel between query chunks, clears it.
+        status[0] += nf;
+        status[1] += nf > (int)gridDim.y ? nf - (int)gridDim.y : 0;
+        if (host_status) { host_status[0] = status[0]; host_status[1] = status[1]; __threadfence_system(); }
+    }
+    if (f >= nf) return;
+    const int q = flag_list[f];
+    const float *qv = queries + (int64_t)q * dim;
+    for (int i = threadIdx.x; i < dim; i += blockDim.x) sqv[i] = qv[i];
+    __syncthreads();
+    const double qn2 = nq2[q];
+    u64 *out = exact_all + (int64_t)f * n_rows;
+    const int d4 = dim & ~3;
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+        const float *e = rows + r * ld;
+        ExactAcc a; a.acc = 0.0;
+        if (metric == 0) {
+            for (int i = 0; i < d4; i += 4) {
+                float4 v = *reinterpret_cast<const float4 *>(e + i);
+                a.cos_step(sqv[i], v.x); a.cos_step(sqv[i + 1], v.y);
+                a.cos_step(sqv[i + 2], v.z); a.cos_step(sqv[i + 3], v.w);
+            }
+            for (int i = d4; i < dim; ++i) a.cos_step(sqv[i], e[i]);
+        } else {
+            for (int i = 0; i < d4; i += 4) {
+                float4 v = *reinterpret_cast<const float4 *>(e + i);
+                a.l2_step(sqv[i], v.x); a.l2_step(sqv[i + 1], v.y);
+                a.l2_step(sqv[i + 2], v.z); a.l2_step(sqv[i + 3], v.w);
+            }
+            for (int i = d4; i < dim; ++i) a.l2_step(sqv[i], e[i]);
+        }
+        double s = exact_finish(a.acc, metric, qn2, ne2[r]);
+        if (penalty) s = s + (double)penalty[r];
+        __stcg(out + r, f64_ord(s));                 // read back by another CTA: keep it out of this SM's L1
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_last = atomicAdd(&slot_ticket[f], 1) == (int)gridDim.x - 1;
+        if (s_last) slot_ticket[f] = 0;              // ready for the next launch
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    exact_select_body(out, n_rows, k, id_base, q, out_ids, out_scores, out_scores64);
 }
