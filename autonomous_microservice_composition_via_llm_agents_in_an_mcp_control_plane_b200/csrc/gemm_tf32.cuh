@@ -57,12 +57,16 @@ struct GemmArgs {
     u64 *pub;                  // [nq][L]  each (CTA, query)'s boot_m-th smallest key of its first tile
     unsigned int *arrive;      // [nqb]    CTAs of a query block that have published (zero when the launch starts)
     unsigned int *arrive_next; // [G_MAX_QBLOCKS] the other slot of the pair: this launch clears it for the next one
+    unsigned int *drop_min;    // [nq] ordered image of the best coarse score the bootstrap tile may have dropped (all-ones: none); never NULL when boot_m > 0
+    int boot_early;            // the bootstrap tile hands its accumulator back before the wait (large tables only, see gemm_tf32_run)
     int boot_m, boot_lists;    // lists 0 .. boot_lists-1 publish their boot_m-th smallest key (boot_lists even)
     const float *rows;         // table base + row pitch, for the L2 row prefetch
     int64_t ld;
     int l2_prefetch;
     int bn;                    // rows per tile (<= 256, a multiple of the cluster size): chosen so that every CTA gets the same number of tiles
     int cluster;               // CTAs per cluster (1, 2 or 4): the query-block CTAs that share a row tile load a slice each and multicast it
+    uint32_t idesc_pair;       // pair mode: instruction descriptor with N = bn
+    int pair;                  // cluster == 2 only: the two CTAs run ONE tcgen05.mma.cta_group::2 (M = 256) instead of two multicast-fed M = 128 MMAs
     int debug;                 // timing experiments only (results are wrong): 1 skip epilogue math, 2 skip row-tile loads, 4 skip query-tile loads, 8 skip MMAs
 };
 #define G_BOOT_MAX 4
@@ -92,6 +96,32 @@ __device__ __forceinline__ void tc_commit(u64 *bar) {
 __device__ __forceinline__ void tc_commit_mc(u64 *bar, uint16_t mask) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                  ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+// ---- CTA pair (cta_group::2) ----
+// a load issued by either CTA of the pair into its own shared memory, its bytes counted on the LEADER's (even rank) mbarrier:
+// clearing bit 24 of a shared::cluster address names the same offset in the even CTA (cute: Sm100MmaPeerBitMask)
+__device__ __forceinline__ void tma_load_2d_pair(void *dst, const CUtensorMap *tm, int c0, int c1, u64 *bar) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(tm), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(u64 *bar) {     // same offset in both CTAs, once the pair's MMAs so far retire
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32_pair(uint32_t d_tmem, u64 adesc, u64 bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive on the mbarrier at this offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(u64 *bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+        ::"r"(smem_u32(bar)), "r"(rank) : "memory");
 }
 // D[tmem] (+)= A[smem desc] * B[smem desc], kind::tf32, issued by one thread
 __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, u64 adesc, u64 bdesc, uint32_t idesc, uint32_t accumulate) {
@@ -182,29 +212,31 @@ __device__ __forceinline__ u64 warp_prune_list(u64 *lp, int n, int kprime, int l
 //           tile is fetched once for 256 queries, which cuts shared-memory fill traffic per output by a third
 //           (6144 B x (1/256 + 1/256) instead of (1/128 + 1/256)); 64 KB per stage, 3 stages.  K2 is bound by
 //           L2 -> SM fill bandwidth (profiles/), so this is the better trade whenever there are >= 256 queries.
-template <int MT> struct GemmCfg {
-    static constexpr int STAGES = MT == 1 ? 4 : 3;
+template <int MT, int PAIR = 0> struct GemmCfg {
+    static constexpr int B_ROWS = PAIR ? G_BN / 2 : G_BN;      // rows of the tile this CTA's shared memory holds
+    static constexpr int STAGES = PAIR ? 6 : (MT == 1 ? 4 : 3);   // pair: 32 KB per stage, 6 stages = 5 k-blocks (~1.8 us of MMA time) in flight
     static constexpr int NBUF = MT == 1 ? 2 : 1;
     static constexpr int A_BYTES = MT * G_BM * G_BK * 4;
     static constexpr int EPI_THREADS = 256 * MT;
     static constexpr int THREADS = 64 + EPI_THREADS;
 };
-template <int MT> struct GemmSmemT {
-    float a[GemmCfg<MT>::STAGES][MT * G_BM * G_BK];
-    float b[GemmCfg<MT>::STAGES][G_BN * G_BK];
+template <int MT, int PAIR = 0> struct GemmSmemT {
+    float a[GemmCfg<MT, PAIR>::STAGES][MT * G_BM * G_BK];
+    float b[GemmCfg<MT, PAIR>::STAGES][GemmCfg<MT, PAIR>::B_ROWS * G_BK];
     float2 meta[2][G_BN];      // per row of the tile: (inv|e| or |e|^2, penalty)
-    u64 full[GemmCfg<MT>::STAGES], empty[GemmCfg<MT>::STAGES], tfull[2], tempty[2];
+    u64 full[GemmCfg<MT, PAIR>::STAGES], empty[GemmCfg<MT, PAIR>::STAGES], tfull[2], tempty[2];
     uint32_t tmem_base;
 };
 
-template <int MT, int KPL, int METRIC>
+template <int MT, int KPL, int METRIC, int PAIR>
 __global__ void __launch_bounds__(GemmCfg<MT>::THREADS, 1)
 gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs a) {
-    using Cfg = GemmCfg<MT>;
+    using Cfg = GemmCfg<MT, (MT == 1 && PAIR) ? 1 : 0>;
+    using Smem = GemmSmemT<MT, (MT == 1 && PAIR) ? 1 : 0>;
     extern __shared__ unsigned char g_smem_raw[];
     // 1024-byte alignment for the 128-byte swizzle; plain pointer arithmetic on the __shared__ array keeps the
     // accesses in the shared address space (a uintptr_t round trip turns them into generic loads)
-    GemmSmemT<MT> &s = *reinterpret_cast<GemmSmemT<MT> *>(g_smem_raw + ((1024u - (smem_u32(g_smem_raw) & 1023u)) & 1023u));
+    Smem &s = *reinterpret_cast<Smem *>(g_smem_raw + ((1024u - (smem_u32(g_smem_raw) & 1023u)) & 1023u));
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qb = blockIdx.x % a.nqb, group = blockIdx.x / a.nqb, ngroups = gridDim.x / a.nqb;
     const int BN = a.bn;                                       // rows per tile; the MMA is always N = 256, columns >= BN are ignored
@@ -216,17 +248,32 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // Cluster of C query-block CTAs that work on the same row tiles: each loads 256 / C rows of the tile and multicasts
     // them to all C, so the tile leaves L2 once per cluster instead of once per CTA (and the CTAs cannot drift apart,
     // which used to turn L2 hits into DRAM re-reads).  A stage slot is refilled only when all C consumers released it.
+    //
+    // Pair mode (a.pair, C == 2, MT == 1): the two CTAs are one tcgen05 CTA pair.  Each loads its own 128 queries (A) and
+    // HALF of the row tile (B), the leader (even rank) issues tcgen05.mma.cta_group::2 with M = 256: its tensor core
+    // and the peer's each produce their own 128 x 256 accumulator, reading B half from either shared memory.  Per SM that
+    // is 32 KB of TMA fill and 32 KB of operand reads per k-block instead of 48 + 48 -- the multicast variant saves L2
+    // traffic but not shared-memory bandwidth, which is what held the M = 128 kernel at 0.70 of the TF32 peak.
     const int C = a.cluster;
     const uint32_t crank = C > 1 ? cluster_ctarank() : 0u;
     const uint16_t cmask = (uint16_t)((1u << C) - 1u);
+    constexpr bool pair = MT == 1 && PAIR != 0;     // compile time: a kernel that holds cta_group::2 code can only be launched in clusters
+    const bool leader = !pair || crank == 0;
     if (threadIdx.x == 0) {
-        for (int i = 0; i < Cfg::STAGES; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], (uint32_t)C); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull[i], 1); mbar_init(&s.tempty[i], Cfg::EPI_THREADS); }
+        // pair: `full` and `tempty` live in the leader only (the peer's loads and epilogue arrive there); `empty` and
+        // `tfull` get one multicast commit each from the leader's MMA thread
+        for (int i = 0; i < Cfg::STAGES; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], pair ? 1u : (uint32_t)C); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&s.tfull[i], 1); mbar_init(&s.tempty[i], Cfg::EPI_THREADS * (pair ? 2 : 1)); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "r"(512u) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if constexpr (pair) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "r"(512u) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)), "r"(512u) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -267,6 +314,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 mbar_wait(&s.empty[stage], phase ^ 1u);
                 if (lane == 0) {
                     const bool la = !(a.debug & 4) || (i == 0 && kb < Cfg::STAGES), lb = !(a.debug & 2) || (i == 0 && kb < Cfg::STAGES);
+                    if constexpr (pair) {
+                        // both halves of the pair report to the leader's barrier, which expects the bytes of both
+                        if (leader) mbar_expect_tx(&s.full[stage], 2 * ((la ? Cfg::A_BYTES : 0) + (lb ? (BN / 2) * G_BK * 4 : 0)));
+                        if (la) tma_load_2d_pair(s.a[stage], &tmA, kb * G_BK, qb * G_BM, &s.full[stage]);
+                        if (lb) tma_load_2d_pair(s.b[stage], &tmB, kb * G_BK, t * BN + (int)crank * (BN / 2), &s.full[stage]);
+                    } else {
                     mbar_expect_tx(&s.full[stage], (la ? Cfg::A_BYTES : 0) + (lb ? BN * G_BK * 4 : 0));
                     if (la) tma_load_2d(s.a[stage], &tmA, kb * G_BK, qb * MT * G_BM, &s.full[stage]);
                     if (lb) {
@@ -277,6 +330,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                            &s.full[stage], cmask);
                         }
                     }
+                    }
                 }
                 __syncwarp();
                 if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
@@ -286,10 +340,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ===== MMA issuer =====
         int stage = 0;
         uint32_t phase = 0;
-        for (int i = 0; i < my_tiles; ++i) {
+        for (int i = 0; i < (leader ? my_tiles : 0); ++i) {   // pair: the leader's thread drives both tensor cores
             const int buf = i % Cfg::NBUF;
             const uint32_t tphase = (uint32_t)(i / Cfg::NBUF) & 1u;
-            mbar_wait(&s.tempty[buf], tphase ^ 1u);           // epilogue has drained this accumulator
+            mbar_wait(&s.tempty[buf], tphase ^ 1u);           // epilogue has drained this accumulator (pair: both epilogues)
             tc_fence_after();
             const uint32_t d_tmem = tmem + (uint32_t)(buf * G_BN);
             for (int kb = 0; kb < KB; ++kb) {
@@ -300,13 +354,17 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                     for (int k = 0; k < G_BK / 8; ++k) {      // +32 bytes along K inside the swizzle atom = +2 in the address field
 #pragma unroll
-                        for (int mt = 0; mt < MT; ++mt)       // query block mt: A rows 128*mt.. (16 KB further), accumulator columns 256*mt..
-                            if (!(a.debug & 8) || k == 0) tc_mma_tf32(d_tmem + (uint32_t)(mt * G_BN), ad + (u64)(2 * k) + (u64)(mt * (G_A_BYTES >> 4)),
-                                        bd + (u64)(2 * k), G_IDESC, (uint32_t)((kb | k) != 0));
+                        for (int mt = 0; mt < MT; ++mt) {     // query block mt: A rows 128*mt.. (16 KB further), accumulator columns 256*mt..
+                            if ((a.debug & 8) && k != 0) continue;
+                            if constexpr (pair) tc_mma_tf32_pair(d_tmem, ad + (u64)(2 * k), bd + (u64)(2 * k), a.idesc_pair, (uint32_t)((kb | k) != 0));
+                            else tc_mma_tf32(d_tmem + (uint32_t)(mt * G_BN), ad + (u64)(2 * k) + (u64)(mt * (G_A_BYTES >> 4)),
+                                             bd + (u64)(2 * k), G_IDESC, (uint32_t)((kb | k) != 0));
+                        }
                     }
-                    if (C == 1) tc_commit(&s.empty[stage]);   // frees the smem stage when these MMAs retire
+                    if constexpr (pair) tc_commit_pair(&s.empty[stage]); // frees the stage in both CTAs
+                    else if (C == 1) tc_commit(&s.empty[stage]);   // frees the smem stage when these MMAs retire
                     else tc_commit_mc(&s.empty[stage], cmask); // ... in every CTA of the cluster: their producers write my copy too
-                    if (kb == KB - 1) tc_commit(&s.tfull[buf]);
+                    if (kb == KB - 1) { if constexpr (pair) tc_commit_pair(&s.tfull[buf]); else tc_commit(&s.tfull[buf]); }
                 }
                 __syncwarp();
                 if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
@@ -327,6 +385,11 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         u64 *mylist = a.lists + ((int64_t)(qvalid ? qg : 0) * L + li) * CAP;
         int cnt = 0;
         float tau_f = qvalid ? CUDART_INF_F : -CUDART_INF_F;   // float image of tau: the common-case reject is one FSETP
+        // hands accumulator `buf` back to the MMA thread; in pair mode that thread lives in the leader CTA
+        auto release_acc = [&](int buf) {
+            if constexpr (pair) { if (leader) mbar_arrive(&s.tempty[buf]); else mbar_arrive_remote(&s.tempty[buf], 0u); }
+            else mbar_arrive(&s.tempty[buf]);
+        };
         auto score = [&](float acc, float2 mm) -> float {
             if (METRIC == 0) return fmaf(-(acc * inq), mm.x, 1.0f) + mm.y;
             return sqrtf(fmaxf(nq2f + mm.x - 2.0f * acc, 0.f)) + mm.y;
@@ -352,7 +415,19 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * G_BN + mt * G_BN + half * 128);
             const int cbase = half * 128;
-            if (a.debug & 1) { tc_fence_before(); mbar_arrive(&s.tempty[buf]); continue; }
+            if (a.debug & 1) { tc_fence_before(); release_acc(buf); continue; }
+            if (a.debug & 32) {                                // timing experiment: read the accumulator, score nothing
+                uint32_t x = 0;
+                for (int c = 0; c < 128 && cbase + c < rows_here; c += 32) {
+                    uint32_t v[32];
+                    tc_ld_32x32(taddr + (uint32_t)c, v);
+                    tc_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) x ^= v[j];
+                }
+                if (x == 0x12345u) cnt++;
+                tc_fence_before(); release_acc(buf); continue;
+            }
             if (a.dump) {
                 for (int c = 0; c < 128 && cbase + c < rows_here; c += 32) {
                     uint32_t v[32];
@@ -366,7 +441,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     }
                 }
                 tc_fence_before();
-                mbar_arrive(&s.tempty[buf]);
+                release_acc(buf);
                 continue;
             }
             if (i == 0 && a.boot_m > 0) {
@@ -394,6 +469,10 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         }
                     }
                 }
+                // The accumulator is handed back right here: what this thread may still need from the tile is in b0..b3.
+                // (Holding it through the publish / wait below kept the MMA thread out of this buffer for longer than
+                // the MMAs of the next tile take -- a measured 14 K-cycle stall, 7 % of the kernel.)
+                if (a.boot_early) { tc_fence_before(); release_acc(buf); }
                 const u64 mine = a.boot_m == 1 ? b0 : a.boot_m == 2 ? b1 : a.boot_m == 3 ? b2 : b3;
                 // only the first boot_lists lists (CTAs with group < boot_lists/2) publish and are waited for:
                 // boot_lists * boot_m >= k' keys below the maximum is all the bound needs, and fewer lists -> lower maximum
@@ -416,6 +495,18 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     }
                     tau_f = t0 == ~0ull ? CUDART_INF_F : ord_f32((uint32_t)(t0 >> 32));   // scores up to and including the bound pass
                 }
+                if (a.boot_early && qvalid) {
+                    // This tile's rows at or below the bound, straight from the registers.  Four are held; if even
+                    // the fourth passes, rows behind it (key > b3, so score >= its score) may have passed too and are
+                    // gone: their best possible score goes to drop_min, which the certificate takes into its threshold
+                    // (rescore_finalize_kernel), so a dropped row that mattered sends the query to the fp64 scan.
+                    const u64 bb[4] = {b0, b1, b2, b3};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (bb[u] != ~0ull && !(ord_f32((uint32_t)(bb[u] >> 32)) > tau_f)) mylist[cnt++] = key_to_raw(bb[u]);
+                    if (b3 != ~0ull && !(ord_f32((uint32_t)(b3 >> 32)) > tau_f)) atomicMin(&a.drop_min[qg], (uint32_t)(b3 >> 32));
+                }
+                if (a.boot_early) continue;                    // otherwise: the filter pass below re-reads the tile
             }
             // ---- filter pass ----
             // Lists hold raw (fp32 score bits, row) pairs: the ordered image is only built when a list is read
@@ -447,7 +538,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
             }
             tc_fence_before();
-            mbar_arrive(&s.tempty[buf]);
+            release_acc(buf);
         }
         if (qvalid && !a.dump) a.list_cnt[(int64_t)qg * L + li] = cnt;
     }
@@ -456,7 +547,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (C > 1) cluster_sync_all();                             // nobody leaves while a peer may still write its smem / barriers
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+        if constexpr (pair) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
     }
 }
 
@@ -471,6 +563,7 @@ struct GemmPlan {
     int tmB_cluster = 0, tmB_bn = 0;
     bool balance_tiles = false; // option "gemm_balance" (measured: no gain -- at Q = 256 the tensor pipe is a co-bottleneck and shorter tiles waste MMA columns)
     int cluster_opt = 0;       // option "gemm_cluster": 0 = automatic, else force 1 / 2 / 4
+    bool allow_pair = true;    // option "gemm_pair": clusters of 2 run as one tcgen05 CTA pair (cta_group::2)
     const float *rows = nullptr;
     int64_t n_rows = 0, ld = 0;
     int dim = 0;
@@ -517,10 +610,11 @@ static int gemm_encode_2d(GemmPlan &p, CUtensorMap *tm, const float *base, int64
 static inline int gemm_kpl_for(int kprime) { return kprime <= 64 ? 4 : kprime <= 128 ? 8 : 16; }
 static inline int gemm_max_kprime() { return 256; }
 
-static const void *gemm_kernel_ptr(int mt, int kpl, int metric) {
-#define G_PICK(MTV, KPL) (metric == 0 ? (const void *)gemm_tf32_kernel<MTV, KPL, 0> : (const void *)gemm_tf32_kernel<MTV, KPL, 1>)
-    if (mt == 2) return kpl == 4 ? G_PICK(2, 4) : kpl == 8 ? G_PICK(2, 8) : G_PICK(2, 16);
-    return kpl == 4 ? G_PICK(1, 4) : kpl == 8 ? G_PICK(1, 8) : G_PICK(1, 16);
+static const void *gemm_kernel_ptr(int mt, int kpl, int metric, bool pair) {
+#define G_PICK(MTV, KPL, PR) (metric == 0 ? (const void *)gemm_tf32_kernel<MTV, KPL, 0, PR> : (const void *)gemm_tf32_kernel<MTV, KPL, 1, PR>)
+    if (mt == 2) return kpl == 4 ? G_PICK(2, 4, 0) : kpl == 8 ? G_PICK(2, 8, 0) : G_PICK(2, 16, 0);
+    if (pair) return kpl == 4 ? G_PICK(1, 4, 1) : kpl == 8 ? G_PICK(1, 8, 1) : G_PICK(1, 16, 1);
+    return kpl == 4 ? G_PICK(1, 4, 0) : kpl == 8 ? G_PICK(1, 8, 0) : G_PICK(1, 16, 0);
 #undef G_PICK
 }
 
@@ -530,7 +624,8 @@ template <class BufT>
 static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const float *rows, int64_t n_rows, int dim,
                          int64_t ld, const float *queries, int nq, const float *inv_nq, const float *nq2f,
                          const float *inv_ne, const double *ne2, const float *penalty, int metric, int kprime,
-                         u64 **out_lists, int **out_cnt, int *out_L, int *out_cap, float *dump = nullptr) {
+                         u64 **out_lists, int **out_cnt, int *out_L, int *out_cap, float *dump = nullptr,
+                         unsigned int *drop_min = nullptr /* [nq], all-ones on entry: enables the cross-CTA bootstrap */) {
     if (!gemm_supported(dim, ld)) { snprintf(p.err, sizeof p.err, "gemm_tf32 needs dim %% 4 == 0 (dim %d, ld %lld)", dim, (long long)ld); return -1; }
     if (kprime > gemm_max_kprime()) { snprintf(p.err, sizeof p.err, "gemm_tf32 keeps at most %d candidates (asked %d)", gemm_max_kprime(), kprime); return -1; }
     if (nq > G_MAX_QBLOCKS * G_BM) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch takes at most %d queries", G_MAX_QBLOCKS * G_BM); return -1; }
@@ -543,15 +638,19 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     int n_tiles = (int)((n_rows + G_BN - 1) / G_BN);
     int ngroups = std::max(1, std::min(n_sm / nqb, n_tiles));
     const int kpl = gemm_kpl_for(kprime), cap = kpl * 32;
-    const void *func = gemm_kernel_ptr(MTsel, kpl, metric);
-    const size_t smem = (MTsel == 2 ? sizeof(GemmSmemT<2>) : sizeof(GemmSmemT<1>)) + 1024;
+    size_t smem = (MTsel == 2 ? sizeof(GemmSmemT<2>) : sizeof(GemmSmemT<1>)) + 1024;
     const int threads = MTsel == 2 ? GemmCfg<2>::THREADS : GemmCfg<1>::THREADS;
-    cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) { snprintf(p.err, sizeof p.err, "gemm_tf32 smem attribute: %s", cudaGetErrorString(e)); return -2; }
+    cudaError_t e = cudaSuccess;
     // cluster size: pairs of query-block CTAs share (multicast) their row tiles.  Measured on config 3's per-GPU share:
     // C = 1 7.37 ms, C = 2 6.78 ms, C = 4 6.88 ms (clusters of 4 leave SMs idle: a cluster must fit inside one GPC)
     int C = p.cluster_opt ? p.cluster_opt : (nqb % 2 == 0 ? 2 : 1);
     if (nqb % C != 0 || dump || (p.debug & 2)) C = 1;
+    // clusters of two run as one tcgen05 CTA pair (option gemm_pair, on by default) unless tiles are being balanced
+    bool pair = C == 2 && MTsel == 1 && p.allow_pair;
+    const void *func = gemm_kernel_ptr(MTsel, kpl, metric, pair);
+    if (pair) smem = sizeof(GemmSmemT<1, 1>) + 1024;
+    e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { snprintf(p.err, sizeof p.err, "gemm_tf32 smem attribute: %s", cudaGetErrorString(e)); return -2; }
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attrs[2];
     cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = st; cfg.attrs = attrs;
@@ -564,7 +663,16 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
         if (cudaOccupancyMaxActiveClusters(&maxc, func, &cfg) == cudaSuccess && maxc > 0) {
             if (maxc * C < nqb * ngroups) ngroups = maxc * C / nqb;
         } else (void)cudaGetLastError();
-        if (ngroups < 1) { C = 1; ngroups = std::max(1, std::min(n_sm / nqb, n_tiles)); }
+        if (ngroups < 1) {
+            C = 1; ngroups = std::max(1, std::min(n_sm / nqb, n_tiles));
+            if (pair) {
+                pair = false;
+                func = gemm_kernel_ptr(MTsel, kpl, metric, false);
+                smem = sizeof(GemmSmemT<1>) + 1024; cfg.dynamicSmemBytes = smem;
+                e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) { snprintf(p.err, sizeof p.err, "gemm_tf32 smem attribute: %s", cudaGetErrorString(e)); return -2; }
+            }
+        }
     }
     // Balanced tiles (option gemm_balance, off by default): shrink the tile height until every group runs the same number of
     // rounds, BN = ceil(N / (rounds * groups)).  Measured on config 2: 155.8 vs 154.1 us -- no gain: the MMA is N = 256 either
@@ -572,7 +680,8 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     // bound as HBM is, so shorter tiles only add tensor work.
     const int rounds = (n_tiles + ngroups - 1) / ngroups;
     int bn = (int)((n_rows + (int64_t)rounds * ngroups - 1) / ((int64_t)rounds * ngroups));
-    bn = std::min(G_BN, std::max(2 * C, (bn + 2 * C - 1) / (2 * C) * (2 * C)));
+    const int bq = pair ? 16 : 2 * C;                // pair: the M = 256 MMA takes N in steps of 16, and each CTA holds N / 2 rows
+    bn = std::min(G_BN, std::max(bq, (bn + bq - 1) / bq * bq));
     if (!p.balance_tiles) bn = G_BN;
     n_tiles = (int)((n_rows + bn - 1) / bn);
     ngroups = std::max(1, std::min(ngroups, n_tiles));
@@ -601,6 +710,8 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     a.arrive = nullptr; a.arrive_next = nullptr;
     a.dump = dump;
     a.rows = rows; a.ld = ld; a.l2_prefetch = p.l2_prefetch ? 1 : 0; a.debug = p.debug; a.cluster = C; a.bn = bn;
+    a.pair = pair ? 1 : 0;
+    a.idesc_pair = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)((2 * G_BM) >> 4) << 24);
     // bootstrap needs every CTA of a query block resident at once: cooperative launch, grid <= #SMs (1 CTA / SM)
     int boot_lists = std::min(L, 32) & ~1;                       // even: both halves of a CTA
     const int m = boot_lists ? (kprime + boot_lists - 1) / boot_lists : G_BOOT_MAX + 1;
@@ -609,8 +720,13 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
         cudaGetDevice(&dev);
         p.coop = (cudaDeviceGetAttribute(&v, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && v) ? 1 : 0;
     }
-    a.boot_m = (!dump && !(p.debug & 1) && p.coop == 1 && m <= G_BOOT_MAX && nqb * ngroups <= n_sm && p.allow_boot) ? m : 0;
+    a.drop_min = drop_min;
+    a.boot_m = (!dump && drop_min && !(p.debug & (1 | 16 | 32)) && p.coop == 1 && m <= G_BOOT_MAX && nqb * ngroups <= n_sm && p.allow_boot) ? m : 0;
     a.boot_lists = boot_lists;
+    // Early hand-back keeps only four rows per (query, half tile) of the first tile and lets the certificate account for the
+    // rest (drop_min).  That is a good trade only when the bound sits far above the final top-k', i.e. when the rows the
+    // bound was estimated from (boot_lists x 128) are a small part of the table; small tables re-read the tile instead.
+    a.boot_early = (a.boot_m && n_rows >= (int64_t)16 * boot_lists * 128) ? 1 : 0;
     if (a.boot_m) {
         if (p.arrive_ws != (const void *)wsb || p.arrive_ws_cap != (size_t)ws.cap) {
             e = cudaMemsetAsync(wsb, 0, hdr, st);

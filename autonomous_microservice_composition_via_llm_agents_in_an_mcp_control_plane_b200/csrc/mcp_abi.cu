@@ -100,7 +100,7 @@ struct mcp_index {
     int opt_path = MCP_PATH_AUTO, opt_kprime = 0, opt_max_fallback = 4, opt_time_coarse = 0;
     // workspace
     Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, exact_key, exact_row, flags,
-        exact_all, out_ids, out_scores, out_scores64, gemm_ws, q_pad, inv_nq_exact, nq2f;
+        exact_all, out_ids, out_scores, out_scores64, gemm_ws, q_pad, nq2f, drop_min;
     int *h_status = nullptr;   // pinned + mapped: [0] certificate failures, [1] unresolved; written by the fallback kernel's status fold
     int *h_status_dev = nullptr;   // the same words as the device addresses them
     Buf slot_ticket;           // one ticket per fallback slot (zero between launches)
@@ -140,7 +140,6 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     CU(cudaHostAlloc(&idx->h_status, 4 * sizeof(int), cudaHostAllocMapped));
     idx->h_status[0] = idx->h_status[1] = 0;
     CU(cudaHostGetDevicePointer(&idx->h_status_dev, idx->h_status, 0));
-    CU(cudaFuncSetAttribute(rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_SMEM_BYTES(8192)));
     CU(cudaFuncSetAttribute(rescore_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_LIMIT));
     int rc = idx->consts.ensure(sizeof(TableConsts));
     if (!rc) rc = idx->flags.ensure(sizeof(int) * 4096);
@@ -157,7 +156,7 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     Buf *bufs[] = {&idx->own_rows, &idx->norm2, &idx->inv_norm, &idx->penalty, &idx->consts, &idx->q_copy,
                    &idx->nq2, &idx->inv_nq, &idx->qflag, &idx->scores, &idx->listsA, &idx->listsB, &idx->cntA,
                    &idx->cntB, &idx->exact_key, &idx->exact_row, &idx->flags, &idx->exact_all, &idx->out_ids,
-                   &idx->out_scores, &idx->out_scores64, &idx->gemm_ws, &idx->q_pad, &idx->inv_nq_exact, &idx->nq2f, &idx->slot_ticket};
+                   &idx->out_scores, &idx->out_scores64, &idx->gemm_ws, &idx->q_pad, &idx->nq2f, &idx->drop_min, &idx->slot_ticket};
     for (Buf *b : bufs) b->release();
     for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
     if (idx->h_status) cudaFreeHost(idx->h_status);
@@ -322,6 +321,8 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
     } else if (!strcmp(name, "gemm_cluster")) {
         if (value != 0 && value != 1 && value != 2 && value != 4) return fail(MCP_EINVAL, "gemm_cluster must be 0, 1, 2 or 4");
         idx->gemm.cluster_opt = (int)value;
+    } else if (!strcmp(name, "gemm_pair")) {
+        idx->gemm.allow_pair = value != 0;
     } else if (!strcmp(name, "gemm_debug")) {
         idx->gemm.debug = (int)value;
     } else if (!strcmp(name, "gemm_l2_prefetch")) {
@@ -515,7 +516,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     if ((size_t)(nq + 8) * sizeof(int) > idx->flags.cap) return fail(MCP_EINVAL, "n_queries %d exceeds the flag buffer", nq);
     // flags: [0] n_flag (zero between kernels) [1] certificate failures [2] unresolved (both since last sync_status) [8..] list
     int *n_flag = idx->flags.as<int>(), *flag_list = n_flag + 8;
-    if ((rc = idx->inv_nq_exact.ensure(sizeof(float) * nq))) return rc;
+    if ((rc = idx->drop_min.ensure(sizeof(unsigned int) * nq))) return rc;
     if ((rc = idx->nq2f.ensure(sizeof(float) * nq))) return rc;
     // coarse kernels only need fp32 norms; the exact fp64 norm of each query is computed inside the fused rescoring
     // kernel (as one more chain), so nothing serial sits in front of the scan
@@ -524,7 +525,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), idx->nq2f.as<float>());
         KL();
     } else {
-        prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), n_flag);
+        prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), n_flag,
+                                                               idx->drop_min.as<unsigned int>());
         KL();
     }
 
@@ -597,7 +599,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             int L, cap; u64 *lists; int *cnts;
             if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, idx->d_rows, n, dim, idx->ld, dq, cq,
                                     idx->inv_nq.as<float>() + q0, idx->nq2f.as<float>() + q0, idx->inv_norm.as<float>(),
-                                    idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap)))
+                                    idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap, nullptr,
+                                    idx->drop_min.as<unsigned int>() + q0)))
                 return fail(rc, "%s", idx->gemm.err);
             idx->stats.kernel_launches++;
             if ((rc = coarse_event(idx, st))) return rc;
@@ -614,7 +617,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
                 idx->d_rows, dim, idx->ld, dq, idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt, cand_stride,
                 pow2_at_least(std::max(std::min(cand_stride, kprime), 2)), k, idx->id_base, idx->consts.as<TableConsts>(), cp,
                 idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
-                out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag);
+                out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag,
+                path == MCP_PATH_GEMM_TF32 ? idx->drop_min.as<unsigned int>() + q0 : nullptr);
             KL();
         }
         // certificate failures: fp64 scan on the device, flag_list holds chunk-local query numbers
@@ -754,7 +758,7 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     if ((rc = idx->nq2f.ensure(sizeof(float) * n_queries))) return rc;
     // the same query norms a search feeds its coarse kernel
     prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
-                                                                 idx->nq2f.as<float>(), nullptr);
+                                                                 idx->nq2f.as<float>(), nullptr, nullptr);
     KCHECK();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     if (path == MCP_PATH_STREAM_FP32) {

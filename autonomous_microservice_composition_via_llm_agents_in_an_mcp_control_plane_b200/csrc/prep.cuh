@@ -109,10 +109,12 @@ prep_queries_kernel(const float *__restrict__ queries, int dim, double *__restri
 // stream while the coarse scan is under way.
 __global__ void __launch_bounds__(128)
 prep_queries_fast_kernel(const float *__restrict__ queries, int n_queries, int dim, float *__restrict__ inv_norm,
-                         float *__restrict__ norm2f, int *__restrict__ n_flag /* NULL, or the certificate's flag count to clear */) {
+                         float *__restrict__ norm2f, int *__restrict__ n_flag /* NULL, or the certificate's flag count to clear */,
+                         unsigned int *__restrict__ drop_min /* NULL, or [n_queries]: reset to "nothing dropped" */) {
     if (n_flag && blockIdx.x == 0 && threadIdx.x == 0) *n_flag = 0;     // first kernel of a search: nothing is flagged yet
     const int q = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (q >= n_queries) return;
+    if (drop_min && lane == 0) drop_min[q] = 0xFFFFFFFFu;
     const float *src = queries + (int64_t)q * dim;
     float acc = 0.f;
     for (int i = lane; i < dim; i += 32) { const float v = src[i]; acc = fmaf(v, v, acc); }

@@ -28,187 +28,21 @@ struct CertParams {
     int debug;             // option gemm_debug >> 8 (timing experiments, wrong results): 1 no chain, 2 no gathers
 };
 
-// ---- K4a: exact rescoring ------------------------------------------------------------------------
-// One CTA = one query x 32 candidates.  The fp64 chain of a candidate (dim dependent FMAs, index order) is
-// the latency floor.  On B200 the fp64 pipe is narrow (tools/fp64_latency.cu, tools/chain_bench.cu: a dependent DFMA
-// every ~8-16 cycles, F2F.F64.F32 ~12 cycles per warp instruction, both on the same pipe, ~0.4 warp instructions per
-// clock per SM), so the chain carries as little as possible: the query is converted to fp64 once per CTA
-// by all threads and kept in shared memory; all 128 threads stream the 32 candidate rows through a 3-stage
-// cp.async ring (64 floats per row per stage, 256 contiguous bytes per row); the 32 lanes of warp 0 each walk
-// their own row out of shared memory, converting only the row element.  grid (ceil(stride / 32), Q).
-#define RS_ROWS 32
-#define RS_COLS 64
-#define RS_PITCH (RS_COLS + 4)        // fp32 ring row pitch (floats): 16-byte aligned rows, conflict-free LDS.128
-#define RS_STAGES 5                   // 4 chunks (~2.4 us of chain time) of row gathers in flight per CTA; 55.5 KB smem at dim 1536 -> 4 CTAs / SM
-#define RS_SMEM_BYTES(dim) (sizeof(double) * (((dim) + 3) & ~3) + sizeof(float) * RS_STAGES * RS_ROWS * RS_PITCH + 16)
+#define RS_ROWS 32                    // candidates per warp (lane = candidate)
 __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-__global__ void __launch_bounds__(RESCORE_THREADS)
-rescore_kernel(const float *__restrict__ rows, int dim, int64_t ld,
-               const float *__restrict__ queries, const double *__restrict__ nq2,
-               const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
-               const u64 *__restrict__ cand, const int *__restrict__ cand_cnt, int cand_stride,
-               u64 *__restrict__ exact_key, int *__restrict__ exact_row) {
-    extern __shared__ __align__(16) unsigned char rs_raw[];
-    const int dimp = (dim + 3) & ~3;                       // rows are padded with zeros up to ld >= dimp
-    double *sq = reinterpret_cast<double *>(rs_raw);       // [dimp] the query, already fp64
-    float *tile = reinterpret_cast<float *>(sq + dimp);    // [RS_STAGES][RS_ROWS][RS_PITCH]
-    __shared__ int s_row[RS_ROWS];
-    const int q = blockIdx.y, j0 = blockIdx.x * RS_ROWS;
-    const int cnt = min(cand_cnt[q], cand_stride);
-    if (j0 >= cand_stride) return;
-    const float *qv = queries + (int64_t)q * dim;
-    {   // query -> fp64 in shared memory; the loads of a thread are issued together, not one per loop trip
-        float t[8];
-        for (int i0 = 0; i0 < dimp; i0 += 8 * RESCORE_THREADS) {
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { const int i = i0 + u * RESCORE_THREADS + threadIdx.x; t[u] = i < dim ? __ldg(qv + i) : 0.f; }
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { const int i = i0 + u * RESCORE_THREADS + threadIdx.x; if (i < dimp) sq[i] = (double)(t[u]); }
-        }
-    }
-    if (threadIdx.x < RS_ROWS) {
-        int j = j0 + threadIdx.x;
-        s_row[threadIdx.x] = (j < cnt) ? (int)(cand[(int64_t)q * cand_stride + j] & 0xFFFFFFFFull) : -1;
-    }
-    __syncthreads();
-    const int nchunks = (dimp + RS_COLS - 1) / RS_COLS;
-    auto issue = [&](int c) {
-        if (c < nchunks) {
-            const int c0 = c * RS_COLS, w4 = min(RS_COLS, dimp - c0) >> 2;
-            float *dst = tile + (size_t)(c % RS_STAGES) * RS_ROWS * RS_PITCH;
-#pragma unroll
-            for (int u = 0; u < (RS_ROWS * RS_COLS / 4) / RESCORE_THREADS; ++u) {
-                const int f = threadIdx.x + u * RESCORE_THREADS, rr = f / (RS_COLS / 4), c4 = f % (RS_COLS / 4);
-                const int row = s_row[rr];
-                if (row >= 0 && c4 < w4) cp_async16(dst + rr * RS_PITCH + c4 * 4, rows + (int64_t)row * ld + c0 + c4 * 4);
-            }
-        }
-        cp_async_commit();
-    };
-    for (int c = 0; c < RS_STAGES - 1; ++c) issue(c);
-    double acc = 0.0;
-    // The chain warp differs from CTA to CTA: warp w sits on scheduler w % 4, and the F2F pipe of one scheduler
-    // cannot feed the chains of every CTA resident on the SM.
-    const int cw = (blockIdx.x + blockIdx.y) & 3, cl = threadIdx.x & 31;
-    const bool chain = (threadIdx.x >> 5) == cw;
-    for (int c = 0; c < nchunks; ++c) {
-        cp_async_wait<RS_STAGES - 2>();
-        __syncthreads();                                   // chunk c has landed; everyone is done with chunk c-1's stage
-        issue(c + RS_STAGES - 1);
-        if (chain) {
-            const int c0 = c * RS_COLS, w = min(RS_COLS, dimp - c0);
-            const float *e = tile + (size_t)(c % RS_STAGES) * RS_ROWS * RS_PITCH + cl * RS_PITCH;
-            const double *qq = sq + c0;
-            if (metric == 0) {
-#pragma unroll 4
-                for (int i = 0; i < w; i += 4) {
-                    const float4 v = *reinterpret_cast<const float4 *>(e + i);
-                    const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
-                    acc = fma(u0.x, (double)(v.x), acc); acc = fma(u0.y, (double)(v.y), acc);
-                    acc = fma(u1.x, (double)(v.z), acc); acc = fma(u1.y, (double)(v.w), acc);
-                }
-            } else {
-#pragma unroll 4
-                for (int i = 0; i < w; i += 4) {
-                    const float4 v = *reinterpret_cast<const float4 *>(e + i);
-                    const double2 u0 = *reinterpret_cast<const double2 *>(qq + i), u1 = *reinterpret_cast<const double2 *>(qq + i + 2);
-                    double d;
-                    d = __dsub_rn(u0.x, (double)(v.x)); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                    d = __dsub_rn(u0.y, (double)(v.y)); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                    d = __dsub_rn(u1.x, (double)(v.z)); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                    d = __dsub_rn(u1.y, (double)(v.w)); acc = __dadd_rn(acc, __dmul_rn(d, d));
-                }
-            }
-        }
-    }
-    if (chain && j0 + cl < cand_stride) {
-        const int64_t o = (int64_t)q * cand_stride + j0 + cl;
-        const int row = s_row[cl];
-        if (row < 0) { exact_key[o] = ~0ull; exact_row[o] = MCP_PAD_ROW; }
-        else {
-            double s = exact_finish(acc, metric, nq2[q], ne2[row]);
-            if (penalty) s = s + (double)penalty[row];
-            exact_key[o] = f64_ord(s);
-            exact_row[o] = row;
-        }
-    }
-}
-
-// ---- K4b: final sort + outputs + certificate; one CTA per query --------------------------------
-__global__ void __launch_bounds__(FINAL_THREADS)
-finalize_kernel(const u64 *__restrict__ exact_key, const int *__restrict__ exact_row,
-                const u64 *__restrict__ cand, const int *__restrict__ cand_cnt, int cand_stride,
-                int npow2, int k, int64_t id_base, const double *__restrict__ nq2,
-                const unsigned char *__restrict__ qflag, const TableConsts *__restrict__ consts,
-                CertParams cp, int32_t *__restrict__ out_ids, float *__restrict__ out_scores,
-                double *__restrict__ out_scores64, int *__restrict__ flag_list, int *__restrict__ n_flag) {
-    __shared__ u64 sk[FINAL_MAX];
-    __shared__ int sv[FINAL_MAX];
-    __shared__ unsigned int s_tmax;
-    int q = blockIdx.x;
-    int cnt = min(cand_cnt[q], cand_stride);
-    if (threadIdx.x == 0) s_tmax = 0;
-    __syncthreads();
-    unsigned int tmax = 0;
-    for (int i = threadIdx.x; i < npow2; i += blockDim.x) {
-        if (i < cnt) {
-            int64_t o = (int64_t)q * cand_stride + i;
-            sk[i] = exact_key[o]; sv[i] = exact_row[o];
-            tmax = max(tmax, (unsigned int)(cand[o] >> 32));
-        } else { sk[i] = ~0ull; sv[i] = MCP_PAD_ROW; }
-    }
-    atomicMax(&s_tmax, tmax);
-    cta_bitonic_sort_pairs(sk, sv, npow2);
-    for (int i = threadIdx.x; i < k; i += blockDim.x) {
-        int64_t o = (int64_t)q * k + i;
-        bool real = (i < cnt) && sv[i] != MCP_PAD_ROW;
-        double s = real ? ord_f64(sk[i]) : CUDART_INF;
-        out_ids[o] = real ? (int32_t)(id_base + sv[i]) : -1;
-        out_scores[o] = (float)s;
-        if (out_scores64) out_scores64[o] = s;
-    }
-    if (threadIdx.x == 0) {
-        bool pass;
-        if (qflag[q]) pass = false;                          // degenerate query: always the fp64 scan
-        else if (cp.complete) pass = true;
-        else if (s_tmax == 0xFFFFFFFFu) pass = true;         // worst survivor is NaN: every dropped row is NaN with a larger id
-        else if (cnt < k) pass = false;                      // cannot happen when !complete; be safe
-        else {
-            double T = (double)ord_f32(s_tmax);
-            double sk_k = ord_f64(sk[k - 1]);                // NaN if fewer than k numeric scores
-            double qn = sqrt(nq2[q]);
-            double en = sqrt(__longlong_as_double((long long)consts->max_norm2_bits));
-            double pen_abs = (double)consts->pen_absmax, pen_max = (double)consts->pen_max;
-            double eps;
-            if (cp.metric == 0) {
-                eps = cp.rel + cp.abs_pen * (2.0 + pen_abs);
-            } else if (cp.path == 2) {
-                // squared distance assembled from norms and a TF32 dot: |d2c - d2| <= delta
-                double delta = 2.0 * cp.rel * qn * en + 4.0 * 5.96e-8 * (qn + en) * (qn + en);
-                double x0 = T - pen_max; x0 = x0 > 0.0 ? x0 * x0 : 0.0;   // every dropped row has coarse d2 >= x0
-                eps = sqrt(x0) - sqrt(fmax(x0 - delta, 0.0)) + cp.abs_pen * (sqrt(x0) + pen_abs);
-            } else {
-                eps = cp.rel * (qn + en) + cp.abs_pen * ((qn + en) + pen_abs);
-            }
-            pass = (sk_k == sk_k) && (sk_k < T - eps);
-        }
-        if (!pass) flag_list[atomicAdd(n_flag, 1)] = q;
-    }
-}
-
 // ---- K4 fused: exact rescoring + query norm + final sort + certificate; one CTA per query ------------------------
 // Replaces prep_queries_kernel + rescore_kernel + finalize_kernel on the search path (three launches, two global round
-// trips).  Warp roles (GP + 2 warps):
+// trips).  Warp roles (GP + RF_NPROD + 1 warps):
 //   * GP candidate warps, lane = candidate (more than GP * 32 candidates take several passes): wait for a chunk of
 //     64 columns on the stage's `full` mbarrier, walk it in index order, release the stage on `empty`.  They issue
 //     nothing but their chain -- an ncu capture of the version where all threads shared the copy loop showed that
 //     loop costing as much as the chains, and the chain (about 15 cycles per element) is the kernel's floor.
-//   * one producer warp: 16 lanes per row issue cp.async (16 bytes each, 256 contiguous bytes per row and chunk) into
+//   * RF_NPROD producer warps: 16 lanes per row issue cp.async (16 bytes each, 256 contiguous bytes per row and chunk) into
 //     a ring of RF_STAGES chunk tiles and hand completion to `full` (cp.async.mbarrier.arrive).  256-byte
 //     cp.async.bulk copies were tried here and ran at about one copy per 44 cycles per SM -- 1.5x slower overall.
 //   * one warp whose lane 0 walks the query against itself: that chain *is* the exact fp64 squared norm of the
@@ -268,7 +102,8 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
                         int npow2, int k, int64_t id_base, const TableConsts *__restrict__ consts, CertParams cp,
                         double *__restrict__ nq2_out, unsigned char *__restrict__ qflag_out,
                         int32_t *__restrict__ out_ids, float *__restrict__ out_scores, double *__restrict__ out_scores64,
-                        int *__restrict__ flag_list, int *__restrict__ n_flag) {
+                        int *__restrict__ flag_list, int *__restrict__ n_flag,
+                        const unsigned int *__restrict__ drop_min /* NULL, or [q]: best coarse score the scan dropped outside its lists */) {
     extern __shared__ __align__(16) unsigned char rf_raw[];
     __shared__ u64 sk[FINAL_MAX];
     __shared__ int sv[FINAL_MAX];
@@ -352,10 +187,9 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
                 }
                 cp_async_commit();
             };
-            // Completion is relayed by hand: cp.async.mbarrier.arrive was measured to fire only when *all* of the
-            // thread's copies (later chunks included) had landed, which serialises the ring.  wait_group has a
-            // watermark, so: keep RF_DEPTH chunks in flight, and once chunk c - RF_DEPTH is known complete every
-            // producer lane arrives on its `full` barrier (release; the candidate warps' try_wait acquires).
+            // Completion is relayed by hand: the warp keeps RF_DEPTH chunks in flight (wait_group's watermark), and once
+            // chunk c - RF_DEPTH is known complete every producer lane arrives on its `full` barrier (release; the
+            // candidate warps' try_wait acquires).  cp.async.mbarrier.arrive.noinc gave the same timing.
             for (int c = 0; c < nchunks + RF_DEPTH; ++c) {
                 if (c < nchunks) issue(c); else cp_async_commit();
                 if (c >= RF_DEPTH) {
@@ -439,13 +273,17 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
         const unsigned char flag = (unsigned char)((s_bad ? 2 : 0) | ((odd || nq2 == 0.0 || s_bad) ? 1 : 0));
         nq2_out[q] = nq2;
         qflag_out[q] = flag;
+        // every row outside the candidate list scored (coarsely) at least T: the worst survivor, or -- when the scan's
+        // bootstrap tile dropped rows without listing them -- the best score such a row can have had
+        const unsigned int dropped = drop_min ? drop_min[q] : 0xFFFFFFFFu;
+        const unsigned int tmax_eff = min(s_tmax, dropped);
         bool pass;
         if (flag) pass = false;                              // degenerate query: always the fp64 scan
-        else if (cp.complete) pass = true;
-        else if (s_tmax == 0xFFFFFFFFu) pass = true;         // worst survivor is NaN: every dropped row is NaN with a larger id
+        else if (cp.complete && dropped == 0xFFFFFFFFu) pass = true;
+        else if (tmax_eff == 0xFFFFFFFFu) pass = true;       // worst survivor is NaN: every dropped row is NaN with a larger id
         else if (cnt < k) pass = false;                      // cannot happen when !complete; be safe
         else {
-            const double T = (double)ord_f32(s_tmax);
+            const double T = (double)ord_f32(tmax_eff);
             const double sk_k = ord_f64(sk[k - 1]);          // NaN if fewer than k numeric scores
             const double qn = sqrt(nq2);
             const double en = sqrt(__longlong_as_double((long long)consts->max_norm2_bits));
