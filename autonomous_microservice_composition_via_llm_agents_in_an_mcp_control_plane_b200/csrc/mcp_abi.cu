@@ -140,7 +140,7 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     CU(cudaHostAlloc(&idx->h_status, 4 * sizeof(int), cudaHostAllocMapped));
     idx->h_status[0] = idx->h_status[1] = 0;
     CU(cudaHostGetDevicePointer(&idx->h_status_dev, idx->h_status, 0));
-    CU(cudaFuncSetAttribute(rescore_finalize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_LIMIT));
+    CU(cudaFuncSetAttribute(rescore_finalize_kernel<5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_LIMIT));
     int rc = idx->consts.ensure(sizeof(TableConsts));
     if (!rc) rc = idx->flags.ensure(sizeof(int) * 4096);
     if (rc) { delete idx; return rc; }
@@ -612,10 +612,12 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
         {
             const int G = (std::min(cand_stride, kprime) + RS_ROWS - 1) / RS_ROWS;
             int GP = std::max(1, cq <= idx->n_sm ? std::min(G, RF_MAXG) : std::min(G, 2));   // few queries: one pass; many: more CTAs per SM
-            while (GP > 1 && RF_SMEM_BYTES(dim, GP) > RF_SMEM_LIMIT) --GP;
-            rescore_finalize_kernel<<<cq, 32 * (GP + RF_NPROD + 1), RF_SMEM_BYTES(dim, GP), st>>>(
+            const int npow2 = pow2_at_least(std::max(std::min(cand_stride, kprime), 2));
+            const int stages = 5;
+            while (GP > 1 && RF_SMEM_BYTES(dim, GP, stages, npow2) > RF_SMEM_LIMIT) --GP;
+            rescore_finalize_kernel<5, 3><<<cq, 32 * (GP + RF_NPROD + 1), RF_SMEM_BYTES(dim, GP, stages, npow2), st>>>(
                 idx->d_rows, dim, idx->ld, dq, idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt, cand_stride,
-                pow2_at_least(std::max(std::min(cand_stride, kprime), 2)), k, idx->id_base, idx->consts.as<TableConsts>(), cp,
+                npow2, k, idx->id_base, idx->consts.as<TableConsts>(), cp,
                 idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
                 out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag,
                 path == MCP_PATH_GEMM_TF32 ? idx->drop_min.as<unsigned int>() + q0 : nullptr);

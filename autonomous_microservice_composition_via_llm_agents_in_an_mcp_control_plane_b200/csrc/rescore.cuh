@@ -50,12 +50,15 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 // Then the CTA sorts, writes the top k and checks the certificate.  nq2 / qflag are also written out for the fp64
 // fallback scan that may follow.
 #define RF_MAXG 4
-#define RF_COLS 64                    // columns per chunk: 256 contiguous bytes of a row per gather
+#define RF_COLS 64                    // columns per chunk: 256 contiguous bytes of a row per gather.  tools/gather_bench.cu: alone, 256-byte
+                                      // pieces gather at 4.5 TB/s over the GPU and 512-byte pieces at 6.1 TB/s, but inside this kernel
+                                      // 512-byte pieces (3 stages to keep two CTAs per SM) measured slower: 45.6 vs 35.8 us
 #define RF_PITCH (RF_COLS + 4)
-#define RF_STAGES 5
 #define RF_NPROD 2                     // producer warps (each keeps its own copies in flight)
-#define RF_DEPTH 3                     // chunks of gathers in flight behind the one being handed over
-#define RF_SMEM_BYTES(dim, gp) (sizeof(double) * (((dim) + 3) & ~3) + sizeof(float) * RF_STAGES * (gp) * RS_ROWS * RF_PITCH + 64)
+// ring shapes (template arguments): <stages, chunks of gathers in flight behind the one being handed over>
+//   <5, 3>  87 KB at GP = 2 -> two CTAs per SM.  A deeper ring for the one-CTA-per-SM case (<10, 8>) measured no faster.
+// dynamic shared memory: query in fp64 | ring | final sort keys (u64) and rows (int), npow2 each
+#define RF_SMEM_BYTES(dim, gp, stages, npow2) (sizeof(double) * (((dim) + 3) & ~3) + sizeof(float) * (stages) * (gp) * RS_ROWS * RF_PITCH + 64 + 12 * (size_t)(npow2))
 #define RF_SMEM_LIMIT (216 * 1024)    // dynamic shared memory the kernel may ask for (227 KB per CTA less its static arrays)
 
 // One candidate's walk over one chunk (w columns, a multiple of 4), in index order.  The compiler left to itself puts
@@ -95,6 +98,7 @@ __device__ __forceinline__ double rf_chain(const float *__restrict__ e, const do
     return acc;
 }
 
+template <int RF_STAGES, int RF_DEPTH>
 __global__ void __launch_bounds__(32 * (RF_MAXG + RF_NPROD + 1))
 rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, const float *__restrict__ queries,
                         const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
@@ -105,8 +109,6 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
                         int *__restrict__ flag_list, int *__restrict__ n_flag,
                         const unsigned int *__restrict__ drop_min /* NULL, or [q]: best coarse score the scan dropped outside its lists */) {
     extern __shared__ __align__(16) unsigned char rf_raw[];
-    __shared__ u64 sk[FINAL_MAX];
-    __shared__ int sv[FINAL_MAX];
     __shared__ int s_row[RF_MAXG * RS_ROWS];
     __shared__ const float *s_rowptr[RF_MAXG * RS_ROWS];
     __shared__ __align__(8) u64 s_full[RF_STAGES], s_empty[RF_STAGES];
@@ -119,6 +121,8 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
     double *sq = reinterpret_cast<double *>(rf_raw);                // [dimp] the query in fp64
     float *tile = reinterpret_cast<float *>(sq + dimp);             // [RF_STAGES][GP * RS_ROWS][RF_PITCH]
     const size_t stage_floats = (size_t)GP * RS_ROWS * RF_PITCH;
+    u64 *sk = reinterpret_cast<u64 *>(tile + RF_STAGES * stage_floats + 16);   // [npow2] (8-byte aligned: every term above is)
+    int *sv = reinterpret_cast<int *>(sk + npow2);                             // [npow2]
     const int q = blockIdx.x;
     const int cnt = min(cand_cnt[q], cand_stride);
     const float *qv = queries + (int64_t)q * dim;
