@@ -375,7 +375,7 @@ static int harvest_events(mcp_index *idx) {
 static int coarse_event(mcp_index *idx, cudaStream_t st) {
     if (!idx->opt_time_coarse) return MCP_OK;
     if (idx->ev_used == (int)idx->ev.size()) {
-        if (idx->ev.size() >= 512 && (idx->ev_used & 1) == 0) { int rc = harvest_events(idx); if (rc) return rc; }
+        if (idx->ev.size() >= 8192 && (idx->ev_used & 1) == 0) { int rc = harvest_events(idx); if (rc) return rc; }
         else { cudaEvent_t e; CU(cudaEventCreate(&e)); idx->ev.push_back(e); }
     }
     CU(cudaEventRecord(idx->ev[idx->ev_used++], st));
