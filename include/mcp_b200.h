@@ -149,8 +149,11 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
  * "gemm_wide" (1 = K2 with 256-query CTAs above 128 queries; default 0 = 128-query CTAs, measured faster),
  * "gemm_l2_prefetch" (1 = K2 with a per-row 1 KB L2 bulk prefetch; default 0, measured slower),
  * "gemm_balance" (1 = K2 tile height shrunk so that every CTA gets the same number of tiles; default 0 = 256-row tiles, measured equal),
- * "gemm_cluster" (CTAs per cluster that multicast the row tile to each other: 0 = automatic, or 1 / 2 / 4),
- * "gemm_debug" (bit mask for timing experiments that switch off parts of K2 -- results are WRONG; default 0),
+ * "gemm_cluster" (CTAs per cluster that share a row tile: 0 = automatic -- 2 when the batch has an even number of
+ * 128-query blocks, else 1 -- or 1 / 2 / 4),
+ * "gemm_pair" (default 1 = a cluster of 2 runs as one tcgen05 CTA pair, cta_group::2 with M = 256; 0 = two M = 128
+ * CTAs that multicast the row tile to each other),
+ * "gemm_debug" (bit mask for timing experiments that switch off parts of K2 / K4 -- results are WRONG; default 0),
  * "gemm_bootstrap" (0 = K2 without the cross-CTA threshold bootstrap; default 1),
  * "time_coarse" (1 = bracket every coarse scan with CUDA events on the caller's stream; the sums
  * appear in mcp_stats after mcp_index_sync_status).                                            */
