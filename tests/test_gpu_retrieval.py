@@ -353,3 +353,46 @@ def test_query_chunking_paths_agree(mcp, oracle):
     oi, os64, _ = oracle.topk(rows.cpu().numpy(), qs.cpu().numpy()[sample], k, 0, None)
     assert np.array_equal(want_i.cpu().numpy()[sample], oi) and np.array_equal(want_s.cpu().numpy()[sample], os64)
     idx.close()
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+def test_cta_pair_and_single_cta_scans_agree_with_oracle(mcp, oracle, metric):
+    """K2 has three shapes: one tcgen05 CTA pair per cluster (cta_group::2, the default for an even number of 128-query
+    blocks), two single CTAs multicasting the row tile, and plain single CTAs.  Same oracle answer from each, with and
+    without balanced tile heights (which change the MMA's N and the TMA box)."""
+    rng = np.random.default_rng(101 + metric)
+    n, d, q, k = 70_001, 96, 256, 16           # > 65536 rows: the bootstrap tile hands its accumulator back early
+    rows = rng.standard_normal((n, d), dtype=np.float32)
+    qs = rng.standard_normal((q, d), dtype=np.float32)
+    pen = (rng.random(n) * 0.02).astype(np.float32)
+    want_ids, want_s64, _ = oracle.topk(rows, qs, k, metric, pen)
+    for opts in ({"gemm_pair": 1}, {"gemm_pair": 0}, {"gemm_cluster": 1}, {"gemm_pair": 1, "gemm_balance": 1}):
+        with mcp.ServiceIndex(d, "cosine" if metric == 0 else "l2") as idx:
+            idx.load(rows).set_penalty(pen)
+            idx.set_option("path", "gemm_tf32")
+            for name, v in opts.items():
+                idx.set_option(name, v)
+            _assert_parity(idx.search(qs, k), want_ids, want_s64)
+            assert idx.stats()["last_path"] == 2, opts
+
+
+def test_bootstrap_tile_drops_are_caught_by_the_certificate(mcp, oracle):
+    """On large tables K2's first tile keeps only four rows per (query, half tile) and records the best score it may
+    have dropped; the certificate must then refuse any answer such a row could belong to.  Here the whole true top-k
+    of query 0 sits inside one half of the first tile (rows 0..39 are near-copies of the query), so 36 of them are
+    dropped by construction: the query has to fail the certificate and come back exact from the fp64 scan."""
+    rng = np.random.default_rng(202)
+    n, d, q, k = 70_000, 64, 256, 32
+    rows = rng.standard_normal((n, d), dtype=np.float32)
+    qs = rng.standard_normal((q, d), dtype=np.float32)
+    rows[:40] = qs[0] + rng.standard_normal((40, d)).astype(np.float32) * 0.05
+    rows[300:330] = qs[130] + rng.standard_normal((30, d)).astype(np.float32) * 0.05   # second query block, next CTA's first tile
+    want_ids, want_s64, _ = oracle.topk(rows, qs, k, 0, None)
+    assert set(range(40)).issuperset(want_ids[0].tolist())
+    with mcp.ServiceIndex(d, "cosine") as idx:
+        idx.load(rows)
+        idx.set_option("path", "gemm_tf32")
+        _assert_parity(idx.search(qs, k), want_ids, want_s64)
+        st = idx.stats()
+        assert st["last_path"] == 2
+        assert st["certificate_failures"] >= 1, "the dropped rows of the bootstrap tile went unnoticed"
