@@ -145,3 +145,13 @@ __device__ __forceinline__ void bulk_load_1d(void *dst, const void *src, uint32_
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  A kernel launched with the programmatic-stream-serialization attribute may be
+// scheduled while its predecessor in the stream is still draining; it must call pdl_wait() before it touches anything
+// the predecessor wrote (the call returns once that grid has completed and its writes are visible; it is a no-op in a
+// kernel launched the ordinary way).  pdl_trigger() in the predecessor lets the dependent's CTAs take free SM
+// resources early -- they then sit in pdl_wait().
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }

@@ -59,6 +59,18 @@ static int fail(int code, const char *fmt, ...) {
 
 extern "C" const char *mcp_last_error(void) { return g_err.c_str(); }
 
+// launch as a programmatic dependent of the previous kernel in the stream (common.cuh: pdl_wait / pdl_trigger)
+template <class... KArgs, class... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 extern "C" int mcp_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -458,8 +470,8 @@ static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64
         Buf &oc = in_is_A ? idx->cntB : idx->cntA;
         if ((rc = ob.ensure(sizeof(u64) * (size_t)nq * L_out * kprime))) return rc;
         if ((rc = oc.ensure(sizeof(int) * (size_t)nq * L_out))) return rc;
-        select_from_lists_kernel<<<dim3(L_out, nq), SEL_THREADS, 0, st>>>(in, in_cnt, L, cap, G, kprime, ob.as<u64>(),
-                                                                          oc.as<int>(), kprime, raw_in ? 1 : 0);
+        CU(launch_pdl(select_from_lists_kernel, dim3(L_out, nq), dim3(SEL_THREADS), 0, st, in, in_cnt, L, cap, G, kprime, ob.as<u64>(),
+                      oc.as<int>(), kprime, raw_in ? 1 : 0));
         KL();
         in = ob.as<u64>(); in_cnt = oc.as<int>(); L = L_out; cap = kprime; in_is_A = !in_is_A; raw_in = false;
     }
@@ -492,10 +504,10 @@ static int run_exact(mcp_index *idx, cudaStream_t st, const float *d_q, const do
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     const int64_t want = (idx->n_rows + EXSEL_THREADS - 1) / EXSEL_THREADS;
     const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)idx->n_sm * 2, want));
-    exact_fallback_kernel<<<dim3(gx, slots), EXSEL_THREADS, sizeof(float) * idx->dim, st>>>(
-        idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag,
-        k, idx->id_base, idx->exact_all.as<u64>(), idx->slot_ticket.as<int>(), out_ids, out_scores, out_scores64,
-        fold_status ? n_flag + 1 : nullptr, fold_status ? idx->h_status_dev : nullptr);
+    CU(launch_pdl(exact_fallback_kernel, dim3(gx, slots), dim3(EXSEL_THREADS), sizeof(float) * idx->dim, st,
+                  idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag,
+                  k, idx->id_base, idx->exact_all.as<u64>(), idx->slot_ticket.as<int>(), out_ids, out_scores, out_scores64,
+                  fold_status ? n_flag + 1 : nullptr, fold_status ? idx->h_status_dev : nullptr));
     KL();
     return MCP_OK;
 }
@@ -615,12 +627,12 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             const int npow2 = pow2_at_least(std::max(std::min(cand_stride, kprime), 2));
             const int stages = 5;
             while (GP > 1 && RF_SMEM_BYTES(dim, GP, stages, npow2) > RF_SMEM_LIMIT) --GP;
-            rescore_finalize_kernel<5, 3><<<cq, 32 * (GP + RF_NPROD + 1), RF_SMEM_BYTES(dim, GP, stages, npow2), st>>>(
-                idx->d_rows, dim, idx->ld, dq, idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt, cand_stride,
-                npow2, k, idx->id_base, idx->consts.as<TableConsts>(), cp,
-                idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
-                out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag,
-                path == MCP_PATH_GEMM_TF32 ? idx->drop_min.as<unsigned int>() + q0 : nullptr);
+            CU(launch_pdl(rescore_finalize_kernel<5, 3>, dim3(cq), dim3(32 * (GP + RF_NPROD + 1)), RF_SMEM_BYTES(dim, GP, stages, npow2), st,
+                          idx->d_rows, dim, idx->ld, dq, idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt, cand_stride,
+                          npow2, k, idx->id_base, idx->consts.as<TableConsts>(), cp,
+                          idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
+                          out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag,
+                          path == MCP_PATH_GEMM_TF32 ? idx->drop_min.as<unsigned int>() + q0 : nullptr));
             KL();
         }
         // certificate failures: fp64 scan on the device, flag_list holds chunk-local query numbers

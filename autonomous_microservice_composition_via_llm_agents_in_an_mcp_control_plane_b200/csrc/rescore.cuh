@@ -124,6 +124,8 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
     u64 *sk = reinterpret_cast<u64 *>(tile + RF_STAGES * stage_floats + 16);   // [npow2] (8-byte aligned: every term above is)
     int *sv = reinterpret_cast<int *>(sk + npow2);                             // [npow2]
     const int q = blockIdx.x;
+    pdl_trigger();
+    pdl_wait();                                                     // the selection that wrote the candidate lists has completed
     const int cnt = min(cand_cnt[q], cand_stride);
     const float *qv = queries + (int64_t)q * dim;
     if (threadIdx.x == 0) {
@@ -462,6 +464,7 @@ exact_fallback_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, i
                       int *__restrict__ status /* NULL, or [failures, unresolved] */, volatile int *host_status) {
     extern __shared__ float sqv[];
     __shared__ int s_last;
+    pdl_wait();                                      // the kernel that flagged queries has completed
     const int f = blockIdx.y;
     const int nf = *n_flag;
     if (status && blockIdx.x == 0 && f == 0 && threadIdx.x == 0) {

@@ -135,6 +135,8 @@ select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_
     __shared__ int base[SEL_THREADS + 1];      // exclusive prefix of the list lengths
     __shared__ int wsum[SEL_THREADS / 32];
     __shared__ int s_lend;
+    pdl_trigger();
+    pdl_wait();                                                // the scan that wrote the lists has completed
     const int g = blockIdx.x, q = blockIdx.y, L_out = gridDim.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int l0 = g * G, nl = min(G, L_in - l0);
