@@ -79,8 +79,8 @@ extern "C" int mcp_device_count(void) {
 
 extern "C" const char *mcp_build_info(void) {
     return "mcp_b200 sm_100a nvcc " MCP_STR(__CUDACC_VER_MAJOR__) "." MCP_STR(__CUDACC_VER_MINOR__)
-           " kernels: prep_rows scan_fp32 gemm_tf32_tcgen05 select_from_scores select_from_lists rescore"
-           " finalize exact_scan exact_select merge_shards kahn_levels";
+           " kernels: prep_rows prep_queries scan_fp32 gemm_tf32_tcgen05 (cta_group::1 / cta_group::2) select_from_scores"
+           " select_from_lists rescore_finalize exact_fallback exact_scan exact_select merge_shards kahn_levels";
 }
 
 // ---------------------------------------------------------------------------------------------
