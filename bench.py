@@ -181,11 +181,13 @@ def cpu_arm(cfg, steps, warmup, sample_rows=None, rows=None, queries=None, penal
     rows = rows[:m]
     penalty = penalty[:m]
     inv = (1.0 / np.linalg.norm(rows, axis=1)).astype(np.float32)
+    mid = 0 if cfg["metric"] == "cosine" else 1
+    n2 = np.einsum("ij,ij->i", rows, rows).astype(np.float32) if mid else None
     for _ in range(warmup):
-        oracle.numpy_topk_baseline(rows, inv, queries, k, 0, penalty)
+        oracle.numpy_topk_baseline(rows, inv, queries, k, mid, penalty, n2)
     t0 = time.perf_counter()
     for _ in range(steps):
-        oracle.numpy_topk_baseline(rows, inv, queries, k, 0, penalty)
+        oracle.numpy_topk_baseline(rows, inv, queries, k, mid, penalty, n2)
     dt = (time.perf_counter() - t0) / steps
     scale = n / m
     return dict(value=q / (dt * scale), ms_per_step=dt * scale * 1e3, cores=oracle.cpu_oracle.cpu_count(),
@@ -220,6 +222,9 @@ def override(cfg, args):
         if v:
             cfg[key] = v
             cfg["label"] += f" [{key}={v} override]"
+    if getattr(args, "metric", None):
+        cfg["metric"] = args.metric
+        cfg["label"] = cfg["label"].replace("cosine", args.metric) + f" [metric={args.metric} override]"
     return cfg
 
 
@@ -234,6 +239,7 @@ def main():
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--queries", type=int, default=0)
     ap.add_argument("--topk", type=int, default=0)
+    ap.add_argument("--metric", choices=["cosine", "l2"], default=None, help="override the workload's distance (SURVEY 8d: config 3 is also run with L2)")
     ap.add_argument("--path", default="auto", choices=["auto", "stream_fp32", "gemm_tf32"])
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (repeatable), e.g. gemm_wide=0")
     ap.add_argument("--no-cpu-baseline", action="store_true")
