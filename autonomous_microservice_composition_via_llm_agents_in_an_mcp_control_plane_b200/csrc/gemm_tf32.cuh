@@ -58,6 +58,10 @@ struct GemmArgs {
     unsigned int *arrive;      // [nqb]    CTAs of a query block that have published (zero when the launch starts)
     unsigned int *arrive_next; // [G_MAX_QBLOCKS] the other slot of the pair: this launch clears it for the next one
     unsigned int *drop_min;    // [nq] ordered image of the best coarse score the bootstrap tile may have dropped (all-ones: none); never NULL when boot_m > 0
+    u64 *progress;             // [ngroups][nqb] (launch epoch << 32 | tile index each CTA has started), or NULL: keeps the CTAs that
+                               // walk the same row tiles within `G_DRIFT` tiles of each other so that the tiles stay in L2
+    int drift;                 // tiles a CTA may run ahead of the slowest CTA of its group
+    uint32_t epoch;            // this launch's number: older entries in `progress` read as "not started"
     int boot_early;            // the bootstrap tile hands its accumulator back before the wait (large tables only, see gemm_tf32_run)
     int boot_m, boot_lists;    // lists 0 .. boot_lists-1 publish their boot_m-th smallest key (boot_lists even)
     const float *rows;         // table base + row pitch, for the L2 row prefetch
@@ -70,6 +74,8 @@ struct GemmArgs {
     int debug;                 // timing experiments only (results are wrong): 1 skip epilogue math, 2 skip row-tile loads, 4 skip query-tile loads, 8 skip MMAs
 };
 #define G_BOOT_MAX 4
+#define G_DRIFT 2
+#define G_MAX_GROUPS 160
 
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -292,6 +298,21 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t phase = 0;
         for (int i = 0; i < my_tiles; ++i) {
             const int t = group + i * ngroups;
+            if (a.progress) {
+                // The nqb CTAs of a group stream the same row tiles.  Left alone they drift apart by more tiles than L2 holds
+                // and each re-fetches the tile from HBM (measured: 21.6 GB read for 7.7 GB of table at config 3).  So each
+                // announces the tile it starts and waits until none of the others is more than a.drift tiles behind.
+                u64 *pg = a.progress + (size_t)group * a.nqb;
+                if (lane == 0) *(volatile u64 *)(pg + qb) = ((u64)a.epoch << 32) | (u64)(uint32_t)i;
+                if (i >= a.drift) {
+                    const u64 want = ((u64)a.epoch << 32) | (u64)(uint32_t)(i - a.drift);
+                    for (;;) {
+                        const u64 v = lane < a.nqb ? *(volatile u64 *)(pg + lane) : ~0ull;
+                        if (__all_sync(MCP_FULL, v >= want)) break;
+                        __nanosleep(100);
+                    }
+                }
+            }
             for (int kb = 0; kb < KB; ++kb) {
                 // DRAM locality: a TMA box touches 256 rows x 128 B, i.e. 256 different DRAM pages, and comes back to
                 // each page one k-block later, long after other tiles have closed it.  Every 8 k-blocks the query
@@ -336,6 +357,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
             }
         }
+        if (a.progress && lane == 0) *(volatile u64 *)(a.progress + (size_t)group * a.nqb + qb) = ((u64)a.epoch << 32) | 0xFFFFFFFFull;   // done: nobody waits for me
     } else if (warp == 1) {
         // ===== MMA issuer =====
         int stage = 0;
@@ -568,6 +590,9 @@ struct GemmPlan {
     int tmB_cluster = 0, tmB_bn = 0;
     bool balance_tiles = false; // option "gemm_balance" (measured: no gain -- at Q = 256 the tensor pipe is a co-bottleneck and shorter tiles waste MMA columns)
     int cluster_opt = 0;       // option "gemm_cluster": 0 = automatic, else force 1 / 2 / 4
+    bool coop_attr = true;     // option "gemm_coop"
+    int sync_tiles = G_DRIFT;  // option "gemm_sync": keep the CTAs of a group within this many tiles of each other (0 = off)
+    uint32_t epoch = 0;
     bool allow_pair = true;    // option "gemm_pair": clusters of 2 run as one tcgen05 CTA pair (cta_group::2)
     const float *rows = nullptr;
     int64_t n_rows = 0, ld = 0;
@@ -698,7 +723,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     // workspace: [arrive counters, two sets][lists][list counts][published bounds].  The counters sit first so that their
     // place does not move with the launch shape: a bootstrap launch uses one set (zero on entry) and clears the other for
     // the launch after it, which saves a memset node per search; only a new workspace is cleared from the host.
-    const size_t hdr = 256;
+    const size_t hdr = 256 + sizeof(u64) * G_MAX_GROUPS * G_MAX_QBLOCKS;   // arrive counter pair, then the progress words
     static_assert(2 * G_MAX_QBLOCKS * sizeof(unsigned int) <= 256, "arrive counter pair");
     const size_t list_bytes = sizeof(u64) * (size_t)nq * L * cap;
     const size_t cnt_off = (hdr + list_bytes + 255) & ~(size_t)255;
@@ -726,12 +751,20 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
         p.coop = (cudaDeviceGetAttribute(&v, cudaDevAttrCooperativeLaunch, dev) == cudaSuccess && v) ? 1 : 0;
     }
     a.drop_min = drop_min;
+    // progress words: only when several clusters share a group's tiles, every CTA is co-resident (the wait spins) and the
+    // table is large enough for drift to matter
+    a.progress = nullptr; a.epoch = 0; a.drift = G_DRIFT;
     a.boot_m = (!dump && drop_min && !(p.debug & (1 | 16 | 32)) && p.coop == 1 && m <= G_BOOT_MAX && nqb * ngroups <= n_sm && p.allow_boot) ? m : 0;
     a.boot_lists = boot_lists;
     // Early hand-back keeps only four rows per (query, half tile) of the first tile and lets the certificate account for the
     // rest (drop_min).  That is a good trade only when the bound sits far above the final top-k', i.e. when the rows the
     // bound was estimated from (boot_lists x 128) are a small part of the table; small tables re-read the tile instead.
     a.boot_early = (a.boot_m && n_rows >= (int64_t)16 * boot_lists * 128) ? 1 : 0;
+    if (a.boot_m && p.sync_tiles && nqb > C && ngroups <= G_MAX_GROUPS && n_rows * (int64_t)dim * 4 > (int64_t)64 << 20) {
+        a.progress = reinterpret_cast<u64 *>(wsb + 256);
+        a.epoch = ++p.epoch;
+        a.drift = p.sync_tiles;
+    }
     if (a.boot_m) {
         if (p.arrive_ws != (const void *)wsb || p.arrive_ws_cap != (size_t)ws.cap) {
             e = cudaMemsetAsync(wsb, 0, hdr, st);
@@ -743,15 +776,17 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
         p.arrive_slot ^= 1;
     }
     int nattr = C > 1 ? 1 : 0;
-    if (a.boot_m) { attrs[nattr].id = cudaLaunchAttributeCooperative; attrs[nattr].val.cooperative = 1; ++nattr; }
+    // option gemm_coop = 0 drops the cooperative attribute (profiling only: Nsight Compute cannot replay the cluster + cooperative
+    // launch; with one CTA per SM on an otherwise idle GPU the CTAs are co-resident anyway, but nothing guarantees it)
+    if (a.boot_m && p.coop_attr) { attrs[nattr].id = cudaLaunchAttributeCooperative; attrs[nattr].val.cooperative = 1; ++nattr; }
     cfg.numAttrs = nattr; cfg.gridDim = dim3(nqb * ngroups);
     void *kargs[3] = {(void *)&tmA, (void *)&p.tmB, (void *)&a};
     if (e == cudaSuccess) {
         // plain / cooperative launches keep their classic entry points: Nsight Compute (2025.2, driver 580) profiles those
         // fine, while the same kernel launched through cudaLaunchKernelExC with cluster + cooperative attributes faulted
-        // under it (never outside it); profiles/ therefore holds captures taken with option gemm_cluster = 1
+        // under it (never outside it): it is the cooperative attribute ncu trips over, so captures use option gemm_coop = 0 (profiles/r1i_summary.md)
         if (C > 1) e = cudaLaunchKernelExC(&cfg, func, kargs);
-        else if (a.boot_m) e = cudaLaunchCooperativeKernel(func, dim3(nqb * ngroups), dim3(threads), kargs, smem, st);
+        else if (a.boot_m && p.coop_attr) e = cudaLaunchCooperativeKernel(func, dim3(nqb * ngroups), dim3(threads), kargs, smem, st);
         else e = cudaLaunchKernel(func, dim3(nqb * ngroups), dim3(threads), kargs, smem, st);
     }
     if (e != cudaSuccess) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch (cluster %d, grid %d): %s", C, nqb * ngroups, cudaGetErrorString(e)); return -2; }

@@ -333,6 +333,11 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
     } else if (!strcmp(name, "gemm_cluster")) {
         if (value != 0 && value != 1 && value != 2 && value != 4) return fail(MCP_EINVAL, "gemm_cluster must be 0, 1, 2 or 4");
         idx->gemm.cluster_opt = (int)value;
+    } else if (!strcmp(name, "gemm_sync")) {
+        if (value < 0 || value > 64) return fail(MCP_EINVAL, "gemm_sync must be in [0, 64]");
+        idx->gemm.sync_tiles = (int)value;
+    } else if (!strcmp(name, "gemm_coop")) {
+        idx->gemm.coop_attr = value != 0;
     } else if (!strcmp(name, "gemm_pair")) {
         idx->gemm.allow_pair = value != 0;
     } else if (!strcmp(name, "gemm_debug")) {
