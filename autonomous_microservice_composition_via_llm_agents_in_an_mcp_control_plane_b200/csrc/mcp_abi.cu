@@ -111,8 +111,8 @@ struct mcp_index {
     // options
     int opt_path = MCP_PATH_AUTO, opt_kprime = 0, opt_max_fallback = 4, opt_time_coarse = 0;
     // workspace
-    Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, exact_key, exact_row, flags,
-        exact_all, out_ids, out_scores, out_scores64, gemm_ws, q_pad, nq2f, drop_min;
+    Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, flags,
+        exact_all, out_ids, gemm_ws, q_pad, nq2f, drop_min;
     int *h_status = nullptr;   // pinned + mapped: [0] certificate failures, [1] unresolved; written by the fallback kernel's status fold
     int *h_status_dev = nullptr;   // the same words as the device addresses them
     Buf slot_ticket;           // one ticket per fallback slot (zero between launches)
@@ -167,8 +167,8 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     cudaDeviceSynchronize();
     Buf *bufs[] = {&idx->own_rows, &idx->norm2, &idx->inv_norm, &idx->penalty, &idx->consts, &idx->q_copy,
                    &idx->nq2, &idx->inv_nq, &idx->qflag, &idx->scores, &idx->listsA, &idx->listsB, &idx->cntA,
-                   &idx->cntB, &idx->exact_key, &idx->exact_row, &idx->flags, &idx->exact_all, &idx->out_ids,
-                   &idx->out_scores, &idx->out_scores64, &idx->gemm_ws, &idx->q_pad, &idx->nq2f, &idx->drop_min, &idx->slot_ticket};
+                   &idx->cntB, &idx->flags, &idx->exact_all, &idx->out_ids,
+                   &idx->gemm_ws, &idx->q_pad, &idx->nq2f, &idx->drop_min, &idx->slot_ticket};
     for (Buf *b : bufs) b->release();
     for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
     if (idx->h_status) cudaFreeHost(idx->h_status);
