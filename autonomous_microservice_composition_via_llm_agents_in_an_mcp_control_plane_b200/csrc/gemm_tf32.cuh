@@ -74,7 +74,7 @@ struct GemmArgs {
     int debug;                 // timing experiments only (results are wrong): 1 skip epilogue math, 2 skip row-tile loads, 4 skip query-tile loads, 8 skip MMAs
 };
 #define G_BOOT_MAX 4
-#define G_DRIFT 2
+#define G_DRIFT 1
 #define G_MAX_GROUPS 160
 
 

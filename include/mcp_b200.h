@@ -153,7 +153,7 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
  * 128-query blocks, else 1 -- or 1 / 2 / 4),
  * "gemm_pair" (default 1 = a cluster of 2 runs as one tcgen05 CTA pair, cta_group::2 with M = 256; 0 = two M = 128
  * CTAs that multicast the row tile to each other),
- * "gemm_sync" (default 2: the CTAs of K2 that stream the same row tiles stay within this many tiles of each other, so the
+ * "gemm_sync" (default 1: the CTAs of K2 that stream the same row tiles stay within this many tiles of each other, so the
  * tiles are served from L2 instead of being re-read from HBM by every query block; 0 = off),
  * "gemm_coop" (default 1; 0 = launch K2 without the cooperative attribute -- for Nsight Compute captures only),
  * "gemm_debug" (bit mask for timing experiments that switch off parts of K2 / K4 -- results are WRONG; default 0),
