@@ -203,3 +203,25 @@ def test_table_file_format_round_trip(mcp, tmp_path):
     (tmp_path / "junk").write_bytes(b"x" * 100)
     with pytest.raises(ValueError):
         mcp.ServiceIndex.open_table(tmp_path / "junk")
+
+
+def test_bench_reference_arm_prints_one_contract_line():
+    """`bench.py --impl reference` runs on the host cores only (here, no GPU): one JSON line with the contract's keys."""
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", "reference", "--rows", "3000", "--queries", "16",
+                        "--topk", "8", "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "top-k retrieval queries/sec" and d["unit"] == "queries/s"
+    for key in ("value", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype",
+                "data", "config", "cpu_baseline", "e2e"):
+        assert key in d, key
+    assert d["cpu_baseline"]["kind"] in ("port", "reference") and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0 and d["value"] > 0
