@@ -594,6 +594,9 @@ struct GemmPlan {
     int sync_tiles = G_DRIFT;  // option "gemm_sync": keep the CTAs of a group within this many tiles of each other (0 = off)
     uint32_t epoch = 0;
     bool allow_pair = true;    // option "gemm_pair": clusters of 2 run as one tcgen05 CTA pair (cta_group::2)
+    bool mc_ok = false;        // the row table is memory this library allocated on this device: only such a table is read with
+                               // multicast loads (TMA multicast loads here read only this GPU's memory, since on B200 a TMA
+                               // multicast load from another GPU's memory hung the GPU); any other table takes plain loads
     const float *rows = nullptr;
     int64_t n_rows = 0, ld = 0;
     int dim = 0;
@@ -677,6 +680,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     if (nqb % C != 0 || dump || (p.debug & 2)) C = 1;
     // clusters of two run as one tcgen05 CTA pair (option gemm_pair, on by default) unless tiles are being balanced
     bool pair = C == 2 && MTsel == 1 && p.allow_pair;
+    if (C > 1 && !pair && !p.mc_ok) C = 1;           // the non-pair cluster shape multicasts the row tile: library-owned tables only
     const void *func = gemm_kernel_ptr(MTsel, kpl, metric, pair);
     if (pair) smem = sizeof(GemmSmemT<1, 1>) + 1024;
     e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -101,6 +101,29 @@ struct Buf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// Every byte of [p, p + bytes) must be plain device memory that lives on `device`: the kernels of an index -- and the
+// TMA tensor maps K2 builds over the table and the queries -- only ever read this GPU's memory.  (TMA multicast loads here
+// read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU.)  Peer
+// allocations, IPC imports and virtual ranges whose mappings reach another GPU report that GPU as their device; mappings
+// are made of >= 2 MiB granules, so one probe per 2 MiB boundary sees every mapping a range is stitched from.
+static int require_local(const void *p, size_t bytes, int device, const char *what) {
+    if (!p || !bytes) return MCP_OK;
+    const uintptr_t lo = (uintptr_t)p, hi = lo + bytes - 1, step = (uintptr_t)2 << 20;
+    for (uintptr_t a = lo;;) {
+        cudaPointerAttributes at;
+        cudaError_t e = cudaPointerGetAttributes(&at, (const void *)a);
+        if (e != cudaSuccess) { cudaGetLastError(); return fail(MCP_EINVAL, "%s: cudaPointerGetAttributes(%p) -> %s", what, (const void *)a, cudaGetErrorString(e)); }
+        if (at.type != cudaMemoryTypeDevice || at.device != device)
+            return fail(MCP_EINVAL, "%s: byte %llu of the buffer is not device memory of GPU %d (memory type %d, device %d); "
+                        "an index reads only its own GPU's memory -- copy remote shards in, or give each GPU its own index",
+                        what, (unsigned long long)(a - lo), device, (int)at.type, at.device);
+        if (a == hi) break;
+        const uintptr_t next = (a & ~(step - 1)) + step;
+        a = next > hi ? hi : next;
+    }
+    return MCP_OK;
+}
+
 struct mcp_index {
     int device = 0, dim = 0, metric = 0, n_sm = 148;
     int64_t n_rows = 0, ld = 0, id_base = 0;
@@ -184,6 +207,9 @@ extern "C" int64_t mcp_index_rows(const mcp_index *idx) { return idx ? idx->n_ro
 // K0 over the adopted / loaded rows; synchronous (load time).
 static int prepare_table(mcp_index *idx, cudaStream_t st) {
     int rc;
+    idx->gemm.valid = false;
+    // a cluster multicasts its row tiles only over a table this library allocated on this device itself
+    idx->gemm.mc_ok = idx->d_rows == idx->own_rows.as<float>();
     if ((rc = idx->norm2.ensure(sizeof(double) * (size_t)idx->n_rows))) return rc;
     if ((rc = idx->inv_norm.ensure(sizeof(float) * (size_t)idx->n_rows))) return rc;
     CU(cudaMemsetAsync(idx->consts.p, 0, sizeof(TableConsts), st));
@@ -197,7 +223,6 @@ static int prepare_table(mcp_index *idx, cudaStream_t st) {
     idx->has_penalty = false;
     if (idx->h_consts.bad_rows)
         return fail(MCP_EINVAL, "%u rows hold NaN/Inf elements (pgvector rejects these at input)", idx->h_consts.bad_rows);
-    idx->gemm.valid = false;
     return MCP_OK;
 }
 
@@ -207,6 +232,7 @@ extern "C" int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_
     if (n_rows >= (1ll << 31) || id_base < 0 || id_base + n_rows > (1ll << 31)) return fail(MCP_EINVAL, "ids must fit int32");
     std::lock_guard<std::mutex> lk(idx->mu);
     CU(cudaSetDevice(idx->device));
+    if (idx->pending) { CU(cudaEventSynchronize(idx->done)); }      // searches in flight read the old table and its norms
     int64_t ld = (idx->dim + 3) & ~3;                       // 16-byte rows; pad columns are zero
     int rc = idx->own_rows.ensure(sizeof(float) * (size_t)n_rows * (size_t)ld);
     if (rc) return rc;
@@ -227,6 +253,9 @@ extern "C" int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, 
     if (n_rows >= (1ll << 31) || id_base < 0 || id_base + n_rows > (1ll << 31)) return fail(MCP_EINVAL, "ids must fit int32");
     std::lock_guard<std::mutex> lk(idx->mu);
     CU(cudaSetDevice(idx->device));
+    int lrc = require_local(rows_device, sizeof(float) * ((size_t)(n_rows - 1) * (size_t)ld + (size_t)idx->dim), idx->device, "adopt_device rows");
+    if (lrc) return lrc;
+    if (idx->pending) { CU(cudaEventSynchronize(idx->done)); }      // searches in flight read the old table and its norms
     idx->own_rows.release();
     idx->d_rows = rows_device; idx->n_rows = n_rows; idx->ld = ld; idx->id_base = id_base;
     return prepare_table(idx, (cudaStream_t)stream);
@@ -309,7 +338,9 @@ extern "C" int mcp_index_set_penalty_device(mcp_index *idx, const float *penalty
     cudaStream_t st = (cudaStream_t)stream;
     if (idx->pending && idx->last_stream != st) { CU(cudaEventSynchronize(idx->done)); }
     if (!penalty_device) return clear_penalty(idx, st);
-    int rc = idx->penalty.ensure(sizeof(float) * (size_t)idx->n_rows);
+    int rc = require_local(penalty_device, sizeof(float) * (size_t)idx->n_rows, idx->device, "set_penalty_device");
+    if (rc) return rc;
+    rc = idx->penalty.ensure(sizeof(float) * (size_t)idx->n_rows);
     if (rc) return rc;
     CU(cudaMemcpyAsync(idx->penalty.p, penalty_device, sizeof(float) * (size_t)idx->n_rows, cudaMemcpyDeviceToDevice, st));
     return penalty_stats(idx, st);
@@ -668,6 +699,7 @@ extern "C" int mcp_index_search_device(mcp_index *idx, const float *queries_devi
     int rc = validate_search(idx, queries_device, n_queries, k, out_ids_device, out_scores_device);
     if (rc) return rc;
     CU(cudaSetDevice(idx->device));
+    if ((rc = require_local(queries_device, sizeof(float) * (size_t)n_queries * idx->dim, idx->device, "search_device queries"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     if ((rc = order_after_previous(idx, st))) return rc;
     rc = search_locked(idx, queries_device, n_queries, k, out_ids_device, out_scores_device, out_scores64_device, st);
@@ -769,6 +801,7 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     CU(cudaSetDevice(idx->device));
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
+    if ((rc = require_local(queries_device, sizeof(float) * (size_t)n_queries * idx->dim, idx->device, "coarse_scores queries"))) return rc;
     if ((rc = order_after_previous(idx, st))) return rc;
     const int dim = idx->dim;
     if ((rc = idx->nq2.ensure(sizeof(double) * n_queries))) return rc;
@@ -952,6 +985,7 @@ extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float
     unsigned char *base = nullptr;
     int rc = noalloc_scratch_for(idx->device, &base);
     if (rc) return rc;
+    if ((rc = require_local(queries_device, sizeof(float) * (size_t)n_queries * idx->dim, idx->device, "search_exact_noalloc queries"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     // carve the array: [scores | nq2 (64 f64) | inv_nq (64 f32) | qflag (64 B) | n_flag + flag list (ints)]
     u64 *scores = reinterpret_cast<u64 *>(base);

@@ -76,7 +76,12 @@ int mcp_index_destroy(mcp_index *idx);
  * service_schemas.input_schema_vector: rows are the N x dim fp32 vectors in table order.
  * load copies host rows to the device; adopt uses caller-owned device memory in place
  * (row pitch `ld` floats, ld >= dim, ld % 4 == 0, base 16-byte aligned; the caller keeps it
- * alive and unmodified until destroy or the next load/adopt).  Both compute per-row fp64
+ * alive and unmodified until destroy or the next load/adopt).  The adopted range, like every
+ * other device pointer handed to an index (queries, penalty), must be ordinary device memory of
+ * the index's own GPU from its first byte to its last: peer allocations, IPC imports, managed
+ * memory and virtual ranges with a mapping on another GPU are refused with MCP_EINVAL.  (The
+ * kernels and the TMA tensor maps K2 builds over these buffers read this GPU's memory only; a
+ * sharded registry gives every GPU its own index over its own rows.)  Both compute per-row fp64
  * squared norms and reject NaN/Inf elements (pgvector rejects them at input).
  * id_base is the service id of row 0 (a row shard of a larger table passes its offset).     */
 int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_rows, int64_t id_base);
@@ -152,7 +157,8 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
  * "gemm_cluster" (CTAs per cluster that share a row tile: 0 = automatic -- 2 when the batch has an even number of
  * 128-query blocks, else 1 -- or 1 / 2 / 4),
  * "gemm_pair" (default 1 = a cluster of 2 runs as one tcgen05 CTA pair, cta_group::2 with M = 256; 0 = two M = 128
- * CTAs that multicast the row tile to each other),
+ * CTAs that multicast the row tile to each other -- on tables made by mcp_index_load only: over adopted memory the
+ * non-pair shapes run as single CTAs with plain loads, multicast being kept to memory the library allocated itself),
  * "gemm_sync" (default 1: the CTAs of K2 that stream the same row tiles stay within this many tiles of each other, so the
  * tiles are served from L2 instead of being re-read from HBM by every query block; 0 = off),
  * "gemm_coop" (default 1; 0 = launch K2 without the cooperative attribute -- for Nsight Compute captures only),
