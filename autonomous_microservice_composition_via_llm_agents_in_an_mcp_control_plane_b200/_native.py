@@ -14,7 +14,7 @@ LIB_PATH: Path = _build.OUT
 _lib = None
 
 METRIC_COSINE, METRIC_L2 = 0, 1
-PATH_AUTO, PATH_STREAM_FP32, PATH_GEMM_TF32, PATH_EXACT_FP64 = 0, 1, 2, 3
+PATH_AUTO, PATH_STREAM_FP32, PATH_GEMM_TF32, PATH_EXACT_FP64, PATH_GEMM_F16 = 0, 1, 2, 3, 4
 MAX_K = 256
 MAX_DAG_NODES = 64
 NOALLOC_MAX_ROWS, NOALLOC_MAX_QUERIES = 1 << 20, 64

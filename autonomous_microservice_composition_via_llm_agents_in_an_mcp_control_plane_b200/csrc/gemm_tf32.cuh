@@ -1,5 +1,12 @@
-// gemm_tf32.cuh -- K2: tcgen05 / TMEM TF32 distance GEMM with the telemetry score and the
-// top-k' filter fused into the epilogue (large query batches).
+// gemm_tf32.cuh -- K2: tcgen05 / TMEM distance GEMM with the telemetry score and the
+// top-k' filter fused into the epilogue (large query batches).  Two operand kinds, one kernel:
+//   kind 0 (tf32): the fp32 table rows themselves, consumed by kind::tf32 MMAs straight from shared memory;
+//   kind 1 (f16):  the fp16 shadow of the table (prep.cuh shadow_rows_kernel: every row scaled by a power of two into fp16's
+//                  range, 11 bits kept -- one more than tf32 keeps) and fp16 images of the queries, consumed by kind::f16
+//                  MMAs at twice the tensor rate and half the bytes.  A 128-byte k-block then holds 64 elements instead
+//                  of 32; tile bytes, swizzle, descriptors and the +32 B step per MMA (K = 16 instead of 8) are the same,
+//                  so the two kinds share everything but the instruction and the element count per k-block.  The scales
+//                  are undone in the epilogue (folded into the inverse norms; one more multiply for L2).
 //
 //   D[128 queries x 256 rows] (fp32, TMEM) += Q[128 x 32] (smem, K-major) * E[256 x 32]^T (smem, K-major)
 //
@@ -71,6 +78,11 @@ struct GemmArgs {
     int cluster;               // CTAs per cluster (1, 2 or 4): the query-block CTAs that share a row tile load a slice each and multicast it
     uint32_t idesc_pair;       // pair mode: instruction descriptor with N = bn
     int pair;                  // cluster == 2 only: the two CTAs run ONE tcgen05.mma.cta_group::2 (M = 256) instead of two multicast-fed M = 128 MMAs
+    int kind;                  // 0: fp32 operands read as tf32 (kind::tf32, K = 8 per MMA); 1: fp16 operands (kind::f16, K = 16 per MMA)
+    int ek;                    // elements per 128-byte k-block: 32 (tf32) or 64 (f16)
+    const float *q_scale_inv;  // kind 1: [nq] 1 / (power-of-two scale of the query's fp16 image)
+    const float *row_scale_inv;// kind 1: [n_rows] the same per shadow row
+    uint32_t idesc_single;     // instruction descriptor of the single-CTA MMA (M = 128, N = 256) for this kind
     int debug;                 // timing experiments only (results are wrong): 1 skip epilogue math, 2 skip row-tile loads, 4 skip query-tile loads, 8 skip MMAs
 };
 #define G_BOOT_MAX 4
@@ -121,6 +133,20 @@ __device__ __forceinline__ void tc_mma_tf32_pair(uint32_t d_tmem, u64 adesc, u64
         "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ void tc_mma_f16_pair(uint32_t d_tmem, u64 adesc, u64 bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t d_tmem, u64 adesc, u64 bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
 // arrive on the mbarrier at this offset in CTA `rank` of the cluster
 __device__ __forceinline__ void mbar_arrive_remote(u64 *bar, uint32_t rank) {
     asm volatile(
@@ -157,9 +183,12 @@ __device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sy
 __device__ __forceinline__ u64 umma_desc_k128(const void *tile) {
     return (u64)((smem_u32(tile) & 0x3FFFF) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
-// instruction descriptor (cute::UMMA::InstrDescriptor): c F32 (1<<4), a/b TF32 (2<<7, 2<<10), both K-major,
-// N >> 3 at [17,23), M >> 4 at [24,29)
-#define G_IDESC ((1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(G_BN >> 3) << 17) | ((uint32_t)(G_BM >> 4) << 24))
+// instruction descriptor (cute::UMMA::InstrDescriptor): c F32 (1<<4), a/b format at [7,10) / [10,13) (TF32 = 2 under
+// kind::tf32, F16 = 0 under kind::f16), both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
+static inline uint32_t g_idesc(int kind, int m, int n) {
+    const uint32_t fmt = kind ? 0u : 2u;
+    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
 
 // K2 lists store raw pairs (fp32 score bits << 32 | row); selection works on the ordered image
 __device__ __forceinline__ u64 raw_to_key(u64 raw) { return ((u64)f32_ord(__uint_as_float((uint32_t)(raw >> 32))) << 32) | (raw & 0xFFFFFFFFull); }
@@ -230,6 +259,7 @@ template <int MT, int PAIR = 0> struct GemmSmemT {
     float a[GemmCfg<MT, PAIR>::STAGES][MT * G_BM * G_BK];
     float b[GemmCfg<MT, PAIR>::STAGES][GemmCfg<MT, PAIR>::B_ROWS * G_BK];
     float2 meta[2][G_BN];      // per row of the tile: (inv|e| or |e|^2, penalty)
+    float mscale[2][G_BN];     // kind 1, L2 metric: 1 / (the shadow row's power-of-two scale)
     u64 full[GemmCfg<MT, PAIR>::STAGES], empty[GemmCfg<MT, PAIR>::STAGES], tfull[2], tempty[2];
     uint32_t tmem_base;
 };
@@ -248,7 +278,8 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int BN = a.bn;                                       // rows per tile; the MMA is always N = 256, columns >= BN are ignored
     const int n_tiles = (int)((a.n_rows + BN - 1) / BN);
     const int my_tiles = group < n_tiles ? (n_tiles - group + ngroups - 1) / ngroups : 0;
-    const int KB = (a.dim + G_BK - 1) / G_BK;
+    const int EK = a.ek;                                       // elements per k-block (128 bytes of a row)
+    const int KB = (a.dim + EK - 1) / EK;
     constexpr int CAP = KPL * 32;
 
     // Cluster of C query-block CTAs that work on the same row tiles: each loads 256 / C rows of the tile and multicasts
@@ -318,7 +349,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 // each page one k-block later, long after other tiles have closed it.  Every 8 k-blocks the query
                 // block 0 CTA therefore pulls the *next* 1 KB of each of the tile's rows into L2 with one bulk prefetch
                 // per row (8 rows per lane): DRAM sees 1 KB bursts, the TMA boxes that follow hit L2.
-                if (a.l2_prefetch && qb == 0 && (kb & 7) == 0) {
+                if (a.l2_prefetch && a.kind == 0 && qb == 0 && (kb & 7) == 0) {
                     int pt = t, pk = kb + 8;
                     if (pk >= KB) { pt = t + ngroups; pk = 0; }
                     if (pt < n_tiles) {
@@ -338,16 +369,16 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     if constexpr (pair) {
                         // both halves of the pair report to the leader's barrier, which expects the bytes of both
                         if (leader) mbar_expect_tx(&s.full[stage], 2 * ((la ? Cfg::A_BYTES : 0) + (lb ? (BN / 2) * G_BK * 4 : 0)));
-                        if (la) tma_load_2d_pair(s.a[stage], &tmA, kb * G_BK, qb * G_BM, &s.full[stage]);
-                        if (lb) tma_load_2d_pair(s.b[stage], &tmB, kb * G_BK, t * BN + (int)crank * (BN / 2), &s.full[stage]);
+                        if (la) tma_load_2d_pair(s.a[stage], &tmA, kb * EK, qb * G_BM, &s.full[stage]);
+                        if (lb) tma_load_2d_pair(s.b[stage], &tmB, kb * EK, t * BN + (int)crank * (BN / 2), &s.full[stage]);
                     } else {
                     mbar_expect_tx(&s.full[stage], (la ? Cfg::A_BYTES : 0) + (lb ? BN * G_BK * 4 : 0));
-                    if (la) tma_load_2d(s.a[stage], &tmA, kb * G_BK, qb * MT * G_BM, &s.full[stage]);
+                    if (la) tma_load_2d(s.a[stage], &tmA, kb * EK, qb * MT * G_BM, &s.full[stage]);
                     if (lb) {
-                        if (C == 1) tma_load_2d(s.b[stage], &tmB, kb * G_BK, t * BN, &s.full[stage]);
+                        if (C == 1) tma_load_2d(s.b[stage], &tmB, kb * EK, t * BN, &s.full[stage]);
                         else {                                 // my slice of the tile, to everyone in the cluster
                             const int srows = BN / C;
-                            tma_load_2d_mc(s.b[stage] + (size_t)crank * srows * G_BK, &tmB, kb * G_BK, t * BN + (int)crank * srows,
+                            tma_load_2d_mc(s.b[stage] + (size_t)crank * srows * G_BK, &tmB, kb * EK, t * BN + (int)crank * srows,
                                            &s.full[stage], cmask);
                         }
                     }
@@ -378,9 +409,16 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                         for (int mt = 0; mt < MT; ++mt) {     // query block mt: A rows 128*mt.. (16 KB further), accumulator columns 256*mt..
                             if ((a.debug & 8) && k != 0) continue;
-                            if constexpr (pair) tc_mma_tf32_pair(d_tmem, ad + (u64)(2 * k), bd + (u64)(2 * k), a.idesc_pair, (uint32_t)((kb | k) != 0));
-                            else tc_mma_tf32(d_tmem + (uint32_t)(mt * G_BN), ad + (u64)(2 * k) + (u64)(mt * (G_A_BYTES >> 4)),
-                                             bd + (u64)(2 * k), G_IDESC, (uint32_t)((kb | k) != 0));
+                            const uint32_t accum = (uint32_t)((kb | k) != 0);
+                            if constexpr (pair) {
+                                if (a.kind) tc_mma_f16_pair(d_tmem, ad + (u64)(2 * k), bd + (u64)(2 * k), a.idesc_pair, accum);
+                                else tc_mma_tf32_pair(d_tmem, ad + (u64)(2 * k), bd + (u64)(2 * k), a.idesc_pair, accum);
+                            } else {
+                                const uint32_t dd = d_tmem + (uint32_t)(mt * G_BN);
+                                const u64 aa = ad + (u64)(2 * k) + (u64)(mt * (G_A_BYTES >> 4));
+                                if (a.kind) tc_mma_f16(dd, aa, bd + (u64)(2 * k), a.idesc_single, accum);
+                                else tc_mma_tf32(dd, aa, bd + (u64)(2 * k), a.idesc_single, accum);
+                            }
                         }
                     }
                     if constexpr (pair) tc_commit_pair(&s.empty[stage]); // frees the stage in both CTAs
@@ -400,8 +438,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int m = quarter * 32 + lane;
         const int qg = (qb * MT + mt) * G_BM + m;
         const bool qvalid = qg < a.nq;
-        const float inq = qvalid ? a.inv_nq[qg] : 0.f;
+        // kind 1: the accumulator is (s_q q^).(s_r e^); 1 / s_q is folded into the query's inverse norm here, 1 / s_r into the
+        // row's as the tile's constants are staged (powers of two: exact); the L2 form undoes both on the dot product
+        const float qsi = (qvalid && a.kind) ? a.q_scale_inv[qg] : 1.f;
+        const float inq = qvalid ? a.inv_nq[qg] * qsi : 0.f;
         const float nq2f = qvalid ? a.nq2f[qg] : 0.f;
+        const float m2q = -2.0f * qsi;
         const int et = threadIdx.x - 64;                       // 0 .. EPI_THREADS-1
         const int L = 2 * ngroups, li = 2 * group + half;      // one list per (CTA, query, half)
         u64 *mylist = a.lists + ((int64_t)(qvalid ? qg : 0) * L + li) * CAP;
@@ -412,30 +454,65 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if constexpr (pair) { if (leader) mbar_arrive(&s.tempty[buf]); else mbar_arrive_remote(&s.tempty[buf], 0u); }
             else mbar_arrive(&s.tempty[buf]);
         };
-        auto score = [&](float acc, float2 mm) -> float {
+        auto score = [&](float acc, int mb, int r) -> float {
+            const float2 mm = s.meta[mb][r];
             if (METRIC == 0) return fmaf(-(acc * inq), mm.x, 1.0f) + mm.y;
+            if (a.kind) acc *= s.mscale[mb][r];
             // sqrt.approx (one MUFU, max relative error 2^-23) instead of the IEEE sqrtf sequence: every lane scores every
             // element, so the epilogue's instruction count is what the L2 metric pays for; the extra ulp is inside the
             // 8-ulp allowance the certificate already makes for the square root and the final add (CertParams::abs_pen)
-            float r;
-            asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(fmaxf(nq2f + mm.x - 2.0f * acc, 0.f)));
-            return r + mm.y;
+            float rt;
+            asm("sqrt.approx.f32 %0, %1;" : "=f"(rt) : "f"(fmaxf(fmaf(m2q, acc, nq2f + mm.x), 0.f)));
+            return rt + mm.y;
         };
+        // my four smallest keys so far: found by the bootstrap pass over the first tile and, when the bootstrap hands its tile back
+        // early (large tables), kept current by the filter pass, so that the shared bound can be tightened as the scan goes on
+        u64 b0 = ~0ull, b1 = ~0ull, b2 = ~0ull, b3 = ~0ull;
+        const bool refresh = a.boot_m > 0 && a.boot_early;
+        // per-row constants of a tile, fetched one tile ahead so that their global-load latency hides under the previous
+        // tile's epilogue instead of sitting in front of the barrier below.  Rows past the table get +inf.
+        auto fetch_meta = [&](int ii, float &m0, float &m1, float &rs) {
+            m0 = 0.f; m1 = CUDART_INF_F; rs = 1.f;
+            const int64_t row = (int64_t)(group + ii * ngroups) * BN + et;
+            if (et < BN && ii < my_tiles && row < a.n_rows) {
+                if (a.kind) rs = a.row_scale_inv[row];
+                m0 = METRIC == 0 ? a.inv_ne[row] * rs : (float)a.ne2[row];
+                m1 = a.penalty ? a.penalty[row] : 0.f;
+            }
+        };
+        float nm0, nm1, nrs;
+        fetch_meta(0, nm0, nm1, nrs);
         for (int i = 0; i < my_tiles; ++i) {
             const int t = group + i * ngroups, buf = i % Cfg::NBUF, mbuf = i & 1;
             const uint32_t tphase = (uint32_t)(i / Cfg::NBUF) & 1u;
             const int64_t row0 = (int64_t)t * BN;
             const int rows_here = (int)min((int64_t)BN, a.n_rows - row0);
-            // per-row constants of this tile (meta[mbuf] was last read two tiles ago; the named barrier of the
-            // tile in between ordered those reads before these writes).  Rows past the table get +inf.
+            // meta[mbuf] was last read two tiles ago; the named barrier of the tile in between ordered those reads before
+            // these writes
             if (et < G_BN) {
-                const int r = et;
-                float m0 = 0.f, m1 = CUDART_INF_F;
-                if (r < rows_here) {
-                    m0 = METRIC == 0 ? a.inv_ne[row0 + r] : (float)a.ne2[row0 + r];
-                    m1 = a.penalty ? a.penalty[row0 + r] : 0.f;
+                s.meta[mbuf][et] = make_float2(nm0, nm1);
+                if (METRIC == 1) s.mscale[mbuf][et] = nrs;
+            }
+            fetch_meta(i + 1, nm0, nm1, nrs);
+            if (refresh && i > 0 && (i & (i - 1)) == 0 && qvalid) {
+                // Tighten the shared bound at tiles 1, 2, 4, 8 ...: each publishing list re-publishes its boot_m-th smallest key
+                // (it only ever decreases) and every list takes the maximum of what is published.  Any such maximum has at
+                // least boot_lists * boot_m >= k' keys of the union at or below it, whichever mix of older and newer values
+                // it is read from, so nothing is waited for.  A list's own threshold never drops below its own boot_m-th
+                // smallest key (it is part of the maximum), so every row that belongs among its four smallest is appended and
+                // seen by the insertion below.  After n rows per list the bound sits near the (2 boot_m / n) quantile, so a
+                // list collects a few dozen rows over the whole scan instead of filling up and being pruned again and again
+                // (the prunes -- one warp selecting while seven wait at the tile barrier -- were 60 % of the epilogue).
+                const u64 mine = a.boot_m == 1 ? b0 : a.boot_m == 2 ? b1 : a.boot_m == 3 ? b2 : b3;
+                u64 *pq = a.pub + (int64_t)qg * a.boot_lists;
+                if (li < a.boot_lists) pq[li] = mine;
+                u64 t0 = 0;
+                const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(pq);
+                for (int l = 0; l < a.boot_lists / 2; ++l) {
+                    const ulonglong2 x = __ldcg(pp + l);
+                    t0 = x.x > t0 ? x.x : t0; t0 = x.y > t0 ? x.y : t0;
                 }
-                s.meta[mbuf][r] = make_float2(m0, m1);
+                if (t0 != ~0ull) tau_f = fminf(tau_f, ord_f32((uint32_t)(t0 >> 32)));   // a NaN bound changes nothing
             }
             asm volatile("bar.sync 1, %0;" ::"n"(Cfg::EPI_THREADS) : "memory");
             mbar_wait(&s.tfull[buf], tphase);
@@ -464,7 +541,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     for (int j = 0; j < 32; ++j) {
                         const int r = cbase + c + j;
                         if (qvalid && r < rows_here)
-                            a.dump[(int64_t)qg * a.n_rows + row0 + r] = score(__uint_as_float(v[j]), s.meta[mbuf][r]);
+                            a.dump[(int64_t)qg * a.n_rows + row0 + r] = score(__uint_as_float(v[j]), mbuf, r);
                     }
                 }
                 tc_fence_before();
@@ -474,7 +551,6 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (i == 0 && a.boot_m > 0) {
                 // ---- bootstrap pass over the first tile: my m smallest keys, publish, wait, take the max ----
                 // four smallest keys in scalars (an indexed array ends up in local memory)
-                u64 b0 = ~0ull, b1 = ~0ull, b2 = ~0ull, b3 = ~0ull;
                 float best_f = CUDART_NAN_F;                   // NaN: nothing is rejected until 4 keys are held
                 for (int c = 0; c < 128 && cbase + c < rows_here; c += 32) {
                     uint32_t v[32];
@@ -483,7 +559,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const int r = cbase + c + j;
-                        const float sc = score(__uint_as_float(v[j]), s.meta[mbuf][r]);
+                        const float sc = score(__uint_as_float(v[j]), mbuf, r);
                         if (!(sc > best_f)) {
                             const u64 key = coarse_key(sc, (uint32_t)(row0 + r));
                             if (r < rows_here && key < b3) {
@@ -543,12 +619,32 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 uint32_t v[32];
                 tc_ld_32x32(taddr + (uint32_t)c, v);
                 tc_ld_wait();
+                // score all 32 first and only then look for survivors: once the shared bound has tightened, whole chunks pass
+                // without one, and the loop below (a branch, a store and the four-smallest insertion per element) is skipped
+                bool any = false;
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    const int r = cbase + c + j;
-                    const float sc = score(__uint_as_float(v[j]), s.meta[mbuf][r]);
-                    if (!(sc > tau_f)) {                       // at or below the threshold, or NaN
-                        if (qvalid && r < rows_here) mylist[cnt++] = ((u64)__float_as_uint(sc) << 32) | (u64)(uint32_t)(row0 + r);
+                    const float sc = score(__uint_as_float(v[j]), mbuf, cbase + c + j);
+                    v[j] = __float_as_uint(sc);
+                    any |= !(sc > tau_f);                      // at or below the threshold, or NaN
+                }
+                if (any) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int r = cbase + c + j;
+                        const float sc = __uint_as_float(v[j]);
+                        if (!(sc > tau_f) && qvalid && r < rows_here) {
+                            mylist[cnt++] = ((u64)v[j] << 32) | (u64)(uint32_t)(row0 + r);
+                            if (refresh) {
+                                const u64 key = coarse_key(sc, (uint32_t)(row0 + r));
+                                if (key < b3) {
+                                    b3 = key;
+                                    if (b3 < b2) { const u64 x = b3; b3 = b2; b2 = x; }
+                                    if (b2 < b1) { const u64 x = b2; b2 = b1; b1 = x; }
+                                    if (b1 < b0) { const u64 x = b1; b1 = b0; b0 = x; }
+                                }
+                            }
+                        }
                     }
                 }
                 // a list within 32 of its capacity is cut back to k' (every chunk appends at most 32)
@@ -597,9 +693,9 @@ struct GemmPlan {
     bool mc_ok = false;        // the row table is memory this library allocated on this device: only such a table is read with
                                // multicast loads (TMA multicast loads here read only this GPU's memory, since on B200 a TMA
                                // multicast load from another GPU's memory hung the GPU); any other table takes plain loads
-    const float *rows = nullptr;
+    const void *rows = nullptr;
     int64_t n_rows = 0, ld = 0;
-    int dim = 0;
+    int dim = 0, kind = -1;
     PFN_encodeTiled encode = nullptr;
     int coop = -1;             // device supports cooperative launch (-1 = not asked yet)
     const void *arrive_ws = nullptr;   // workspace (pointer, capacity) whose arrive-counter pair is known to be initialised
@@ -608,13 +704,16 @@ struct GemmPlan {
     bool allow_boot = true;    // option "gemm_bootstrap"
     bool l2_prefetch = false;  // option "gemm_l2_prefetch"
     int debug = 0;             // option "gemm_debug" (timing experiments, wrong results)
-    bool allow_wide = false;    // option "gemm_wide": 256-query CTAs when there are more than 128 queries
     char err[256] = {0};
 };
 
-static inline bool gemm_supported(int dim, int64_t ld) { return (dim % 4) == 0 && (ld % 4) == 0 && dim >= 4; }
+// a TMA tensor map needs a 16-byte aligned base and row pitch; the innermost extent (dim) is free -- columns past it read as zero
+static inline bool gemm_supported(int kind, const void *base, int64_t ld) {
+    const int64_t pitch = ld * (kind ? 2 : 4);
+    return base && (pitch % 16) == 0 && (((uintptr_t)base) & 15) == 0;
+}
 
-static int gemm_encode_2d(GemmPlan &p, CUtensorMap *tm, const float *base, int64_t rows, int dim, int64_t ld, int box_rows) {
+static int gemm_encode_2d(GemmPlan &p, CUtensorMap *tm, int kind, const void *base, int64_t rows, int dim, int64_t ld, int box_rows) {
     if (!p.encode) {
         void *fn = nullptr;
         cudaDriverEntryPointQueryResult qres;
@@ -626,10 +725,10 @@ static int gemm_encode_2d(GemmPlan &p, CUtensorMap *tm, const float *base, int64
         p.encode = (PFN_encodeTiled)fn;
     }
     cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)rows};
-    cuuint64_t gstride[1] = {(cuuint64_t)ld * 4};
-    cuuint32_t box[2] = {G_BK, (cuuint32_t)box_rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * (kind ? 2 : 4)};
+    cuuint32_t box[2] = {(cuuint32_t)(kind ? 2 * G_BK : G_BK), (cuuint32_t)box_rows};     // 128 bytes of a row x box_rows rows
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = p.encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)base, gdim, gstride, box, estr,
+    CUresult r = p.encode(tm, kind ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)base, gdim, gstride, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -645,7 +744,7 @@ static inline int gemm_max_kprime() { return 256; }
 
 static const void *gemm_kernel_ptr(int mt, int kpl, int metric, bool pair) {
 #define G_PICK(MTV, KPL, PR) (metric == 0 ? (const void *)gemm_tf32_kernel<MTV, KPL, 0, PR> : (const void *)gemm_tf32_kernel<MTV, KPL, 1, PR>)
-    if (mt == 2) return kpl == 4 ? G_PICK(2, 4, 0) : kpl == 8 ? G_PICK(2, 8, 0) : G_PICK(2, 16, 0);
+    (void)mt;                                        // 256-query CTAs (MT = 2) measured slower and are no longer instantiated
     if (pair) return kpl == 4 ? G_PICK(1, 4, 1) : kpl == 8 ? G_PICK(1, 8, 1) : G_PICK(1, 16, 1);
     return kpl == 4 ? G_PICK(1, 4, 0) : kpl == 8 ? G_PICK(1, 8, 0) : G_PICK(1, 16, 0);
 #undef G_PICK
@@ -653,26 +752,31 @@ static const void *gemm_kernel_ptr(int mt, int kpl, int metric, bool pair) {
 
 // One launch over <= G_MAX_QBLOCKS * 128 queries.  Lists come back as [nq][L][cap] in `ws`.
 // Returns 0, or a negative MCP_E* code with the message in plan.err.
+// kind 0: rows / queries are fp32 with pitches ld / ldq floats; kind 1: scaled fp16 images with pitches in fp16 elements
+// and their inverse scales in q_scale_inv [nq] / row_scale_inv [n_rows].
 template <class BufT>
-static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const float *rows, int64_t n_rows, int dim,
-                         int64_t ld, const float *queries, int nq, const float *inv_nq, const float *nq2f,
+static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int kind, const void *rows, int64_t n_rows, int dim,
+                         int64_t ld, const void *queries, int64_t ldq, int nq, const float *inv_nq, const float *nq2f,
                          const float *inv_ne, const double *ne2, const float *penalty, int metric, int kprime,
                          u64 **out_lists, int **out_cnt, int *out_L, int *out_cap, float *dump = nullptr,
-                         unsigned int *drop_min = nullptr /* [nq], all-ones on entry: enables the cross-CTA bootstrap */) {
-    if (!gemm_supported(dim, ld)) { snprintf(p.err, sizeof p.err, "gemm_tf32 needs dim %% 4 == 0 (dim %d, ld %lld)", dim, (long long)ld); return -1; }
+                         unsigned int *drop_min = nullptr /* [nq], all-ones on entry: enables the cross-CTA bootstrap */,
+                         const float *q_scale_inv = nullptr, const float *row_scale_inv = nullptr) {
+    if (!gemm_supported(kind, rows, ld) || !gemm_supported(kind, queries, ldq)) {
+        snprintf(p.err, sizeof p.err, "gemm scan needs 16-byte aligned operands and row pitches (kind %d, ld %lld, ldq %lld)", kind, (long long)ld, (long long)ldq);
+        return -1;
+    }
     if (kprime > gemm_max_kprime()) { snprintf(p.err, sizeof p.err, "gemm_tf32 keeps at most %d candidates (asked %d)", gemm_max_kprime(), kprime); return -1; }
     if (nq > G_MAX_QBLOCKS * G_BM) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch takes at most %d queries", G_MAX_QBLOCKS * G_BM); return -1; }
-    // 256-query CTAs (option gemm_wide) or 128-query CTAs
-    const int MTsel = (nq > G_BM && p.allow_wide) ? 2 : 1;
+    const int MTsel = 1;                                         // 128-query CTAs
     CUtensorMap tmA;
-    int rc = gemm_encode_2d(p, &tmA, queries, nq, dim, dim, MTsel * G_BM);
+    int rc = gemm_encode_2d(p, &tmA, kind, queries, nq, dim, ldq, MTsel * G_BM);
     if (rc) return rc;
     const int nqb = (nq + MTsel * G_BM - 1) / (MTsel * G_BM);
     int n_tiles = (int)((n_rows + G_BN - 1) / G_BN);
     int ngroups = std::max(1, std::min(n_sm / nqb, n_tiles));
     const int kpl = gemm_kpl_for(kprime), cap = kpl * 32;
-    size_t smem = (MTsel == 2 ? sizeof(GemmSmemT<2>) : sizeof(GemmSmemT<1>)) + 1024;
-    const int threads = MTsel == 2 ? GemmCfg<2>::THREADS : GemmCfg<1>::THREADS;
+    size_t smem = sizeof(GemmSmemT<1>) + 1024;
+    const int threads = GemmCfg<1>::THREADS;
     cudaError_t e = cudaSuccess;
     // cluster size: pairs of query-block CTAs share (multicast) their row tiles.  Measured on config 3's per-GPU share:
     // C = 1 7.37 ms, C = 2 6.78 ms, C = 4 6.88 ms (clusters of 4 leave SMs idle: a cluster must fit inside one GPC)
@@ -719,9 +823,9 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     if (!p.balance_tiles) bn = G_BN;
     n_tiles = (int)((n_rows + bn - 1) / bn);
     ngroups = std::max(1, std::min(ngroups, n_tiles));
-    if (!p.valid || p.rows != rows || p.n_rows != n_rows || p.ld != ld || p.dim != dim || p.tmB_cluster != C || p.tmB_bn != bn) {
-        if ((rc = gemm_encode_2d(p, &p.tmB, rows, n_rows, dim, ld, bn / C))) return rc;
-        p.rows = rows; p.n_rows = n_rows; p.ld = ld; p.dim = dim; p.tmB_cluster = C; p.tmB_bn = bn; p.valid = true;
+    if (!p.valid || p.rows != rows || p.n_rows != n_rows || p.ld != ld || p.dim != dim || p.tmB_cluster != C || p.tmB_bn != bn || p.kind != kind) {
+        if ((rc = gemm_encode_2d(p, &p.tmB, kind, rows, n_rows, dim, ld, bn / C))) return rc;
+        p.rows = rows; p.n_rows = n_rows; p.ld = ld; p.dim = dim; p.tmB_cluster = C; p.tmB_bn = bn; p.kind = kind; p.valid = true;
     }
     const int L = 2 * ngroups;                       // one list per (CTA, query, half tile)
     // workspace: [arrive counters, two sets][lists][list counts][published bounds].  The counters sit first so that their
@@ -743,9 +847,13 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     a.pub = reinterpret_cast<u64 *>(wsb + pub_off);
     a.arrive = nullptr; a.arrive_next = nullptr;
     a.dump = dump;
-    a.rows = rows; a.ld = ld; a.l2_prefetch = p.l2_prefetch ? 1 : 0; a.debug = p.debug; a.cluster = C; a.bn = bn;
+    a.rows = kind ? nullptr : (const float *)rows; a.ld = ld; a.l2_prefetch = (p.l2_prefetch && !kind) ? 1 : 0; a.debug = p.debug; a.cluster = C; a.bn = bn;
     a.pair = pair ? 1 : 0;
-    a.idesc_pair = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)((2 * G_BM) >> 4) << 24);
+    a.kind = kind; a.ek = kind ? 2 * G_BK : G_BK;
+    a.q_scale_inv = q_scale_inv; a.row_scale_inv = row_scale_inv;
+    if (kind && (!q_scale_inv || !row_scale_inv)) { snprintf(p.err, sizeof p.err, "fp16 scan without operand scales"); return -1; }
+    a.idesc_single = g_idesc(kind, G_BM, G_BN);
+    a.idesc_pair = g_idesc(kind, 2 * G_BM, bn);
     // bootstrap needs every CTA of a query block resident at once: cooperative launch, grid <= #SMs (1 CTA / SM)
     int boot_lists = std::min(L, 32) & ~1;                       // even: both halves of a CTA
     const int m = boot_lists ? (kprime + boot_lists - 1) / boot_lists : G_BOOT_MAX + 1;
@@ -764,7 +872,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, const
     // rest (drop_min).  That is a good trade only when the bound sits far above the final top-k', i.e. when the rows the
     // bound was estimated from (boot_lists x 128) are a small part of the table; small tables re-read the tile instead.
     a.boot_early = (a.boot_m && n_rows >= (int64_t)16 * boot_lists * 128) ? 1 : 0;
-    if (a.boot_m && p.sync_tiles && nqb > C && ngroups <= G_MAX_GROUPS && n_rows * (int64_t)dim * 4 > (int64_t)64 << 20) {
+    if (a.boot_m && p.sync_tiles && nqb > C && ngroups <= G_MAX_GROUPS && n_rows * (int64_t)dim * (kind ? 2 : 4) > (int64_t)64 << 20) {
         a.progress = reinterpret_cast<u64 *>(wsb + 256);
         a.epoch = ++p.epoch;
         a.drift = p.sync_tiles;

@@ -129,13 +129,18 @@ struct mcp_index {
     int64_t n_rows = 0, ld = 0, id_base = 0;
     const float *d_rows = nullptr;
     Buf own_rows, norm2, inv_norm, penalty, consts;
+    Buf shadow;                 // fp16 image of the table (rows scaled by powers of two), pitch ldh elements: K2's fp16 operand; empty when option "shadow" is 0
+    Buf shadow_scale;           // [n_rows] fp32: 1 / scale of each shadow row
+    int64_t ldh = 0;
+    bool has_shadow = false;
+    int opt_shadow = 1;
     bool has_penalty = false;
     TableConsts h_consts{};
     // options
     int opt_path = MCP_PATH_AUTO, opt_kprime = 0, opt_max_fallback = 4, opt_time_coarse = 0;
     // workspace
     Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, flags,
-        exact_all, out_ids, gemm_ws, q_pad, nq2f, drop_min;
+        exact_all, out_ids, gemm_ws, q_pad, nq2f, drop_min, rho_q, q_op, q_scale;
     int *h_status = nullptr;   // pinned + mapped: [0] certificate failures, [1] unresolved; written by the fallback kernel's status fold
     int *h_status_dev = nullptr;   // the same words as the device addresses them
     Buf slot_ticket;           // one ticket per fallback slot (zero between launches)
@@ -191,7 +196,7 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     Buf *bufs[] = {&idx->own_rows, &idx->norm2, &idx->inv_norm, &idx->penalty, &idx->consts, &idx->q_copy,
                    &idx->nq2, &idx->inv_nq, &idx->qflag, &idx->scores, &idx->listsA, &idx->listsB, &idx->cntA,
                    &idx->cntB, &idx->flags, &idx->exact_all, &idx->out_ids,
-                   &idx->gemm_ws, &idx->q_pad, &idx->nq2f, &idx->drop_min, &idx->slot_ticket};
+                   &idx->gemm_ws, &idx->q_pad, &idx->nq2f, &idx->drop_min, &idx->slot_ticket, &idx->shadow, &idx->shadow_scale, &idx->rho_q, &idx->q_op, &idx->q_scale};
     for (Buf *b : bufs) b->release();
     for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
     if (idx->h_status) cudaFreeHost(idx->h_status);
@@ -217,6 +222,22 @@ static int prepare_table(mcp_index *idx, cudaStream_t st) {
     prep_rows_kernel<false><<<blocks, PREP_ROWS, 0, st>>>(idx->d_rows, idx->n_rows, idx->dim, idx->ld,
                                                           idx->norm2.as<double>(), idx->inv_norm.as<float>(),
                                                           nullptr, idx->consts.as<TableConsts>());
+    KCHECK();
+    // fp16 shadow (K2's fp16 operand: half the bytes, twice the tensor rate) + the rounding residuals the certificate needs.
+    // A table too large for a shadow beside it still works: the tf32 scan reads the fp32 rows themselves.
+    idx->ldh = (idx->dim + 7) & ~7;
+    idx->has_shadow = false;
+    if (idx->opt_shadow) {
+        rc = idx->shadow.ensure(sizeof(__half) * (size_t)idx->n_rows * (size_t)idx->ldh);
+        if (!rc) rc = idx->shadow_scale.ensure(sizeof(float) * (size_t)idx->n_rows);
+        if (rc == MCP_ENOMEM) { cudaGetLastError(); idx->shadow.release(); idx->shadow_scale.release(); }
+        else if (rc) return rc;
+        else idx->has_shadow = true;
+    } else { idx->shadow.release(); idx->shadow_scale.release(); }
+    shadow_rows_kernel<<<(unsigned)((idx->n_rows + 7) / 8), 256, 0, st>>>(idx->d_rows, idx->n_rows, idx->dim, idx->ld, idx->norm2.as<double>(),
+                                                                     idx->has_shadow ? idx->shadow.as<__half>() : nullptr, idx->ldh,
+                                                                     idx->has_shadow ? idx->shadow_scale.as<float>() : nullptr,
+                                                                     idx->consts.as<TableConsts>());
     KCHECK();
     CU(cudaMemcpyAsync(&idx->h_consts, idx->consts.p, sizeof(TableConsts), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -283,6 +304,12 @@ extern "C" int mcp_index_update_rows(mcp_index *idx, int64_t first_row, const fl
     prep_rows_kernel<false><<<blocks, PREP_ROWS, 0, st>>>(idx->d_rows + first_row * idx->ld, n_rows, idx->dim, idx->ld,
                                                           idx->norm2.as<double>() + first_row, idx->inv_norm.as<float>() + first_row,
                                                           nullptr, c);
+    KCHECK();
+    // shadow rows and residual maxima of the changed rows (the maxima, like the maximum norm, only ever grow)
+    shadow_rows_kernel<<<(unsigned)((n_rows + 7) / 8), 256, 0, st>>>(idx->d_rows + first_row * idx->ld, n_rows, idx->dim, idx->ld,
+                                                                idx->norm2.as<double>() + first_row,
+                                                                idx->has_shadow ? idx->shadow.as<__half>() + first_row * idx->ldh : nullptr,
+                                                                idx->ldh, idx->has_shadow ? idx->shadow_scale.as<float>() + first_row : nullptr, c);
     KCHECK();
     CU(cudaMemcpyAsync(&idx->h_consts, c, sizeof(TableConsts), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -351,7 +378,7 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
     if (!name) return fail(MCP_EINVAL, "option name is NULL");
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!strcmp(name, "path")) {
-        if (value < MCP_PATH_AUTO || value > MCP_PATH_EXACT_FP64) return fail(MCP_EINVAL, "path %lld", (long long)value);
+        if (value < MCP_PATH_AUTO || value > MCP_PATH_GEMM_F16) return fail(MCP_EINVAL, "path %lld", (long long)value);
         idx->opt_path = (int)value;
     } else if (!strcmp(name, "kprime")) {
         if (value < 0 || value > FINAL_MAX) return fail(MCP_EINVAL, "kprime %lld outside [0, %d]", (long long)value, FINAL_MAX);
@@ -375,8 +402,9 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
         idx->gemm.debug = (int)value;
     } else if (!strcmp(name, "gemm_l2_prefetch")) {
         idx->gemm.l2_prefetch = value != 0;
-    } else if (!strcmp(name, "gemm_wide")) {
-        idx->gemm.allow_wide = value != 0;
+    } else if (!strcmp(name, "shadow")) {
+        if (idx->n_rows) return fail(MCP_ESTATE, "option shadow must be set before the table is loaded");
+        idx->opt_shadow = value != 0;
     } else if (!strcmp(name, "gemm_bootstrap")) {
         idx->gemm.allow_boot = value != 0;
     } else if (!strcmp(name, "time_coarse")) {
@@ -523,9 +551,12 @@ static int choose_kprime(const mcp_index *idx, int k) {
 
 static int choose_path(const mcp_index *idx, int nq) {
     if (idx->h_consts.odd_rows) return MCP_PATH_EXACT_FP64;   // rows the fp32 coarse pass cannot bound
+    if (idx->opt_path == MCP_PATH_GEMM_F16 && !idx->has_shadow) return MCP_PATH_GEMM_TF32;   // no shadow: the fp32 rows themselves
     if (idx->opt_path != MCP_PATH_AUTO) return idx->opt_path;
-    return (nq >= 8 && gemm_supported(idx->dim, idx->ld)) ? MCP_PATH_GEMM_TF32 : MCP_PATH_STREAM_FP32;
+    if (nq < 8) return MCP_PATH_STREAM_FP32;
+    return idx->has_shadow ? MCP_PATH_GEMM_F16 : MCP_PATH_GEMM_TF32;
 }
+static bool is_gemm_path(int path) { return path == MCP_PATH_GEMM_TF32 || path == MCP_PATH_GEMM_F16; }
 
 // fp64 scan + exact select for the flagged queries, slots at a time, in one launch (exact_fallback_kernel)
 static int run_exact(mcp_index *idx, cudaStream_t st, const float *d_q, const double *nq2, int k, int slots,
@@ -555,7 +586,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     const int64_t n = idx->n_rows;
     const int path = choose_path(idx, nq);
     int kprime = choose_kprime(idx, k);
-    if (path == MCP_PATH_GEMM_TF32) kprime = std::min(kprime, gemm_max_kprime());   // >= k since k <= 256
+    if (is_gemm_path(path)) kprime = std::min(kprime, gemm_max_kprime());   // >= k since k <= 256
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
 
     if ((rc = idx->nq2.ensure(sizeof(double) * nq))) return rc;
@@ -573,8 +604,20 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             d_q, dim, idx->nq2.as<double>(), idx->inv_nq.as<float>(), idx->qflag.as<unsigned char>(), idx->nq2f.as<float>());
         KL();
     } else {
+        // the tensor-core scans read an operand image of the queries: scaled fp16 (pitch ldh), or -- tf32 with dim % 4 != 0 -- an fp32
+        // copy whose pitch a tensor map accepts; otherwise the caller's queries are the operand
+        void *q_out = nullptr; int ldq = dim, as_f16 = 0;
+        if (path == MCP_PATH_GEMM_F16) { ldq = (int)idx->ldh; as_f16 = 1; }
+        else if (path == MCP_PATH_GEMM_TF32 && (dim & 3)) ldq = (dim + 3) & ~3;
+        if (as_f16 || ldq != dim) {
+            if ((rc = idx->q_op.ensure((size_t)nq * ldq * (as_f16 ? 2 : 4)))) return rc;
+            q_out = idx->q_op.p;
+        }
+        if ((rc = idx->rho_q.ensure(sizeof(float) * 2 * (size_t)nq))) return rc;
+        if ((rc = idx->q_scale.ensure(sizeof(float) * (size_t)nq))) return rc;
         prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), n_flag,
-                                                               idx->drop_min.as<unsigned int>());
+                                                               idx->drop_min.as<unsigned int>(), idx->rho_q.as<float>(), q_out, ldq, as_f16,
+                                                               idx->q_scale.as<float>());
         KL();
     }
 
@@ -603,8 +646,17 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     CertParams cp;
     cp.metric = idx->metric; cp.path = path; cp.complete = (n <= kprime);
     const double u = 5.9604644775390625e-08;   // 2^-24
+    cp.kind = 0; cp.rho_e = 0.0;
     if (path == MCP_PATH_STREAM_FP32) cp.rel = 2.0 * (dim / 32.0 + 32.0) * u;   // + the fp32 tree-summed query norm
-    else cp.rel = 1.02 * 0.001953125 + dim * 4.0 * u;      // TF32 truncation of both operands (2^-9) + fp32 accumulation
+    else {
+        // operand rounding enters per query through rho_q and the table's rho_e (rescore.cuh); what is left is the fp32
+        // accumulation inside the tensor core and the rounding of the two fp32 inverse norms (the query's is a tree sum)
+        cp.rel = dim * 4.0 * u + 128.0 * u;
+        cp.kind = path == MCP_PATH_GEMM_F16 ? 2 : 1;
+        const unsigned int rb = path == MCP_PATH_GEMM_F16 ? idx->h_consts.rho_f16 : idx->h_consts.rho_tf32;
+        float rf; memcpy(&rf, &rb, sizeof rf);
+        cp.rho_e = (double)rf;
+    }
     cp.abs_pen = 8.0 * u;
     cp.debug = idx->gemm.debug >> 8;
 
@@ -645,10 +697,16 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
                 return rc;
         } else {
             int L, cap; u64 *lists; int *cnts;
-            if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, idx->d_rows, n, dim, idx->ld, dq, cq,
+            const bool bf = path == MCP_PATH_GEMM_F16;
+            const int ldq = bf ? (int)idx->ldh : (dim + 3) & ~3;
+            const void *qop = bf ? (const void *)(idx->q_op.as<__half>() + (int64_t)q0 * ldq)
+                                 : (dim & 3) ? (const void *)(idx->q_op.as<float>() + (int64_t)q0 * ldq) : (const void *)dq;
+            if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, bf ? 1 : 0, bf ? (const void *)idx->shadow.p : (const void *)idx->d_rows,
+                                    n, dim, bf ? idx->ldh : idx->ld, qop, ldq, cq,
                                     idx->inv_nq.as<float>() + q0, idx->nq2f.as<float>() + q0, idx->inv_norm.as<float>(),
                                     idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap, nullptr,
-                                    idx->drop_min.as<unsigned int>() + q0)))
+                                    idx->drop_min.as<unsigned int>() + q0, bf ? idx->q_scale.as<float>() + q0 : nullptr,
+                                    bf ? idx->shadow_scale.as<float>() : nullptr)))
                 return fail(rc, "%s", idx->gemm.err);
             idx->stats.kernel_launches++;
             if ((rc = coarse_event(idx, st))) return rc;
@@ -668,7 +726,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
                           npow2, k, idx->id_base, idx->consts.as<TableConsts>(), cp,
                           idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
                           out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag,
-                          path == MCP_PATH_GEMM_TF32 ? idx->drop_min.as<unsigned int>() + q0 : nullptr));
+                          is_gemm_path(path) ? idx->drop_min.as<unsigned int>() + q0 : nullptr,
+                          is_gemm_path(path) ? idx->rho_q.as<float>() + 2 * q0 : nullptr));
             KL();
         }
         // certificate failures: fp64 scan on the device, flag_list holds chunk-local query numbers
@@ -677,7 +736,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             return rc;
         // flags[1] failures, [2] unresolved, [3] ticket: folded by exact_fallback_kernel's last CTA
         idx->stats.rows_scanned += n;
-        idx->stats.bytes_scanned += n * (int64_t)dim * 4;
+        idx->stats.bytes_scanned += path == MCP_PATH_GEMM_F16 ? n * idx->ldh * 2 : n * (int64_t)dim * 4;
         idx->stats.candidates_rescored += (int64_t)cq * kc;
     }
     return MCP_OK;
@@ -809,8 +868,18 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     if ((rc = idx->qflag.ensure(n_queries))) return rc;
     if ((rc = idx->nq2f.ensure(sizeof(float) * n_queries))) return rc;
     // the same query norms a search feeds its coarse kernel
+    const bool bf = path == MCP_PATH_GEMM_F16;
+    if (bf && !idx->has_shadow) return fail(MCP_ESTATE, "coarse_scores: the index holds no fp16 shadow table");
+    const int ldq = bf ? (int)idx->ldh : (dim + 3) & ~3;
+    void *q_out = nullptr;
+    if (bf || (path == MCP_PATH_GEMM_TF32 && ldq != dim)) {
+        if ((rc = idx->q_op.ensure((size_t)n_queries * ldq * (bf ? 2 : 4)))) return rc;
+        q_out = idx->q_op.p;
+    }
+    if ((rc = idx->q_scale.ensure(sizeof(float) * (size_t)n_queries))) return rc;
     prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
-                                                                 idx->nq2f.as<float>(), nullptr, nullptr);
+                                                                 idx->nq2f.as<float>(), nullptr, nullptr, nullptr, q_out, ldq, bf ? 1 : 0,
+                                                                 idx->q_scale.as<float>());
     KCHECK();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     if (path == MCP_PATH_STREAM_FP32) {
@@ -821,14 +890,16 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
                                     out_scores_device + (int64_t)p * idx->n_rows, idx->n_rows)))
                 return rc;
         }
-    } else if (path == MCP_PATH_GEMM_TF32) {
+    } else if (is_gemm_path(path)) {
         u64 *l; int *c; int L, cap;
-        if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, idx->d_rows, idx->n_rows, dim, idx->ld, queries_device,
+        if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, bf ? 1 : 0, bf ? (const void *)idx->shadow.p : (const void *)idx->d_rows,
+                                idx->n_rows, dim, bf ? idx->ldh : idx->ld, q_out ? (const void *)q_out : (const void *)queries_device, ldq,
                                 n_queries, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), idx->inv_norm.as<float>(),
-                                idx->norm2.as<double>(), pen, idx->metric, 64, &l, &c, &L, &cap, out_scores_device)))
+                                idx->norm2.as<double>(), pen, idx->metric, 64, &l, &c, &L, &cap, out_scores_device, nullptr,
+                                bf ? idx->q_scale.as<float>() : nullptr, bf ? idx->shadow_scale.as<float>() : nullptr)))
             return fail(rc, "%s", idx->gemm.err);
     } else
-        return fail(MCP_EINVAL, "coarse_scores: path must be STREAM_FP32 or GEMM_TF32");
+        return fail(MCP_EINVAL, "coarse_scores: path must be STREAM_FP32, GEMM_TF32 or GEMM_F16");
     CU(cudaEventRecord(idx->done, st));
     idx->pending = true;
     return MCP_OK;

@@ -23,7 +23,9 @@ struct CertParams {
     int metric;
     int path;              // MCP_PATH_*
     int complete;          // candidate set == all rows: nothing was dropped
-    double rel;            // relative coarse error bound of the dot product / squared distance
+    double rel;            // relative coarse error bound of the dot product / squared distance that does not depend on the query
+    int kind;              // tensor-core scans: 1 tf32, 2 fp16 operands (0: the fp32 streaming scan, `rel` is the whole bound)
+    double rho_e;          // tensor-core scans: largest rounding residual ratio of a table row in that format (TableConsts::rho_*)
     double abs_pen;        // multiplier of pen_absmax for fp32 rounding of the final add
     int debug;             // option gemm_debug >> 8 (timing experiments, wrong results): 1 no chain, 2 no gathers
 };
@@ -107,7 +109,8 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
                         double *__restrict__ nq2_out, unsigned char *__restrict__ qflag_out,
                         int32_t *__restrict__ out_ids, float *__restrict__ out_scores, double *__restrict__ out_scores64,
                         int *__restrict__ flag_list, int *__restrict__ n_flag,
-                        const unsigned int *__restrict__ drop_min /* NULL, or [q]: best coarse score the scan dropped outside its lists */) {
+                        const unsigned int *__restrict__ drop_min /* NULL, or [q]: best coarse score the scan dropped outside its lists */,
+                        const float *__restrict__ rho_q /* NULL, or [q][2]: the query's rounding residual ratios (tf32, fp16) */) {
     extern __shared__ __align__(16) unsigned char rf_raw[];
     __shared__ int s_row[RF_MAXG * RS_ROWS];
     __shared__ const float *s_rowptr[RF_MAXG * RS_ROWS];
@@ -294,15 +297,24 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
             const double qn = sqrt(nq2);
             const double en = sqrt(__longlong_as_double((long long)consts->max_norm2_bits));
             const double pen_abs = (double)consts->pen_absmax, pen_max = (double)consts->pen_max;
+            // Tensor-core scans multiply rounded operands q^ = q - g, e^ = e - d:  q.e - q^.e^ = g.e + q^.d, so
+            // |q.e - q^.e^| <= |g||e| + |q^||d| <= (rho_q + (1 + rho_q) rho_e) |q||e|  (Cauchy-Schwarz on the residuals; rho_e is
+            // the table's maximum, rho_q this query's own).  cp.rel adds the fp32 accumulation inside the tensor core and the
+            // rounding of the two inverse norms.
+            double rel = cp.rel;
+            if (cp.kind && rho_q) {
+                const double rq = (double)rho_q[2 * q + (cp.kind - 1)];
+                rel += 1.001 * (rq + (1.0 + rq) * cp.rho_e);
+            }
             double eps;
             if (cp.metric == 0) {
-                eps = cp.rel + cp.abs_pen * (2.0 + pen_abs);
-            } else if (cp.path == 2) {
-                const double delta = 2.0 * cp.rel * qn * en + 4.0 * 5.96e-8 * (qn + en) * (qn + en);
+                eps = rel + cp.abs_pen * (2.0 + pen_abs);
+            } else if (cp.path == 2 || cp.path == 4) {
+                const double delta = 2.0 * rel * qn * en + 4.0 * 5.96e-8 * (qn + en) * (qn + en);
                 double x0 = T - pen_max; x0 = x0 > 0.0 ? x0 * x0 : 0.0;
                 eps = sqrt(x0) - sqrt(fmax(x0 - delta, 0.0)) + cp.abs_pen * (sqrt(x0) + pen_abs);
             } else {
-                eps = cp.rel * (qn + en) + cp.abs_pen * ((qn + en) + pen_abs);
+                eps = rel * (qn + en) + cp.abs_pen * ((qn + en) + pen_abs);
             }
             pass = (sk_k == sk_k) && (sk_k < T - eps);
         }

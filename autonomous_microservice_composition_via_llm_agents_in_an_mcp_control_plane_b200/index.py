@@ -21,7 +21,7 @@ from . import _native as nat
 
 _METRICS = {"cosine": nat.METRIC_COSINE, "l2": nat.METRIC_L2, 0: 0, 1: 1}
 _PATHS = {"auto": nat.PATH_AUTO, "stream_fp32": nat.PATH_STREAM_FP32, "gemm_tf32": nat.PATH_GEMM_TF32,
-          "exact_fp64": nat.PATH_EXACT_FP64}
+          "exact_fp64": nat.PATH_EXACT_FP64, "gemm_f16": nat.PATH_GEMM_F16}
 
 
 def _np_ptr(a: np.ndarray) -> C.c_void_p:

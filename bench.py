@@ -240,7 +240,7 @@ def main():
     ap.add_argument("--queries", type=int, default=0)
     ap.add_argument("--topk", type=int, default=0)
     ap.add_argument("--metric", choices=["cosine", "l2"], default=None, help="override the workload's distance (SURVEY 8d: config 3 is also run with L2)")
-    ap.add_argument("--path", default="auto", choices=["auto", "stream_fp32", "gemm_tf32"])
+    ap.add_argument("--path", default="auto", choices=["auto", "stream_fp32", "gemm_tf32", "gemm_f16"])
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (repeatable), e.g. gemm_wide=0")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")

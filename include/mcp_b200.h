@@ -46,6 +46,8 @@ extern "C" {
 #define MCP_PATH_STREAM_FP32 1 /* K1: fp32 CUDA-core streaming scan                        */
 #define MCP_PATH_GEMM_TF32 2   /* K2: tcgen05 / TMEM TF32 distance GEMM                    */
 #define MCP_PATH_EXACT_FP64 3  /* full fp64 scan (the certificate's fallback, also a checker) */
+#define MCP_PATH_GEMM_F16 4    /* K2 over the fp16 shadow table: kind::f16 MMAs, half the bytes, twice the tensor rate.
+                                  AUTO takes it for batches of 8 and more whenever the index holds a shadow            */
 
 typedef struct mcp_index mcp_index;
 
@@ -151,7 +153,10 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
 
 /* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
  * query before exact rescoring, >= k), "max_fallback" (device-side fp64 re-scans per batch),
- * "gemm_wide" (1 = K2 with 256-query CTAs above 128 queries; default 0 = 128-query CTAs, measured faster),
+ * "shadow" (default 1: load / adopt also build an fp16 image of the table (each row scaled by a power of two), +50 % device memory, which the batched scan
+ * reads instead of the fp32 rows; the answer stays exact -- candidates are rescored in fp64 from the fp32 rows and certified
+ * with a bound computed from the actual rounding residuals.  0 = no shadow, the batched scan reads the fp32 rows as tf32.
+ * Set it before the table is loaded.  When the shadow does not fit in device memory the index quietly goes without),
  * "gemm_l2_prefetch" (1 = K2 with a per-row 1 KB L2 bulk prefetch; default 0, measured slower),
  * "gemm_balance" (1 = K2 tile height shrunk so that every CTA gets the same number of tiles; default 0 = 256-row tiles, measured equal),
  * "gemm_cluster" (CTAs per cluster that share a row tile: 0 = automatic -- 2 when the batch has an even number of

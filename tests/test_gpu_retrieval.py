@@ -13,12 +13,9 @@ import cases
 pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).parent / "golden"
 REL_TOL = 1e-5
-PATHS = ["stream_fp32", "gemm_tf32", "exact_fp64"]
-
-
-def _gemm_ready(mcp, dim):
-    """The TF32 path only exists for dims its TMA tiling accepts; otherwise it must refuse loudly."""
-    return dim % 4 == 0
+PATHS = ["stream_fp32", "gemm_tf32", "gemm_f16", "exact_fp64"]
+PATH_CODE = {"stream_fp32": 1, "gemm_tf32": 2, "exact_fp64": 3, "gemm_f16": 4}
+COARSE = ["stream_fp32", "gemm_tf32", "gemm_f16"]
 
 
 def _assert_parity(got, want_ids, want_s64):
@@ -50,13 +47,11 @@ def test_golden_and_oracle(mcp, oracle, name, path):
     c = {"config1": cases.config1, "small_l2": lambda: cases.small_l2(oracle.telemetry_penalty),
          "edge_cases": lambda: cases.edge_cases(oracle.telemetry_penalty),
          "config2_small": lambda: cases.config2_small(oracle.telemetry_penalty)}[name]()
-    if path == "gemm_tf32" and not _gemm_ready(mcp, c["rows"].shape[1]):
-        pytest.skip("dim not a multiple of 4: the GEMM path does not take it")
     k = min(c["k"], 256)
     g = np.load(GOLD / f"retrieval_{name}.npz")
     got, stats = _run(mcp, c, path, k=k)
     _assert_parity(got, g["ids"][:, :k], g["scores64"][:, :k])
-    assert stats["last_path"] == {"stream_fp32": 1, "gemm_tf32": 2, "exact_fp64": 3}[path]
+    assert stats["last_path"] == PATH_CODE[path]
 
 
 @pytest.mark.parametrize("metric", [0, 1])
@@ -74,7 +69,7 @@ def test_seeded_batches(mcp, oracle, metric, path):
         _assert_parity(got, want_ids, want_s64)
 
 
-@pytest.mark.parametrize("path", ["stream_fp32", "gemm_tf32"])
+@pytest.mark.parametrize("path", COARSE)
 def test_certificate_catches_near_ties(mcp, oracle, path):
     """Rows that differ from each other by ~1 ulp in score: the coarse pass cannot order them, the
     certificate must notice when k' is too small and the fp64 scan must fix it."""
@@ -162,7 +157,7 @@ def test_device_pointer_api_and_shard_merge(mcp, oracle):
         idx.close()
 
 
-@pytest.mark.parametrize("path", ["stream_fp32", "gemm_tf32"])
+@pytest.mark.parametrize("path", COARSE)
 def test_config2_full_size_properties(mcp, oracle, path):
     """BASELINE config 2 at full size (100K x 1536, 256 queries, top-32, cosine + telemetry).
     The oracle checks a sample of queries; every query is checked against the GPU fp64 scan
@@ -199,18 +194,39 @@ def test_config2_full_size_properties(mcp, oracle, path):
     idx.close()
 
 
+def _rho(v, fmt):
+    """Upper bound of |v - round(v)|_2 / |v|_2 per row, as prep.cuh computes it (TableConsts::rho_*, rho_q): tf32 drops the
+    low 13 mantissa bits; the fp16 image is the row scaled by the power of two that puts its largest element in [2^14, 2^15),
+    rounded to nearest even."""
+    v = np.ascontiguousarray(v, np.float32)
+    if fmt == "tf32":
+        r = (v.view(np.uint32) & np.uint32(0xFFFFE000)).view(np.float32).astype(np.float64)
+    else:
+        vmax = np.abs(v).max(axis=1, keepdims=True)
+        sc = np.exp2(14.0 - np.floor(np.log2(vmax))).astype(np.float32)
+        r = (v * sc).astype(np.float16).astype(np.float64) / sc.astype(np.float64)
+    delta = v.astype(np.float64) - r
+    n2 = (v.astype(np.float64) ** 2).sum(axis=1)
+    return np.sqrt((delta ** 2).sum(axis=1) * (1.0 + 2.0 ** -10) / n2) * (1.0 + 1e-6)
+
+
 @pytest.mark.parametrize("metric", [0, 1])
-@pytest.mark.parametrize("path", ["stream_fp32", "gemm_tf32"])
+@pytest.mark.parametrize("path", COARSE)
 def test_coarse_scores_within_certified_bounds(mcp, oracle, metric, path):
     """Every coarse score must lie within the error bound the certificate assumes for its kernel
     (rescore.cuh / mcp_abi.cu CertParams); also localises a wrong TMA / UMMA descriptor to the element.
     Ragged on purpose: N not a multiple of the 256-row tile, Q = 150 (second query block half empty),
-    dim = 200 is not a multiple of the 32-float k-block (TMA zero fill)."""
+    dim = 200 is not a multiple of the 128-byte k-block (TMA zero fill), dim = 1530 is not a multiple of 4 (padded pitch).
+    Tensor-core scans: the bound is rho_q + (1 + rho_q) rho_e relative to |q||e|, from the operands' actual rounding
+    residuals; on this data it is ~2.4x below the worst-case per-element bound (2^-9 for tf32), and the fp16 shadow's is
+    half of tf32's again."""
     import torch
 
     dev = torch.device("cuda:0")
     u = 2.0 ** -24
-    for n, d, q in [(3000, 1536, 150), (777, 200, 5)]:
+    for n, d, q in [(3000, 1536, 150), (777, 200, 5), (600, 1530, 9)]:
+        if path == "stream_fp32" and d % 4:
+            continue                                   # the validation entry point runs K1 on unpadded queries only
         rng = np.random.default_rng(n + metric)
         rows = (rng.standard_normal((n, d), dtype=np.float32) * rng.uniform(0.5, 2.0, (n, 1)).astype(np.float32))
         qs = rng.standard_normal((q, d), dtype=np.float32)
@@ -221,7 +237,13 @@ def test_coarse_scores_within_certified_bounds(mcp, oracle, metric, path):
             got = idx.coarse_scores_device(torch.from_numpy(qs).to(dev), path)
             torch.cuda.synchronize()
             got = got.cpu().numpy().astype(np.float64)
-        rel = 2.0 * (d / 32.0 + 32.0) * u if path == "stream_fp32" else 1.02 * 2.0 ** -9 + d * 4.0 * u
+        if path == "stream_fp32":
+            rel = 2.0 * (d / 32.0 + 32.0) * u
+        else:
+            fmt = "tf32" if path == "gemm_tf32" else "f16"
+            rq, re = _rho(qs, fmt)[:, None], _rho(rows, fmt).max()
+            rel = d * 4.0 * u + 128.0 * u + 1.001 * (rq + (1.0 + rq) * re)
+            assert rel.max() < 0.6 * 2.0 ** -9 + d * 4.0 * u, "residual bound is not tighter than the worst case"
         qn = np.linalg.norm(qs.astype(np.float64), axis=1)[:, None]
         en = np.linalg.norm(rows.astype(np.float64), axis=1)[None, :]
         if metric == 0:
@@ -344,7 +366,7 @@ def test_query_chunking_paths_agree(mcp, oracle):
     idx.set_option("path", "exact_fp64").set_option("max_fallback", 16)
     want_i, _, want_s = (t.clone() for t in idx.search_device(qs, k))
     idx.sync_status()
-    for path in ("gemm_tf32", "stream_fp32"):
+    for path in ("gemm_tf32", "gemm_f16", "stream_fp32"):
         idx.set_option("path", path)
         ids, _, s64 = idx.search_device(qs, k)
         assert idx.sync_status()[1] == 0
@@ -355,8 +377,9 @@ def test_query_chunking_paths_agree(mcp, oracle):
     idx.close()
 
 
+@pytest.mark.parametrize("path", ["gemm_tf32", "gemm_f16"])
 @pytest.mark.parametrize("metric", [0, 1])
-def test_cta_pair_and_single_cta_scans_agree_with_oracle(mcp, oracle, metric):
+def test_cta_pair_and_single_cta_scans_agree_with_oracle(mcp, oracle, metric, path):
     """K2 has three shapes: one tcgen05 CTA pair per cluster (cta_group::2, the default for an even number of 128-query
     blocks), two single CTAs multicasting the row tile, and plain single CTAs.  Same oracle answer from each, with and
     without balanced tile heights (which change the MMA's N and the TMA box)."""
@@ -369,11 +392,11 @@ def test_cta_pair_and_single_cta_scans_agree_with_oracle(mcp, oracle, metric):
     for opts in ({"gemm_pair": 1}, {"gemm_pair": 0}, {"gemm_cluster": 1}, {"gemm_pair": 1, "gemm_balance": 1}):
         with mcp.ServiceIndex(d, "cosine" if metric == 0 else "l2") as idx:
             idx.load(rows).set_penalty(pen)
-            idx.set_option("path", "gemm_tf32")
+            idx.set_option("path", path)
             for name, v in opts.items():
                 idx.set_option(name, v)
             _assert_parity(idx.search(qs, k), want_ids, want_s64)
-            assert idx.stats()["last_path"] == 2, opts
+            assert idx.stats()["last_path"] == PATH_CODE[path], opts
 
 
 def test_bootstrap_tile_drops_are_caught_by_the_certificate(mcp, oracle):

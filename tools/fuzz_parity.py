@@ -28,7 +28,7 @@ def main():
         q = int(rng.choice([1, 7, 8, 33, 128, 129, 256, 300, 512]))
         k = int(rng.choice([1, 8, 32, 64, 200]))
         metric = int(rng.integers(0, 2))
-        path = str(rng.choice(["auto", "auto", "gemm_tf32", "stream_fp32"]))
+        path = str(rng.choice(["auto", "auto", "gemm_tf32", "gemm_f16", "stream_fp32"]))
         rows = rng.standard_normal((n, d), dtype=np.float32)
         if rng.random() < 0.3 and n > 50:                       # clusters of near-duplicates and exact duplicates
             rows[n // 2:n // 2 + 20] = rows[0] + rng.standard_normal((20, d)).astype(np.float32) * 1e-3
@@ -45,8 +45,6 @@ def main():
             opts["gemm_balance"] = 1
         if rng.random() < 0.15:
             opts["gemm_cluster"] = 1
-        if path == "gemm_tf32" and d % 4:
-            path = "auto"
         want_ids, want_s64, _ = oracle.topk(rows, qs, k, metric, pen)
         with mcp.ServiceIndex(d, "cosine" if metric == 0 else "l2") as idx:
             idx.load(rows)
