@@ -48,6 +48,7 @@ SIGNATURES = {
     "mcp_index_set_penalty_device": (_i32, [_vp, _vp, _vp]),
     "mcp_index_search": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "mcp_index_search_device": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "mcp_index_repair_device": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     "mcp_index_coarse_scores_device": (_i32, [_vp, _i32, _vp, _i32, _vp, _vp]),
     "mcp_index_search_exact_noalloc_device": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp, _vp]),
     "mcp_index_sync_status": (_i32, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
@@ -55,6 +56,8 @@ SIGNATURES = {
     "mcp_index_get_stats": (_i32, [_vp, C.POINTER(McpStats)]),
     "mcp_index_rows": (_i64, [_vp]),
     "mcp_merge_topk_device": (_i32, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "mcp_merge_packed_block_bytes": (_i64, [_i32, _i32]),
+    "mcp_merge_topk_packed_device": (_i32, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "mcp_dag_levels": (_i32, [_i32, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "mcp_dag_levels_device": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "mcp_last_error": (C.c_char_p, []),

@@ -64,6 +64,7 @@ struct GemmArgs {
     u64 *pub;                  // [nq][L]  each (CTA, query)'s boot_m-th smallest key of its first tile
     unsigned int *arrive;      // [nqb]    CTAs of a query block that have published (zero when the launch starts)
     unsigned int *arrive_next; // [G_MAX_QBLOCKS] the other slot of the pair: this launch clears it for the next one
+    u64 *tau_pub;              // [nq] (launch epoch << 32 | float bits of the shared bound), posted by list 0 of each query as the scan goes on
     unsigned int *drop_min;    // [nq] ordered image of the best coarse score the bootstrap tile may have dropped (all-ones: none); never NULL when boot_m > 0
     u64 *progress;             // [ngroups][nqb] (launch epoch << 32 | tile index each CTA has started), or NULL: keeps the CTAs that
                                // walk the same row tiles within `G_DRIFT` tiles of each other so that the tiles stay in L2
@@ -468,7 +469,12 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // my four smallest keys so far: found by the bootstrap pass over the first tile and, when the bootstrap hands its tile back
         // early (large tables), kept current by the filter pass, so that the shared bound can be tightened as the scan goes on
         u64 b0 = ~0ull, b1 = ~0ull, b2 = ~0ull, b3 = ~0ull;
-        const bool refresh = a.boot_m > 0 && a.boot_early;
+        // ... and, from then on, four small scores of rows this list has seen, ascending (floats; +inf = none).  They need not be
+        // THE four smallest: the maximum of any four seen scores bounds the list's fourth-smallest from above, which is all the
+        // shared bound asks for.  So they are updated only where that is cheap (from tile 4 on, when survivors are rare).
+        float f0 = CUDART_INF_F, f1 = CUDART_INF_F, f2 = CUDART_INF_F, f3 = CUDART_INF_F;
+        u64 tp = 0;                                            // tau_pub word read one tile ago (epoch 0 never matches)
+        const bool refresh = a.boot_m > 0 && a.boot_early && !(a.debug & 64);
         // per-row constants of a tile, fetched one tile ahead so that their global-load latency hides under the previous
         // tile's epilogue instead of sitting in front of the barrier below.  Rows past the table get +inf.
         auto fetch_meta = [&](int ii, float &m0, float &m1, float &rs) {
@@ -494,25 +500,36 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (METRIC == 1) s.mscale[mbuf][et] = nrs;
             }
             fetch_meta(i + 1, nm0, nm1, nrs);
-            if (refresh && i > 0 && (i & (i - 1)) == 0 && qvalid) {
-                // Tighten the shared bound at tiles 1, 2, 4, 8 ...: each publishing list re-publishes its boot_m-th smallest key
-                // (it only ever decreases) and every list takes the maximum of what is published.  Any such maximum has at
-                // least boot_lists * boot_m >= k' keys of the union at or below it, whichever mix of older and newer values
-                // it is read from, so nothing is waited for.  A list's own threshold never drops below its own boot_m-th
-                // smallest key (it is part of the maximum), so every row that belongs among its four smallest is appended and
-                // seen by the insertion below.  After n rows per list the bound sits near the (2 boot_m / n) quantile, so a
-                // list collects a few dozen rows over the whole scan instead of filling up and being pruned again and again
-                // (the prunes -- one warp selecting while seven wait at the tile barrier -- were 60 % of the epilogue).
-                const u64 mine = a.boot_m == 1 ? b0 : a.boot_m == 2 ? b1 : a.boot_m == 3 ? b2 : b3;
+            if (refresh && qvalid) {
+                // Tighten the shared bound as the scan goes on.  At tiles 1, 2, 4, 8 ... each publishing list re-publishes its
+                // boot_m-th smallest key (it only ever decreases); one tile later the thread of list 0 (one CTA per query
+                // block) takes the maximum of what is published and posts it, tagged with this launch's epoch, in tau_pub;
+                // every list reads that one word per tile, a tile ahead of its use.  Any such maximum has at least
+                // boot_lists * boot_m >= k' keys of the union at or below it, whichever mix of older and newer values it was
+                // taken from, so nobody waits for anybody.  After n rows per list the bound sits near the
+                // (2 boot_m / n) quantile: a list collects a few dozen rows over the whole scan instead of filling up and
+                // being pruned again and again (the prunes -- one warp selecting while seven wait at the tile barrier -- were
+                // 60 % of the epilogue).  (First version: every thread read all the published keys itself; 38 K threads
+                // hitting the same 64 KB at the same moment cost ~20 us per round.)
+                if ((uint32_t)(tp >> 32) == a.epoch) tau_f = fminf(tau_f, __uint_as_float((uint32_t)tp));
+                tp = __ldcg(a.tau_pub + qg);
                 u64 *pq = a.pub + (int64_t)qg * a.boot_lists;
-                if (li < a.boot_lists) pq[li] = mine;
-                u64 t0 = 0;
-                const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(pq);
-                for (int l = 0; l < a.boot_lists / 2; ++l) {
-                    const ulonglong2 x = __ldcg(pp + l);
-                    t0 = x.x > t0 ? x.x : t0; t0 = x.y > t0 ? x.y : t0;
+                if (i > 0 && (i & (i - 1)) == 0 && li < a.boot_lists) {
+                    const float fm = a.boot_m == 1 ? f0 : a.boot_m == 2 ? f1 : a.boot_m == 3 ? f2 : f3;
+                    // a key at or above every key with that score: "at least boot_m of my keys are at or below this one"
+                    pq[li] = fm < CUDART_INF_F ? (((u64)f32_ord(fm) << 32) | 0xFFFFFFFFull) : ~0ull;
                 }
-                if (t0 != ~0ull) tau_f = fminf(tau_f, ord_f32((uint32_t)(t0 >> 32)));   // a NaN bound changes nothing
+                if (li == 0 && i > 1 && ((i - 1) & (i - 2)) == 0) {
+                    const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(pq);
+                    ulonglong2 x[16];
+#pragma unroll
+                    for (int l = 0; l < 16; ++l) x[l] = l < a.boot_lists / 2 ? __ldcg(pp + l) : make_ulonglong2(0ull, 0ull);
+                    u64 t0 = 0;
+#pragma unroll
+                    for (int l = 0; l < 16; ++l) { t0 = x[l].x > t0 ? x[l].x : t0; t0 = x[l].y > t0 ? x[l].y : t0; }
+                    const float tf = ord_f32((uint32_t)(t0 >> 32));
+                    if (t0 != ~0ull && tf == tf) a.tau_pub[qg] = ((u64)a.epoch << 32) | (u64)__float_as_uint(tf);
+                }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(Cfg::EPI_THREADS) : "memory");
             mbar_wait(&s.tfull[buf], tphase);
@@ -609,6 +626,14 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         if (bb[u] != ~0ull && !(ord_f32((uint32_t)(bb[u] >> 32)) > tau_f)) mylist[cnt++] = key_to_raw(bb[u]);
                     if (b3 != ~0ull && !(ord_f32((uint32_t)(b3 >> 32)) > tau_f)) atomicMin(&a.drop_min[qg], (uint32_t)(b3 >> 32));
                 }
+                if (refresh) {                                 // the four smallest of tile 0 seed the float set (NaN keys: none)
+                    f0 = b0 == ~0ull ? CUDART_INF_F : ord_f32((uint32_t)(b0 >> 32)); f1 = b1 == ~0ull ? CUDART_INF_F : ord_f32((uint32_t)(b1 >> 32));
+                    f2 = b2 == ~0ull ? CUDART_INF_F : ord_f32((uint32_t)(b2 >> 32)); f3 = b3 == ~0ull ? CUDART_INF_F : ord_f32((uint32_t)(b3 >> 32));
+                    if (!(f0 == f0)) f0 = CUDART_INF_F;
+                    if (!(f1 == f1)) f1 = CUDART_INF_F;
+                    if (!(f2 == f2)) f2 = CUDART_INF_F;
+                    if (!(f3 == f3)) f3 = CUDART_INF_F;
+                }
                 if (a.boot_early) continue;                    // otherwise: the filter pass below re-reads the tile
             }
             // ---- filter pass ----
@@ -622,27 +647,23 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 // score all 32 first and only then look for survivors: once the shared bound has tightened, whole chunks pass
                 // without one, and the loop below (a branch, a store and the four-smallest insertion per element) is skipped
                 bool any = false;
+                const bool ins = refresh && i >= 4;
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const float sc = score(__uint_as_float(v[j]), mbuf, cbase + c + j);
                     v[j] = __float_as_uint(sc);
                     any |= !(sc > tau_f);                      // at or below the threshold, or NaN
                 }
-                if (any) {
+                if (any || (a.debug & 128)) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const int r = cbase + c + j;
                         const float sc = __uint_as_float(v[j]);
                         if (!(sc > tau_f) && qvalid && r < rows_here) {
                             mylist[cnt++] = ((u64)v[j] << 32) | (u64)(uint32_t)(row0 + r);
-                            if (refresh) {
-                                const u64 key = coarse_key(sc, (uint32_t)(row0 + r));
-                                if (key < b3) {
-                                    b3 = key;
-                                    if (b3 < b2) { const u64 x = b3; b3 = b2; b2 = x; }
-                                    if (b2 < b1) { const u64 x = b2; b2 = b1; b1 = x; }
-                                    if (b1 < b0) { const u64 x = b1; b1 = b0; b0 = x; }
-                                }
+                            if (ins && sc < f3) {              // branch-free insertion into the ascending four (never NaN: sc < f3)
+                                f3 = fminf(f3, fmaxf(f2, sc)); f2 = fminf(f2, fmaxf(f1, sc));
+                                f1 = fminf(f1, fmaxf(f0, sc)); f0 = fminf(f0, sc);
                             }
                         }
                     }
@@ -831,7 +852,11 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     // workspace: [arrive counters, two sets][lists][list counts][published bounds].  The counters sit first so that their
     // place does not move with the launch shape: a bootstrap launch uses one set (zero on entry) and clears the other for
     // the launch after it, which saves a memset node per search; only a new workspace is cleared from the host.
-    const size_t hdr = 256 + sizeof(u64) * G_MAX_GROUPS * G_MAX_QBLOCKS;   // arrive counter pair, then the progress words
+    // header: arrive counter pair, the progress words, the shared-bound words.  All three are only ever matched against this
+    // launch's epoch (or are zero), so they sit at fixed offsets -- a place that moved with the launch shape could hold another
+    // launch's list data that happens to look like a tagged word -- and a new workspace is cleared once.
+    const size_t tau_off = 256 + sizeof(u64) * G_MAX_GROUPS * G_MAX_QBLOCKS;
+    const size_t hdr = tau_off + sizeof(u64) * G_MAX_QBLOCKS * G_BM;
     static_assert(2 * G_MAX_QBLOCKS * sizeof(unsigned int) <= 256, "arrive counter pair");
     const size_t list_bytes = sizeof(u64) * (size_t)nq * L * cap;
     const size_t cnt_off = (hdr + list_bytes + 255) & ~(size_t)255;
@@ -845,6 +870,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     a.lists = reinterpret_cast<u64 *>(wsb + hdr);
     a.list_cnt = reinterpret_cast<int *>(wsb + cnt_off);
     a.pub = reinterpret_cast<u64 *>(wsb + pub_off);
+    a.tau_pub = reinterpret_cast<u64 *>(wsb + tau_off);
     a.arrive = nullptr; a.arrive_next = nullptr;
     a.dump = dump;
     a.rows = kind ? nullptr : (const float *)rows; a.ld = ld; a.l2_prefetch = (p.l2_prefetch && !kind) ? 1 : 0; a.debug = p.debug; a.cluster = C; a.bn = bn;
@@ -865,7 +891,9 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     a.drop_min = drop_min;
     // progress words: only when several clusters share a group's tiles, every CTA is co-resident (the wait spins) and the
     // table is large enough for drift to matter
-    a.progress = nullptr; a.epoch = 0; a.drift = G_DRIFT;
+    a.progress = nullptr; a.drift = G_DRIFT;
+    if (++p.epoch == 0) p.epoch = 1;                 // never 0: stale words of other launches (or fresh memory) must not match
+    a.epoch = p.epoch;
     a.boot_m = (!dump && drop_min && !(p.debug & (1 | 16 | 32)) && p.coop == 1 && m <= G_BOOT_MAX && nqb * ngroups <= n_sm && p.allow_boot) ? m : 0;
     a.boot_lists = boot_lists;
     // Early hand-back keeps only four rows per (query, half tile) of the first tile and lets the certificate account for the
@@ -874,7 +902,6 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     a.boot_early = (a.boot_m && n_rows >= (int64_t)16 * boot_lists * 128) ? 1 : 0;
     if (a.boot_m && p.sync_tiles && nqb > C && ngroups <= G_MAX_GROUPS && n_rows * (int64_t)dim * (kind ? 2 : 4) > (int64_t)64 << 20) {
         a.progress = reinterpret_cast<u64 *>(wsb + 256);
-        a.epoch = ++p.epoch;
         a.drift = p.sync_tiles;
     }
     if (a.boot_m) {

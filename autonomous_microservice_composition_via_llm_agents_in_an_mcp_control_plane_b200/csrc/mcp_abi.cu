@@ -80,7 +80,7 @@ extern "C" int mcp_device_count(void) {
 extern "C" const char *mcp_build_info(void) {
     return "mcp_b200 sm_100a nvcc " MCP_STR(__CUDACC_VER_MAJOR__) "." MCP_STR(__CUDACC_VER_MINOR__)
            " kernels: prep_rows prep_queries scan_fp32 gemm_tf32_tcgen05 (cta_group::1 / cta_group::2) select_from_scores"
-           " select_from_lists rescore_finalize exact_fallback exact_scan exact_select merge_shards kahn_levels";
+           " select_from_lists rescore_finalize exact_scan2 exact_pick exact_select shadow_rows merge_shards kahn_levels";
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -137,13 +137,14 @@ struct mcp_index {
     bool has_penalty = false;
     TableConsts h_consts{};
     // options
-    int opt_path = MCP_PATH_AUTO, opt_kprime = 0, opt_max_fallback = 4, opt_time_coarse = 0;
+    int opt_path = MCP_PATH_AUTO, opt_kprime = 0, opt_max_fallback = XS_MAXS, opt_time_coarse = 0;
     // workspace
     Buf q_copy, nq2, inv_nq, qflag, scores, listsA, listsB, cntA, cntB, flags,
         exact_all, out_ids, gemm_ws, q_pad, nq2f, drop_min, rho_q, q_op, q_scale;
     int *h_status = nullptr;   // pinned + mapped: [0] certificate failures, [1] unresolved; written by the fallback kernel's status fold
     int *h_status_dev = nullptr;   // the same words as the device addresses them
-    Buf slot_ticket;           // one ticket per fallback slot (zero between launches)
+    Buf sp_keys, sp_rows, sp_cnt, bound_key, bound_row;   // the fallback's sparse lists [slot][XS_SPARSE_CAP] and per-query bounds
+    Buf unres;                 // [0] count, [1..] queries whose sparse list overflowed (host entry point re-answers them)
     unsigned char *h_stage = nullptr;   // pinned staging for the host-buffer search: results + status in one copy
     size_t h_stage_cap = 0;
     cudaStream_t stream = nullptr;
@@ -158,6 +159,8 @@ struct mcp_index {
 };
 
 #define SCORE_BUDGET_BYTES (512ull << 20)
+#define XS_SMEM_LIMIT (220u * 1024u)      // dynamic shared memory exact_scan2_kernel may ask for
+#define UNRES_MAX 4096
 
 static int check_idx(const mcp_index *idx) { return idx ? MCP_OK : fail(MCP_EINVAL, "index handle is NULL"); }
 
@@ -181,10 +184,13 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     idx->h_status[0] = idx->h_status[1] = 0;
     CU(cudaHostGetDevicePointer(&idx->h_status_dev, idx->h_status, 0));
     CU(cudaFuncSetAttribute(rescore_finalize_kernel<5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_LIMIT));
+    CU(cudaFuncSetAttribute(exact_scan2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XS_SMEM_LIMIT));
     int rc = idx->consts.ensure(sizeof(TableConsts));
     if (!rc) rc = idx->flags.ensure(sizeof(int) * 4096);
+    if (!rc) rc = idx->unres.ensure(sizeof(int) * (1 + UNRES_MAX));
     if (rc) { delete idx; return rc; }
     CU(cudaMemset(idx->flags.p, 0, sizeof(int) * 8));
+    CU(cudaMemset(idx->unres.p, 0, sizeof(int)));
     *out = idx;
     return MCP_OK;
 }
@@ -196,7 +202,7 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     Buf *bufs[] = {&idx->own_rows, &idx->norm2, &idx->inv_norm, &idx->penalty, &idx->consts, &idx->q_copy,
                    &idx->nq2, &idx->inv_nq, &idx->qflag, &idx->scores, &idx->listsA, &idx->listsB, &idx->cntA,
                    &idx->cntB, &idx->flags, &idx->exact_all, &idx->out_ids,
-                   &idx->gemm_ws, &idx->q_pad, &idx->nq2f, &idx->drop_min, &idx->slot_ticket, &idx->shadow, &idx->shadow_scale, &idx->rho_q, &idx->q_op, &idx->q_scale};
+                   &idx->gemm_ws, &idx->q_pad, &idx->nq2f, &idx->drop_min, &idx->sp_keys, &idx->sp_rows, &idx->sp_cnt, &idx->bound_key, &idx->bound_row, &idx->unres, &idx->shadow, &idx->shadow_scale, &idx->rho_q, &idx->q_op, &idx->q_scale};
     for (Buf *b : bufs) b->release();
     for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
     if (idx->h_status) cudaFreeHost(idx->h_status);
@@ -384,7 +390,7 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
         if (value < 0 || value > FINAL_MAX) return fail(MCP_EINVAL, "kprime %lld outside [0, %d]", (long long)value, FINAL_MAX);
         idx->opt_kprime = (int)value;
     } else if (!strcmp(name, "max_fallback")) {
-        if (value < 1 || value > 64) return fail(MCP_EINVAL, "max_fallback %lld outside [1, 64]", (long long)value);
+        if (value < 1 || value > XS_MAXS) return fail(MCP_EINVAL, "max_fallback %lld outside [1, %d]", (long long)value, XS_MAXS);
         idx->opt_max_fallback = (int)value;
     } else if (!strcmp(name, "gemm_balance")) {
         idx->gemm.balance_tiles = value != 0;
@@ -558,23 +564,60 @@ static int choose_path(const mcp_index *idx, int nq) {
 }
 static bool is_gemm_path(int path) { return path == MCP_PATH_GEMM_TF32 || path == MCP_PATH_GEMM_F16; }
 
-// fp64 scan + exact select for the flagged queries, slots at a time, in one launch (exact_fallback_kernel)
-static int run_exact(mcp_index *idx, cudaStream_t st, const float *d_q, const double *nq2, int k, int slots,
-                     int32_t *out_ids, float *out_scores, double *out_scores64, bool fold_status) {
+// slots one pass of the fp64 scan serves: what fits in shared memory beside the row ring, at most opt_max_fallback
+static int scan_slots(const mcp_index *idx) {
+    const size_t per = sizeof(double) * (size_t)((idx->dim + 3) & ~3);
+    const int fit = (int)((XS_SMEM_LIMIT - XS_TILE_BYTES) / per);
+    return std::max(1, std::min(fit, idx->opt_max_fallback));
+}
+static int scan_grid(const mcp_index *idx) {
+    const int64_t tiles = (idx->n_rows + XS_ROWS - 1) / XS_ROWS;
+    return (int)std::max<int64_t>(1, std::min<int64_t>(idx->n_sm, tiles));
+}
+
+// path = exact_fp64: flag_list holds `c` queries (flag_all_kernel); dense fp64 scan S slots at a time + exact select
+static int run_exact_dense(mcp_index *idx, cudaStream_t st, const float *d_q, const double *nq2, int k, int c,
+                           int32_t *out_ids, float *out_scores, double *out_scores64) {
     int rc;
-    if ((rc = idx->exact_all.ensure(sizeof(u64) * (size_t)slots * (size_t)idx->n_rows))) return rc;
-    if (sizeof(int) * (size_t)slots > idx->slot_ticket.cap) {
-        if ((rc = idx->slot_ticket.ensure(sizeof(int) * (size_t)std::max(slots, 64)))) return rc;
-        CU(cudaMemsetAsync(idx->slot_ticket.p, 0, idx->slot_ticket.cap, st));
-    }
+    const int S = scan_slots(idx);
+    if ((rc = idx->exact_all.ensure(sizeof(u64) * (size_t)S * (size_t)idx->n_rows))) return rc;
     int *flag_list = idx->flags.as<int>() + 8, *n_flag = idx->flags.as<int>();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
-    const int64_t want = (idx->n_rows + EXSEL_THREADS - 1) / EXSEL_THREADS;
-    const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)idx->n_sm * 2, want));
-    CU(launch_pdl(exact_fallback_kernel, dim3(gx, slots), dim3(EXSEL_THREADS), sizeof(float) * idx->dim, st,
-                  idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag,
-                  k, idx->id_base, idx->exact_all.as<u64>(), idx->slot_ticket.as<int>(), out_ids, out_scores, out_scores64,
-                  fold_status ? n_flag + 1 : nullptr, fold_status ? idx->h_status_dev : nullptr));
+    for (int s0 = 0; s0 < c; s0 += S) {
+        const int sc = std::min(S, c - s0);
+        exact_scan2_kernel<<<scan_grid(idx), XS_THREADS, XS_SMEM_BYTES(idx->dim, S), st>>>(
+            idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag, s0, S,
+            idx->exact_all.as<u64>(), XsSparse{});
+        KL();
+        exact_select_kernel<<<sc, EXSEL_THREADS, 0, st>>>(idx->exact_all.as<u64>(), idx->n_rows, k, idx->id_base, flag_list, n_flag, s0,
+                                                          out_ids, out_scores, out_scores64);
+        KL();
+    }
+    return MCP_OK;
+}
+
+// The certificate's fallback, device-driven: one sparse fp64 scan over however many queries were flagged (none, normally:
+// the kernel then exits at once) and one pick kernel that writes their exact top k and folds the status words.
+static int run_fallback(mcp_index *idx, cudaStream_t st, const float *d_q, const double *nq2, int k, int cq, int q_base,
+                        int32_t *out_ids, float *out_scores, double *out_scores64) {
+    int rc;
+    const size_t need = (size_t)cq * XS_SPARSE_CAP;
+    if (sizeof(int) * (size_t)cq > idx->sp_cnt.cap) {
+        if ((rc = idx->sp_cnt.ensure(sizeof(int) * (size_t)std::max(cq, 1024)))) return rc;
+        CU(cudaMemsetAsync(idx->sp_cnt.p, 0, idx->sp_cnt.cap, st));
+    }
+    if ((rc = idx->sp_keys.ensure(sizeof(u64) * need))) return rc;
+    if ((rc = idx->sp_rows.ensure(sizeof(int) * need))) return rc;
+    int *flag_list = idx->flags.as<int>() + 8, *n_flag = idx->flags.as<int>();
+    const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
+    XsSparse sp{idx->bound_key.as<u64>(), idx->bound_row.as<int>(), idx->sp_keys.as<u64>(), idx->sp_rows.as<int>(), idx->sp_cnt.as<int>(), XS_SPARSE_CAP};
+    const int S = scan_slots(idx);
+    CU(launch_pdl(exact_scan2_kernel, dim3(scan_grid(idx)), dim3(XS_THREADS), XS_SMEM_BYTES(idx->dim, S), st,
+                  idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag, 0, S,
+                  (u64 *)nullptr, sp));
+    KL();
+    CU(launch_pdl(exact_pick_kernel, dim3(std::min(cq, 2 * idx->n_sm)), dim3(256), 0, st, flag_list, n_flag, sp, k, idx->id_base, q_base,
+                  out_ids, out_scores, out_scores64, n_flag + 1, idx->h_status_dev, idx->unres.as<int>(), UNRES_MAX));
     KL();
     return MCP_OK;
 }
@@ -596,6 +639,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     // flags: [0] n_flag (zero between kernels) [1] certificate failures [2] unresolved (both since last sync_status) [8..] list
     int *n_flag = idx->flags.as<int>(), *flag_list = n_flag + 8;
     if ((rc = idx->drop_min.ensure(sizeof(unsigned int) * nq))) return rc;
+    if ((rc = idx->bound_key.ensure(sizeof(u64) * nq))) return rc;
+    if ((rc = idx->bound_row.ensure(sizeof(int) * nq))) return rc;
     if ((rc = idx->nq2f.ensure(sizeof(float) * nq))) return rc;
     // coarse kernels only need fp32 norms; the exact fp64 norm of each query is computed inside the fused rescoring
     // kernel (as one more chain), so nothing serial sits in front of the scan
@@ -624,12 +669,12 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     idx->stats.searches++; idx->stats.queries += nq; idx->stats.last_path = path; idx->stats.last_kprime = kprime;
 
     if (path == MCP_PATH_EXACT_FP64) {
-        const int slots = idx->opt_max_fallback;
+        const int slots = 256;                     // flag list entries per round (the scan takes them scan_slots() at a time)
         for (int q0 = 0; q0 < nq; q0 += slots) {
             int c = std::min(slots, nq - q0);
             flag_all_kernel<<<(c + 127) / 128, 128, 0, st>>>(flag_list, n_flag, q0, c);
             KL();
-            if ((rc = run_exact(idx, st, d_q, idx->nq2.as<double>(), k, c, out_ids, out_scores, out_scores64, false))) return rc;
+            if ((rc = run_exact_dense(idx, st, d_q, idx->nq2.as<double>(), k, c, out_ids, out_scores, out_scores64))) return rc;
         }
         clear_flag_kernel<<<1, 1, 0, st>>>(n_flag);
         KL();
@@ -727,14 +772,15 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
                           idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
                           out_scores + (int64_t)q0 * k, out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, flag_list, n_flag,
                           is_gemm_path(path) ? idx->drop_min.as<unsigned int>() + q0 : nullptr,
-                          is_gemm_path(path) ? idx->rho_q.as<float>() + 2 * q0 : nullptr));
+                          is_gemm_path(path) ? idx->rho_q.as<float>() + 2 * q0 : nullptr,
+                          idx->bound_key.as<u64>(), idx->bound_row.as<int>()));
             KL();
         }
         // certificate failures: fp64 scan on the device, flag_list holds chunk-local query numbers
-        if ((rc = run_exact(idx, st, dq, idx->nq2.as<double>() + q0, k, idx->opt_max_fallback, out_ids + (int64_t)q0 * k, out_scores + (int64_t)q0 * k,
-                            out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr, true)))
+        if ((rc = run_fallback(idx, st, dq, idx->nq2.as<double>() + q0, k, cq, q0, out_ids + (int64_t)q0 * k, out_scores + (int64_t)q0 * k,
+                               out_scores64 ? out_scores64 + (int64_t)q0 * k : nullptr)))
             return rc;
-        // flags[1] failures, [2] unresolved, [3] ticket: folded by exact_fallback_kernel's last CTA
+        // flags[1] failures, [2] unresolved, [3] ticket: folded by exact_pick_kernel's last CTA
         idx->stats.rows_scanned += n;
         idx->stats.bytes_scanned += path == MCP_PATH_GEMM_F16 ? n * idx->ldh * 2 : n * (int64_t)dim * 4;
         idx->stats.candidates_rescored += (int64_t)cq * kc;
@@ -748,6 +794,32 @@ static int validate_search(const mcp_index *idx, const void *q, int nq, int k, c
     if (nq < 1 || nq > 4000) return fail(MCP_EINVAL, "n_queries %d outside [1, 4000]", nq);
     if (k < 1 || k > MCP_MAX_K) return fail(MCP_EINVAL, "k %d outside [1, %d]", k, MCP_MAX_K);
     return MCP_OK;
+}
+
+// Re-answer the queries listed in idx->unres with the dense fp64 scan (one at a time: this is the rare path behind the rare
+// path) and clear the list.  Synchronises the stream.
+static int resolve_leftovers(mcp_index *idx, const float *d_q, int nq, int k, int32_t *out_ids, float *out_scores,
+                             double *out_scores64, cudaStream_t st) {
+    std::vector<int> h(1 + UNRES_MAX);
+    CU(cudaMemcpyAsync(h.data(), idx->unres.p, sizeof(int) * (1 + UNRES_MAX), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemsetAsync(idx->unres.p, 0, sizeof(int), st));
+    CU(cudaStreamSynchronize(st));
+    const int n = h[0];
+    const int saved = idx->opt_path;
+    idx->opt_path = MCP_PATH_EXACT_FP64;
+    int rc = MCP_OK;
+    if (n > UNRES_MAX) {                                  // more than the list holds: the whole batch
+        rc = search_locked(idx, d_q, nq, k, out_ids, out_scores, out_scores64, st);
+    } else {
+        for (int i = 0; i < n && !rc; ++i) {
+            const int q = h[1 + i];
+            if (q < 0 || q >= nq) continue;
+            rc = search_locked(idx, d_q + (int64_t)q * idx->dim, 1, k, out_ids + (int64_t)q * k, out_scores + (int64_t)q * k,
+                               out_scores64 ? out_scores64 + (int64_t)q * k : nullptr, st);
+        }
+    }
+    idx->opt_path = saved;
+    return rc;
 }
 
 extern "C" int mcp_index_search_device(mcp_index *idx, const float *queries_device, int n_queries, int k,
@@ -791,6 +863,24 @@ extern "C" int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_fail
     return MCP_OK;
 }
 
+extern "C" int mcp_index_repair_device(mcp_index *idx, const float *queries_device, int n_queries, int k,
+                                       int32_t *out_ids_device, float *out_scores_device, double *out_scores64_device,
+                                       void *stream) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    int rc = validate_search(idx, queries_device, n_queries, k, out_ids_device, out_scores_device);
+    if (rc) return rc;
+    CU(cudaSetDevice(idx->device));
+    if ((rc = require_local(queries_device, sizeof(float) * (size_t)n_queries * idx->dim, idx->device, "repair_device queries"))) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if ((rc = order_after_previous(idx, st))) return rc;
+    if (idx->pending) { CU(cudaEventSynchronize(idx->done)); idx->pending = false; }
+    rc = resolve_leftovers(idx, queries_device, n_queries, k, out_ids_device, out_scores_device, out_scores64_device, st);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(st));
+    return MCP_OK;
+}
+
 extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n_queries, int k, int32_t *out_ids,
                                 float *out_scores, double *out_scores64) {
     if (check_idx(idx)) return MCP_EINVAL;
@@ -826,22 +916,22 @@ extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n
     int32_t *d_ids = reinterpret_cast<int32_t *>(dbase + off_ids);
     float *d_sc = reinterpret_cast<float *>(dbase + off_sc);
     CU(cudaMemcpyAsync(idx->q_copy.p, queries_host, sizeof(float) * (size_t)n_queries * idx->dim, cudaMemcpyHostToDevice, st));
-    for (int attempt = 0; attempt < 2; ++attempt) {
-        int saved = idx->opt_path;
-        if (attempt == 1) idx->opt_path = MCP_PATH_EXACT_FP64;      // leftovers beyond the device-side fallback slots (rare)
-        rc = search_locked(idx, idx->q_copy.as<float>(), n_queries, k, d_ids, d_sc, d_s64, st);
-        idx->opt_path = saved;
+    rc = search_locked(idx, idx->q_copy.as<float>(), n_queries, k, d_ids, d_sc, d_s64, st);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(idx->h_stage, dbase, total, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
+    CU(cudaStreamSynchronize(st));
+    const int hs[2] = {idx->h_status[0], idx->h_status[1]};
+    idx->h_status[0] = idx->h_status[1] = 0;
+    idx->stats.certificate_failures += hs[0];
+    idx->stats.exact_scans += hs[0] - hs[1];
+    if (hs[1] > 0) {
+        // Queries whose fallback list overflowed (thousands of rows inside the coarse error band of the k-th score): exactly
+        // those are re-answered by the dense fp64 scan, each into its own rows of the result; nothing else is recomputed.
+        rc = resolve_leftovers(idx, idx->q_copy.as<float>(), n_queries, k, d_ids, d_sc, d_s64, st);
         if (rc) return rc;
         CU(cudaMemcpyAsync(idx->h_stage, dbase, total, cudaMemcpyDeviceToHost, st));
-        CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
         CU(cudaStreamSynchronize(st));
-        const int hs[2] = {idx->h_status[0], idx->h_status[1]};
-        idx->h_status[0] = idx->h_status[1] = 0;
-        if (attempt == 0) {
-            idx->stats.certificate_failures += hs[0];
-            idx->stats.exact_scans += hs[0] - hs[1];
-        }
-        if (hs[1] == 0) break;
     }
     memcpy(out_ids, idx->h_stage + off_ids, sizeof(int32_t) * nk);
     memcpy(out_scores, idx->h_stage + off_sc, sizeof(float) * nk);
@@ -908,19 +998,42 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
 // ---------------------------------------------------------------------------------------------
 // shard merge
 // ---------------------------------------------------------------------------------------------
-extern "C" int mcp_merge_topk_device(const double *scores64_device, const int32_t *ids_device, int n_shards,
-                                     int n_queries, int k, int32_t *out_ids_device, float *out_scores_device,
-                                     double *out_scores64_device, void *stream) {
-    if (!scores64_device || !ids_device || !out_ids_device || !out_scores_device) return fail(MCP_EINVAL, "NULL buffer");
+static int merge_launch(const double *scores64, const int32_t *ids, int64_t stride_s, int64_t stride_i, int n_shards, int n_queries,
+                        int k, int32_t *out_ids, float *out_scores, double *out_scores64, void *stream) {
+    if (!scores64 || !ids || !out_ids || !out_scores) return fail(MCP_EINVAL, "NULL buffer");
     if (n_shards < 1 || n_queries < 1 || k < 1 || k > MCP_MAX_K) return fail(MCP_EINVAL, "bad sizes");
     if ((int64_t)n_shards * k > MERGE_MAX) return fail(MCP_EINVAL, "n_shards * k = %d exceeds %d", n_shards * k, MERGE_MAX);
     int npow2 = pow2_at_least(std::max(n_shards * k, 2));
     size_t smem = (size_t)npow2 * (sizeof(u64) + sizeof(int));
     CU(cudaFuncSetAttribute(merge_shards_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     merge_shards_kernel<<<n_queries, MERGE_THREADS, smem, (cudaStream_t)stream>>>(
-        scores64_device, ids_device, n_shards, n_queries, k, npow2, out_ids_device, out_scores_device, out_scores64_device);
+        scores64, ids, n_shards, stride_s, stride_i, n_queries, k, npow2, out_ids, out_scores, out_scores64);
     KCHECK();
     return MCP_OK;
+}
+
+extern "C" int mcp_merge_topk_device(const double *scores64_device, const int32_t *ids_device, int n_shards,
+                                     int n_queries, int k, int32_t *out_ids_device, float *out_scores_device,
+                                     double *out_scores64_device, void *stream) {
+    const int64_t qk = (int64_t)n_queries * k;
+    return merge_launch(scores64_device, ids_device, qk, qk, n_shards, n_queries, k, out_ids_device, out_scores_device,
+                        out_scores64_device, stream);
+}
+
+extern "C" int64_t mcp_merge_packed_block_bytes(int n_queries, int k) {
+    const int64_t qk = (int64_t)n_queries * k;
+    return (qk * 12 + 15) & ~(int64_t)15;
+}
+
+extern "C" int mcp_merge_topk_packed_device(const void *packed_device, int n_shards, int n_queries, int k,
+                                            int32_t *out_ids_device, float *out_scores_device, double *out_scores64_device,
+                                            void *stream) {
+    if (!packed_device) return fail(MCP_EINVAL, "NULL buffer");
+    if (((uintptr_t)packed_device) & 15) return fail(MCP_EINVAL, "packed buffer must be 16-byte aligned");
+    const int64_t qk = (int64_t)n_queries * k, block = mcp_merge_packed_block_bytes(n_queries, k);
+    const unsigned char *base = static_cast<const unsigned char *>(packed_device);
+    return merge_launch(reinterpret_cast<const double *>(base), reinterpret_cast<const int32_t *>(base + qk * 8), block / 8, block / 4,
+                        n_shards, n_queries, k, out_ids_device, out_scores_device, out_scores64_device, stream);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1071,14 +1184,13 @@ extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float
     // every query's norm is rewritten here; nothing from an earlier call is read
     prep_rows_kernel<true><<<1, PREP_ROWS, 0, st>>>(queries_device, n_queries, dim, dim, nq2, inv_nq, qflag, nullptr);
     KCHECK();
-    const int64_t want = (idx->n_rows + 255) / 256;
-    const int gx = (int)std::min<int64_t>((int64_t)idx->n_sm * 8, want);
+    const int gx = scan_grid(idx);
     for (int q = 0; q < n_queries; ++q) {
         flag_all_kernel<<<1, 32, 0, st>>>(flag_list, n_flag, q, 1);        // (re)sets the flag word and the one-entry list
         KCHECK();
-        exact_scan_kernel<<<dim3(gx, 1), 256, sizeof(float) * dim, st>>>(idx->d_rows, idx->n_rows, dim, idx->ld, queries_device,
-                                                                       nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list,
-                                                                       n_flag, 0, scores);   // writes scores[0 .. n_rows)
+        exact_scan2_kernel<<<gx, XS_THREADS, XS_SMEM_BYTES(dim, 1), st>>>(idx->d_rows, idx->n_rows, dim, idx->ld, queries_device,
+                                                                         nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list,
+                                                                         n_flag, 0, 1, scores, XsSparse{});   // writes scores[0 .. n_rows)
         KCHECK();
         exact_select_kernel<<<1, EXSEL_THREADS, 0, st>>>(scores, idx->n_rows, k, idx->id_base, flag_list, n_flag, 0,
                                                           out_ids_device, out_scores_device, out_scores64_device);

@@ -10,6 +10,8 @@
 
 __global__ void __launch_bounds__(MERGE_THREADS)
 merge_shards_kernel(const double *__restrict__ scores64, const int32_t *__restrict__ ids, int n_shards,
+                    int64_t shard_stride_scores /* doubles between two shards' score blocks */,
+                    int64_t shard_stride_ids /* int32s between two shards' id blocks */,
                     int n_queries, int k, int npow2, int32_t *__restrict__ out_ids,
                     float *__restrict__ out_scores, double *__restrict__ out_scores64) {
     extern __shared__ unsigned char smem_raw[];
@@ -21,9 +23,9 @@ merge_shards_kernel(const double *__restrict__ scores64, const int32_t *__restri
         u64 key = ~0ull; int id = MCP_PAD_ROW;
         if (i < total) {
             int s = i / k, j = i - s * k;
-            int64_t o = ((int64_t)s * n_queries + q) * k + j;
-            int32_t v = ids[o];
-            if (v >= 0) { key = f64_ord(scores64[o]); id = v; }
+            int64_t o = (int64_t)q * k + j;
+            int32_t v = ids[(int64_t)s * shard_stride_ids + o];
+            if (v >= 0) { key = f64_ord(scores64[(int64_t)s * shard_stride_scores + o]); id = v; }
         }
         sk[i] = key; sv[i] = id;
     }

@@ -110,7 +110,9 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
                         int32_t *__restrict__ out_ids, float *__restrict__ out_scores, double *__restrict__ out_scores64,
                         int *__restrict__ flag_list, int *__restrict__ n_flag,
                         const unsigned int *__restrict__ drop_min /* NULL, or [q]: best coarse score the scan dropped outside its lists */,
-                        const float *__restrict__ rho_q /* NULL, or [q][2]: the query's rounding residual ratios (tf32, fp16) */) {
+                        const float *__restrict__ rho_q /* NULL, or [q][2]: the query's rounding residual ratios (tf32, fp16) */,
+                        u64 *__restrict__ bound_key, int *__restrict__ bound_row /* [q]: for a flagged query, the k-th best exact (score, row)
+                                                                                    pair among its candidates -- what the fp64 scan filters with */) {
     extern __shared__ __align__(16) unsigned char rf_raw[];
     __shared__ int s_row[RF_MAXG * RS_ROWS];
     __shared__ const float *s_rowptr[RF_MAXG * RS_ROWS];
@@ -318,49 +320,212 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
             }
             pass = (sk_k == sk_k) && (sk_k < T - eps);
         }
-        if (!pass) flag_list[atomicAdd(n_flag, 1)] = q;
+        if (!pass) {
+            flag_list[atomicAdd(n_flag, 1)] = q;
+            // the true k-th pair cannot exceed the k-th pair of any k rows; pads (fewer than k candidates) mean "no bound"
+            bound_key[q] = sk[k - 1]; bound_row[q] = sv[k - 1];
+        }
     }
 }
 
-// ---- K4c: fp64 scan of every row for the flagged queries ---------------------------------------
-// grid (blocks, max_fallback); slot f serves query flag_list[slot0 + f]; slots past *n_flag exit.
-__global__ void __launch_bounds__(256)
-exact_scan_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64_t ld,
-                  const float *__restrict__ queries, const double *__restrict__ nq2,
-                  const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
-                  const int *__restrict__ flag_list, const int *__restrict__ n_flag, int slot0,
-                  u64 *__restrict__ exact_all /* [slots][n_rows] */) {
-    extern __shared__ float sqv[];
-    int f = blockIdx.y;
-    if (slot0 + f >= *n_flag) return;
-    int q = flag_list[slot0 + f];
-    const float *qv = queries + (int64_t)q * dim;
-    for (int i = threadIdx.x; i < dim; i += blockDim.x) sqv[i] = qv[i];
-    __syncthreads();
-    double qn2 = nq2[q];
-    u64 *out = exact_all + (int64_t)f * n_rows;
-    int d4 = dim & ~3;
-    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
-        const float *e = rows + r * ld;
-        ExactAcc a; a.acc = 0.0;
-        if (metric == 0) {
-            for (int i = 0; i < d4; i += 4) {
-                float4 v = *reinterpret_cast<const float4 *>(e + i);
-                a.cos_step(sqv[i], v.x); a.cos_step(sqv[i + 1], v.y);
-                a.cos_step(sqv[i + 2], v.z); a.cos_step(sqv[i + 3], v.w);
+// ---- K4c: fp64 scan of every row for the flagged queries ---------------------------------------------------------
+// The certificate's fallback, the explicit path = exact_fp64 and the allocation-free entry point all run this kernel.
+// It streams the table once per pass for up to S flagged queries ("slots") at a time:
+//   * rows come in through a cp.async ring of [XS_ROWS rows][XS_COLS columns] tiles (256 contiguous bytes per row and
+//     chunk), so HBM is read in full lines -- a thread walking its own 6 KB row with loads 6 KB apart, as the first
+//     version did, ran at a fraction of the HBM rate;
+//   * thread = (row of the tile, half of the slots): it walks ITS row in index order, one fp64 chain per slot it owns (the
+//     oracle's arithmetic and order, so scores are bit-equal), reading the queries as fp64 from shared memory (warp-wide
+//     broadcasts) -- up to four independent chains per thread hide the DFMA latency.
+// Output, dense mode: the ordered fp64 image of every score, [slot][n_rows] (exact_select_kernel then picks the top k).
+// Output, sparse mode: only rows whose (score, row) pair is at or below the query's bound -- the k-th best exact pair among
+// the candidates the coarse pass found, which the true k-th pair cannot exceed -- appended to a short per-slot list.  A
+// handful of rows per query instead of n_rows scores, so the fallback needs no n_rows-sized scratch and serves any number
+// of flagged queries in one launch (the kernel loops over them S at a time).
+#define XS_ROWS 128
+#define XS_COLS 64
+#define XS_PITCH (XS_COLS + 4)          // 68 floats = 17 x 16 B: float4 reads of 8 consecutive rows hit 8 different bank groups
+#define XS_STAGES 3
+#define XS_THREADS 256
+#define XS_MAXS 8
+#define XS_SPARSE_CAP 2048
+#define XS_TILE_BYTES (sizeof(float) * XS_STAGES * XS_ROWS * XS_PITCH)
+#define XS_SMEM_BYTES(dim, S) (sizeof(double) * (size_t)(S) * (size_t)(((dim) + 3) & ~3) + XS_TILE_BYTES)
+
+struct XsSparse {
+    const u64 *bound_key;      // [query] ordered fp64 image of the bound score (all-ones: no bound)
+    const int *bound_row;      // [query] row of the bound pair
+    u64 *keys;                 // [slot][cap]
+    int *rows;                 // [slot][cap]
+    int *cnt;                  // [slot] appended so far (may exceed cap: the list overflowed); zero on entry
+    int cap;
+};
+
+__global__ void __launch_bounds__(XS_THREADS, 1)
+exact_scan2_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64_t ld,
+                   const float *__restrict__ queries, const double *__restrict__ nq2,
+                   const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
+                   const int *__restrict__ flag_list, const int *__restrict__ n_flag, int slot0, int S,
+                   u64 *__restrict__ dense /* [S][n_rows] for slots slot0 .. slot0+S-1, or NULL: sparse */, XsSparse sp) {
+    extern __shared__ __align__(16) unsigned char xs_raw[];
+    pdl_trigger();
+    pdl_wait();                                      // the kernel that flagged queries has completed
+    const int nf_all = *n_flag;
+    const int g_end = dense ? min(nf_all, slot0 + S) : nf_all;
+    if (slot0 >= g_end) return;                      // nothing flagged: the common case
+    const int dimp = (dim + 3) & ~3;
+    double *sq = reinterpret_cast<double *>(xs_raw);                 // [S][dimp] the pass's queries in fp64
+    float *tile = reinterpret_cast<float *>(sq + (size_t)S * dimp);  // [XS_STAGES][XS_ROWS][XS_PITCH]
+    const int row_l = threadIdx.x & (XS_ROWS - 1), half = threadIdx.x / XS_ROWS;
+    const int nchunks = (dimp + XS_COLS - 1) / XS_COLS;
+    const int64_t n_tiles = (n_rows + XS_ROWS - 1) / XS_ROWS;
+    const int my_tiles = (int64_t)blockIdx.x < n_tiles ? (int)((n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+    const int n_it = my_tiles * nchunks;
+    auto issue = [&](int it) {
+        if (it < n_it) {
+            const int ti = it / nchunks, c = it - ti * nchunks, st = it % XS_STAGES;
+            const int64_t r0 = ((int64_t)blockIdx.x + (int64_t)ti * gridDim.x) * XS_ROWS;
+            float *dst = tile + (size_t)st * XS_ROWS * XS_PITCH;
+#pragma unroll
+            for (int u = 0; u < XS_ROWS * (XS_COLS / 4) / XS_THREADS; ++u) {
+                const int e = threadIdx.x + u * XS_THREADS, r = e / (XS_COLS / 4), ch = e % (XS_COLS / 4);
+                const int col = c * XS_COLS + ch * 4;
+                if (col < dimp) cp_async16(dst + r * XS_PITCH + ch * 4, rows + min(r0 + r, n_rows - 1) * ld + col);
             }
-            for (int i = d4; i < dim; ++i) a.cos_step(sqv[i], e[i]);
-        } else {
-            for (int i = 0; i < d4; i += 4) {
-                float4 v = *reinterpret_cast<const float4 *>(e + i);
-                a.l2_step(sqv[i], v.x); a.l2_step(sqv[i + 1], v.y);
-                a.l2_step(sqv[i + 2], v.z); a.l2_step(sqv[i + 3], v.w);
-            }
-            for (int i = d4; i < dim; ++i) a.l2_step(sqv[i], e[i]);
         }
-        double s = exact_finish(a.acc, metric, qn2, ne2[r]);
-        if (penalty) s = s + (double)penalty[r];
-        out[r] = f64_ord(s);
+        cp_async_commit();
+    };
+    for (int s0 = slot0; s0 < g_end; s0 += S) {
+        const int sc = min(S, g_end - s0);           // slots of this pass
+        __syncthreads();                             // the previous pass has left sq and the ring
+        for (int u = 0; u < sc; ++u) {
+            const float *qv = queries + (int64_t)flag_list[s0 + u] * dim;
+            for (int i = threadIdx.x; i < dimp; i += XS_THREADS) sq[(size_t)u * dimp + i] = i < dim ? (double)qv[i] : 0.0;
+        }
+        // my slots: half, half + 2, half + 4, half + 6
+        const int myn = sc > half ? (sc - half + 1) / 2 : 0;
+        int myq[4]; double mynq2[4]; u64 mybk[4]; int mybr[4];
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+            myq[v] = v < myn ? flag_list[s0 + half + 2 * v] : 0;
+            mynq2[v] = v < myn ? nq2[myq[v]] : 1.0;
+            mybk[v] = (v < myn && !dense) ? sp.bound_key[myq[v]] : ~0ull;
+            mybr[v] = (v < myn && !dense) ? sp.bound_row[myq[v]] : 0x7FFFFFFF;
+        }
+        for (int it = 0; it < XS_STAGES - 1; ++it) issue(it);
+        double acc[4] = {0.0, 0.0, 0.0, 0.0};
+        for (int it = 0; it < n_it; ++it) {
+            issue(it + XS_STAGES - 1);
+            cp_async_wait<XS_STAGES - 1>();
+            __syncthreads();                         // chunk `it` has landed for every thread (and sq is complete on the first turn)
+            const int ti = it / nchunks, c = it - ti * nchunks;
+            const int c0 = c * XS_COLS, w = min(XS_COLS, dimp - c0);
+            const float *e = tile + (size_t)(it % XS_STAGES) * XS_ROWS * XS_PITCH + row_l * XS_PITCH;
+            if (c == 0) { acc[0] = acc[1] = acc[2] = acc[3] = 0.0; }
+            if (myn > 0) {
+                for (int j = 0; j < w; j += 4) {
+                    const float4 x = *reinterpret_cast<const float4 *>(e + j);
+                    const double d0 = (double)x.x, d1 = (double)x.y, d2 = (double)x.z, d3 = (double)x.w;
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) {
+                        if (v < myn) {
+                            const double *qq = sq + (size_t)(half + 2 * v) * dimp + c0 + j;
+                            const double2 qa = *reinterpret_cast<const double2 *>(qq), qb = *reinterpret_cast<const double2 *>(qq + 2);
+                            if (metric == 0) {
+                                acc[v] = fma(qa.x, d0, acc[v]); acc[v] = fma(qa.y, d1, acc[v]);
+                                acc[v] = fma(qb.x, d2, acc[v]); acc[v] = fma(qb.y, d3, acc[v]);
+                            } else {
+                                double t;
+                                t = __dsub_rn(qa.x, d0); acc[v] = __dadd_rn(acc[v], __dmul_rn(t, t));
+                                t = __dsub_rn(qa.y, d1); acc[v] = __dadd_rn(acc[v], __dmul_rn(t, t));
+                                t = __dsub_rn(qb.x, d2); acc[v] = __dadd_rn(acc[v], __dmul_rn(t, t));
+                                t = __dsub_rn(qb.y, d3); acc[v] = __dadd_rn(acc[v], __dmul_rn(t, t));
+                            }
+                        }
+                    }
+                }
+            }
+            if (c == nchunks - 1) {
+                const int64_t row = ((int64_t)blockIdx.x + (int64_t)ti * gridDim.x) * XS_ROWS + row_l;
+                if (row < n_rows && myn > 0) {
+                    const double ne2r = ne2[row], pr = penalty ? (double)penalty[row] : 0.0;
+#pragma unroll
+                    for (int v = 0; v < 4; ++v) {
+                        if (v < myn) {
+                            double sco = exact_finish(acc[v], metric, mynq2[v], ne2r);
+                            if (penalty) sco = sco + pr;
+                            const u64 key = f64_ord(sco);
+                            const int slot = s0 + half + 2 * v;
+                            if (dense) __stcg(dense + (int64_t)(slot - slot0) * n_rows + row, key);
+                            else if (key < mybk[v] || (key == mybk[v] && row <= (int64_t)mybr[v])) {
+                                const int p = atomicAdd(&sp.cnt[slot], 1);
+                                if (p < sp.cap) { sp.keys[(int64_t)slot * sp.cap + p] = key; sp.rows[(int64_t)slot * sp.cap + p] = (int)row; }
+                            }
+                        }
+                    }
+                }
+            }
+            __syncthreads();                         // everyone has left this stage before the next turn refills it
+        }
+        cp_async_wait<0>();
+    }
+}
+
+// ---- sparse lists -> top k, one CTA per flagged query; folds the status words -------------------------------------
+// status: [0] certificate failures, [1] unresolved (a sparse list overflowed: the bound let more than `cap` rows through --
+// only data with thousands of rows inside the coarse error band of the k-th score does that), [2] ticket.  The last CTA
+// mirrors the totals into host-mapped memory, so the host needs no copy to learn them.  unres: [0] count, [1..] global query
+// numbers of the unresolved queries (the host entry point re-answers exactly those with the dense scan).
+__global__ void __launch_bounds__(256)
+exact_pick_kernel(const int *__restrict__ flag_list, const int *__restrict__ n_flag, XsSparse sp, int k, int64_t id_base,
+                  int q_base, int32_t *__restrict__ out_ids, float *__restrict__ out_scores, double *__restrict__ out_scores64,
+                  int *__restrict__ status, volatile int *host_status, int *__restrict__ unres, int unres_cap) {
+    __shared__ u64 sk[XS_SPARSE_CAP];
+    __shared__ int sv[XS_SPARSE_CAP];
+    pdl_trigger();
+    pdl_wait();
+    const int nf = *n_flag;
+    for (int f = blockIdx.x; f < nf; f += gridDim.x) {
+        const int q = flag_list[f];
+        const int c = sp.cnt[f];
+        __syncthreads();                             // everyone has read the count (and left sk / sv of the previous turn)
+        if (threadIdx.x == 0) sp.cnt[f] = 0;         // ready for the next launch
+        if (c > sp.cap) {
+            if (threadIdx.x == 0) {
+                atomicAdd(&status[1], 1);
+                const int p = atomicAdd(&unres[0], 1);
+                if (p < unres_cap) unres[1 + p] = q_base + q;
+            }
+            continue;
+        }
+        int np2 = 2;
+        while (np2 < c) np2 <<= 1;
+        np2 = max(np2, 2);
+        for (int i = threadIdx.x; i < np2; i += blockDim.x) {
+            const bool real = i < c;
+            sk[i] = real ? sp.keys[(int64_t)f * sp.cap + i] : ~0ull;
+            sv[i] = real ? sp.rows[(int64_t)f * sp.cap + i] : MCP_PAD_ROW;
+        }
+        cta_bitonic_sort_pairs(sk, sv, np2);
+        for (int i = threadIdx.x; i < k; i += blockDim.x) {
+            const int64_t o = (int64_t)q * k + i;
+            const bool real = i < c && sv[i] != MCP_PAD_ROW;
+            const double s = real ? ord_f64(sk[i]) : CUDART_INF;
+            out_ids[o] = real ? (int32_t)(id_base + sv[i]) : -1;
+            out_scores[o] = (float)s;
+            if (out_scores64) out_scores64[o] = s;
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int t = atomicAdd(&status[2], 1);
+        if (t == (int)gridDim.x - 1) {
+            status[2] = 0;
+            __threadfence();
+            status[0] += nf;
+            if (host_status) { host_status[0] = status[0]; host_status[1] = *(volatile int *)&status[1]; __threadfence_system(); }
+        }
     }
 }
 
@@ -462,69 +627,3 @@ exact_select_kernel(const u64 *__restrict__ exact_all, int64_t n_rows, int k, in
     exact_select_body(exact_all + (int64_t)f * n_rows, n_rows, k, id_base, flag_list[slot0 + f], out_ids, out_scores, out_scores64);
 }
 
-// ---- K4c + K4d in one launch: the certificate's fallback ------------------------------------------------------------
-// grid (blocks, slots) x EXSEL_THREADS.  Slot f serves query flag_list[f]; slots past *n_flag exit at once, which is
-// the common case (no certificate failed), so the search pays one empty launch here instead of two.  The CTAs of a
-// live slot scan the table in fp64, and the last of them to finish (per-slot ticket) selects the slot's top k.
-__global__ void __launch_bounds__(EXSEL_THREADS)
-exact_fallback_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64_t ld,
-                      const float *__restrict__ queries, const double *__restrict__ nq2,
-                      const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
-                      const int *__restrict__ flag_list, const int *__restrict__ n_flag, int k, int64_t id_base,
-                      u64 *__restrict__ exact_all /* [slots][n_rows] */, int *__restrict__ slot_ticket /* [slots], zero */,
-                      int32_t *__restrict__ out_ids, float *__restrict__ out_scores, double *__restrict__ out_scores64,
-                      int *__restrict__ status /* NULL, or [failures, unresolved] */, volatile int *host_status) {
-    extern __shared__ float sqv[];
-    __shared__ int s_last;
-    pdl_wait();                                      // the kernel that flagged queries has completed
-    const int f = blockIdx.y;
-    const int nf = *n_flag;
-    if (status && blockIdx.x == 0 && f == 0 && threadIdx.x == 0) {
-        // one thread folds this batch's flag count into the running status and mirrors it into host-mapped memory, so
-        // the host needs no copy node to read it.  The count itself is left alone (other CTAs may not have read it
-        // yet): the first kernel of the next search, or clear_flag_kernel between query chunks, clears it.
-        status[0] += nf;
-        status[1] += nf > (int)gridDim.y ? nf - (int)gridDim.y : 0;
-        if (host_status) { host_status[0] = status[0]; host_status[1] = status[1]; __threadfence_system(); }
-    }
-    if (f >= nf) return;
-    const int q = flag_list[f];
-    const float *qv = queries + (int64_t)q * dim;
-    for (int i = threadIdx.x; i < dim; i += blockDim.x) sqv[i] = qv[i];
-    __syncthreads();
-    const double qn2 = nq2[q];
-    u64 *out = exact_all + (int64_t)f * n_rows;
-    const int d4 = dim & ~3;
-    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
-        const float *e = rows + r * ld;
-        ExactAcc a; a.acc = 0.0;
-        if (metric == 0) {
-            for (int i = 0; i < d4; i += 4) {
-                float4 v = *reinterpret_cast<const float4 *>(e + i);
-                a.cos_step(sqv[i], v.x); a.cos_step(sqv[i + 1], v.y);
-                a.cos_step(sqv[i + 2], v.z); a.cos_step(sqv[i + 3], v.w);
-            }
-            for (int i = d4; i < dim; ++i) a.cos_step(sqv[i], e[i]);
-        } else {
-            for (int i = 0; i < d4; i += 4) {
-                float4 v = *reinterpret_cast<const float4 *>(e + i);
-                a.l2_step(sqv[i], v.x); a.l2_step(sqv[i + 1], v.y);
-                a.l2_step(sqv[i + 2], v.z); a.l2_step(sqv[i + 3], v.w);
-            }
-            for (int i = d4; i < dim; ++i) a.l2_step(sqv[i], e[i]);
-        }
-        double s = exact_finish(a.acc, metric, qn2, ne2[r]);
-        if (penalty) s = s + (double)penalty[r];
-        __stcg(out + r, f64_ord(s));                 // read back by another CTA: keep it out of this SM's L1
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        s_last = atomicAdd(&slot_ticket[f], 1) == (int)gridDim.x - 1;
-        if (s_last) slot_ticket[f] = 0;              // ready for the next launch
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    exact_select_body(out, n_rows, k, id_base, q, out_ids, out_scores, out_scores64);
-}

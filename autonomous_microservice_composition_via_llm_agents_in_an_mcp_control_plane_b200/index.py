@@ -191,6 +191,15 @@ class ServiceIndex:
             C.c_void_p(sc.data_ptr()), C.c_void_p(sc64.data_ptr()) if sc64 is not None else None, _stream_ptr()))
         return ids, sc, sc64
 
+    def repair_device(self, queries, k: int, out: tuple):
+        """After ``sync_status`` reported unresolved queries for the ``search_device`` call that produced ``out``: re-answers
+        exactly those (dense fp64 scan) in place.  Blocks."""
+        ids, sc, sc64 = out
+        nat.check(self._lib.mcp_index_repair_device(
+            self._h, C.c_void_p(queries.data_ptr()), queries.shape[0], int(k), C.c_void_p(ids.data_ptr()),
+            C.c_void_p(sc.data_ptr()), C.c_void_p(sc64.data_ptr()) if sc64 is not None else None, _stream_ptr()))
+        return out
+
     def search_exact_noalloc_device(self, queries, k: int, out: tuple):
         """fp64 full scan through ``mcp_index_search_exact_noalloc_device``: the library allocates nothing, so the
         caller hands in the outputs too -- ``out = (ids int32 [Q,k], scores fp32 [Q,k], scores fp64 [Q,k])`` CUDA
@@ -251,4 +260,38 @@ def merge_topk_device(scores64, ids, out: Optional[tuple] = None):
     nat.check(nat.lib().mcp_merge_topk_device(C.c_void_p(scores64.data_ptr()), C.c_void_p(ids.data_ptr()), s, q, k,
                                               C.c_void_p(oi.data_ptr()), C.c_void_p(os32.data_ptr()),
                                               C.c_void_p(os64.data_ptr()), _stream_ptr()))
+    return oi, os32, os64
+
+
+def packed_block_bytes(n_queries: int, k: int) -> int:
+    """Bytes of one shard's block in the packed gather buffer (``mcp_merge_topk_packed_device``)."""
+    return int(nat.lib().mcp_merge_packed_block_bytes(int(n_queries), int(k)))
+
+
+def packed_views(block, n_queries: int, k: int):
+    """(ids int32 [Q,k], scores fp64 [Q,k]) views into one shard's block (a CUDA uint8 tensor of ``packed_block_bytes``)."""
+    import torch
+
+    qk = n_queries * k
+    sc64 = block[: qk * 8].view(torch.float64).view(n_queries, k)
+    ids = block[qk * 8: qk * 12].view(torch.int32).view(n_queries, k)
+    return ids, sc64
+
+
+def merge_topk_packed_device(packed, n_shards: int, n_queries: int, k: int, out: Optional[tuple] = None):
+    """[S * block] gathered uint8 buffer -> global (ids, scores32, scores64)."""
+    import torch
+
+    if not (packed.is_cuda and packed.dtype == torch.uint8 and packed.is_contiguous()
+            and packed.numel() == n_shards * packed_block_bytes(n_queries, k)):
+        raise ValueError("packed merge needs a contiguous CUDA uint8 buffer of n_shards blocks")
+    if out is None:
+        dev = packed.device
+        out = (torch.empty((n_queries, k), dtype=torch.int32, device=dev),
+               torch.empty((n_queries, k), dtype=torch.float32, device=dev),
+               torch.empty((n_queries, k), dtype=torch.float64, device=dev))
+    oi, os32, os64 = out
+    nat.check(nat.lib().mcp_merge_topk_packed_device(C.c_void_p(packed.data_ptr()), n_shards, n_queries, k,
+                                                     C.c_void_p(oi.data_ptr()), C.c_void_p(os32.data_ptr()),
+                                                     C.c_void_p(os64.data_ptr()), _stream_ptr()))
     return oi, os32, os64

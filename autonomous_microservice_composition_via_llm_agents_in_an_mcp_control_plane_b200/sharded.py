@@ -3,7 +3,7 @@
 Partition: rank g owns the contiguous rows
 ``[g*ceil(N/S), min((g+1)*ceil(N/S), N))``; service ids stay global row numbers (``id_base``).
 Queries are replicated; every rank answers them on its shard with the exact local top-k
-(``ServiceIndex``), the sorted (score_f64, id) lists are exchanged with one all-gather
+(``ServiceIndex``), the sorted (score_f64, id) lists are exchanged with ONE all-gather of packed blocks
 (S * Q * k * 12 bytes: 6 MiB for config 3 -- latency-bound on NVLink 5 / NVSwitch) and every rank merges
 them with the K5 kernel using the same (score, id) key, so the result is identical to the
 unsharded search.  There is no other collective on the data path.
@@ -41,6 +41,30 @@ def merge_gathered_cpu(scores64: np.ndarray, ids: np.ndarray) -> Tuple[np.ndarra
     return out_ids.astype(np.int32), out_sc
 
 
+def block_bytes(n_queries: int, k: int) -> int:
+    """Bytes of one rank's block in the packed exchange: [Q*k fp64 scores][Q*k int32 ids], padded to 16 (the layout
+    ``mcp_merge_topk_packed_device`` reads; the same arithmetic as ``mcp_merge_packed_block_bytes``)."""
+    return (n_queries * k * 12 + 15) & ~15
+
+
+def pack_block_cpu(scores64: np.ndarray, ids: np.ndarray) -> np.ndarray:
+    q, k = ids.shape
+    blk = np.zeros(block_bytes(q, k), np.uint8)
+    blk[: q * k * 8] = np.ascontiguousarray(scores64, np.float64).view(np.uint8).reshape(-1)
+    blk[q * k * 8: q * k * 12] = np.ascontiguousarray(ids, np.int32).view(np.uint8).reshape(-1)
+    return blk
+
+
+def unpack_blocks_cpu(packed: np.ndarray, world: int, n_queries: int, k: int) -> Tuple[np.ndarray, np.ndarray]:
+    """gathered [world * block] uint8 -> ([S,Q,k] fp64 scores, [S,Q,k] int32 ids)."""
+    b = block_bytes(n_queries, k)
+    blocks = np.ascontiguousarray(packed, np.uint8).reshape(world, b)
+    qk = n_queries * k
+    sc = np.stack([blocks[s, : qk * 8].copy().view(np.float64).reshape(n_queries, k) for s in range(world)])
+    ids = np.stack([blocks[s, qk * 8: qk * 12].copy().view(np.int32).reshape(n_queries, k) for s in range(world)])
+    return sc, ids
+
+
 class ShardedIndex:
     """Per-rank handle: local ``ServiceIndex`` + the exchange step."""
 
@@ -58,6 +82,7 @@ class ShardedIndex:
         self.device = torch.cuda.current_device() if device is None else device
         self.local = ServiceIndex(dim, metric, self.device)
         self._gather = None
+        self._last = None
 
     def adopt_shard(self, rows, n_total: int):
         lo, hi = shard_bounds(n_total, self.world, self.rank)
@@ -70,22 +95,63 @@ class ShardedIndex:
         return self
 
     def search_device(self, queries, k: int):
-        """-> (ids, scores32, scores64) on this rank's GPU, identical on every rank."""
+        """-> (ids, scores32, scores64) on this rank's GPU, identical on every rank.  Enqueues only: the local search writes
+        its (score fp64, id) lists straight into this rank's block of one packed buffer, ONE all-gather exchanges the blocks
+        (12 B x Q x k per rank) and K5 merges them.  ``check()`` tells whether any rank left a query uncertified."""
         import torch
 
-        from .index import merge_topk_device
+        from .index import merge_topk_packed_device, packed_block_bytes, packed_views
 
-        ids, sc, sc64 = self.local.search_device(queries, k)
-        if self.world == 1:
-            return ids, sc, sc64
         q = queries.shape[0]
-        if self._gather is None or self._gather[0].shape != (self.world, q, k):
-            self._gather = (torch.empty((self.world, q, k), dtype=torch.float64, device=queries.device),
-                            torch.empty((self.world, q, k), dtype=torch.int32, device=queries.device))
-        g_sc, g_ids = self._gather
-        self.dist.all_gather_into_tensor(g_sc.view(-1), sc64.view(-1), group=self.group)
-        self.dist.all_gather_into_tensor(g_ids.view(-1), ids.view(-1), group=self.group)
-        return merge_topk_device(g_sc, g_ids)
+        if self.world == 1:
+            self._last = (queries, k, None)
+            return self.local.search_device(queries, k)
+        blk = packed_block_bytes(q, k)
+        if self._gather is None or self._gather[0] != (q, k):
+            dev = queries.device
+            self._gather = ((q, k), torch.zeros(blk, dtype=torch.uint8, device=dev),
+                            torch.empty(self.world * blk, dtype=torch.uint8, device=dev),
+                            torch.empty((q, k), dtype=torch.float32, device=dev))
+        _, mine, allb, sc32 = self._gather
+        ids, sc64 = packed_views(mine, q, k)
+        self.local.search_device(queries, k, out=(ids, sc32, sc64))
+        self.dist.all_gather_into_tensor(allb, mine, group=self.group)
+        self._last = (queries, k, (ids, sc32, sc64))
+        return merge_topk_packed_device(allb, self.world, q, k)
+
+    def check(self, repair: bool = True):
+        """Blocks until this rank's searches have finished.  -> (certificate failures, unresolved) summed over ranks since the
+        previous check.  Unresolved queries (a fallback list overflowed -- rare) hold uncertified rows: with ``repair`` the
+        ranks that have some re-answer exactly those with the dense fp64 scan, and the LAST search is exchanged and merged
+        again; the repaired result is returned as a third element."""
+        import torch
+
+        fails, unres = self.local.sync_status()
+        if self.world == 1:
+            if unres and repair and self._last is not None and self._last[2] is None:
+                raise RuntimeError("unresolved queries on an unsharded search: call ServiceIndex.repair_device with the outputs")
+            return fails, unres, None
+        t = torch.tensor([fails, unres], dtype=torch.int64, device=torch.device("cuda", self.device))
+        self.dist.all_reduce(t, group=self.group)
+        tot_f, tot_u = (int(x) for x in t.tolist())
+        fixed = None
+        if tot_u and repair and self._last is not None:
+            from .index import merge_topk_packed_device
+
+            queries, k, out = self._last
+            if unres:
+                self.local.repair_device(queries, k, out)
+            (_q, _k), mine, allb, _ = self._gather
+            self.dist.all_gather_into_tensor(allb, mine, group=self.group)
+            fixed = merge_topk_packed_device(allb, self.world, queries.shape[0], k)
+            torch.cuda.synchronize()
+        return tot_f, tot_u, fixed
+
+    def search(self, queries, k: int):
+        """search_device + check: finished, certified results."""
+        out = self.search_device(queries, k)
+        _, unres, fixed = self.check()
+        return fixed if fixed is not None else out
 
     def sync_status(self):
         return self.local.sync_status()

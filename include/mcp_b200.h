@@ -109,9 +109,10 @@ int mcp_index_set_penalty_device(mcp_index *idx, const float *penalty_device, vo
  * out_ids [n_queries*k], out_scores [n_queries*k] fp32 (the fp64 score rounded once);
  * out_scores64 may be NULL.  The host variant copies in/out and returns finished results.
  * The device variant only enqueues work on `stream`; queries that fail the exactness
- * certificate are re-answered on the device by the fp64 scan inside the same call, up to an
- * internal per-batch limit -- mcp_index_sync_status reports whether any were left over (the
- * host variant handles those itself).                                                        */
+ * certificate are re-answered on the device by the fp64 scan inside the same call, however
+ * many there are.  mcp_index_sync_status reports the rare leftovers (n_unresolved: queries
+ * whose fallback list overflowed); mcp_index_repair_device re-answers those (the host variant
+ * does all of this itself).                                                                  */
 int mcp_index_search(mcp_index *idx, const float *queries_host, int n_queries, int k,
                      int32_t *out_ids, float *out_scores, double *out_scores64);
 int mcp_index_search_device(mcp_index *idx, const float *queries_device, int n_queries, int k,
@@ -119,10 +120,19 @@ int mcp_index_search_device(mcp_index *idx, const float *queries_device, int n_q
                             double *out_scores64_device, void *stream);
 /* blocks until every search_device issued on this index has finished and reports the totals since
  * the previous sync_status; n_* may be NULL.  n_unresolved > 0 means that many queries still hold
- * uncertified results: re-run them with option "path" = MCP_PATH_EXACT_FP64.  Consecutive
+ * uncertified results: call mcp_index_repair_device.  Consecutive
  * search_device calls on the same stream queue behind one another without host waits; a call on
  * a different stream waits for the previous one first (they share the index's workspace).     */
 int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_failures, int32_t *n_unresolved);
+
+/* After mcp_index_sync_status reported n_unresolved > 0 for ONE search_device call: the same arguments again.  Exactly the
+ * unresolved queries (their fallback list overflowed: thousands of rows within the coarse error band of the k-th score) are
+ * re-answered in place by the dense fp64 scan; every other row of the outputs is left alone.  Blocks until done.  (The host
+ * variant mcp_index_search does this itself.)  With several search_device calls between two sync_status calls the list of
+ * unresolved queries mixes them: sync after each call whose answers you mean to repair.                                  */
+int mcp_index_repair_device(mcp_index *idx, const float *queries_device, int n_queries, int k,
+                            int32_t *out_ids_device, float *out_scores_device,
+                            double *out_scores64_device, void *stream);
 
 /* validation aid: the coarse score (distance + penalty, fp32) of every (query,row) pair as one coarse
  * kernel computes it, out [n_queries * n_rows]; path = MCP_PATH_STREAM_FP32 or MCP_PATH_GEMM_TF32.
@@ -152,7 +162,7 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
                                           double *out_scores64_device, void *stream);
 
 /* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
- * query before exact rescoring, >= k), "max_fallback" (device-side fp64 re-scans per batch),
+ * query before exact rescoring, >= k), "max_fallback" (queries one pass of the fp64 scan serves at a time, 1 .. 8; default 8),
  * "shadow" (default 1: load / adopt also build an fp16 image of the table (each row scaled by a power of two), +50 % device memory, which the batched scan
  * reads instead of the fp32 rows; the answer stays exact -- candidates are rescored in fp64 from the fp32 rows and certified
  * with a bound computed from the actual rounding residuals.  0 = no shadow, the batched scan reads the fp32 rows as tf32.
@@ -182,6 +192,15 @@ int64_t mcp_index_rows(const mcp_index *idx);
 int mcp_merge_topk_device(const double *scores64_device, const int32_t *ids_device, int n_shards,
                           int n_queries, int k, int32_t *out_ids_device, float *out_scores_device,
                           double *out_scores64_device, void *stream);
+
+/* The same merge over ONE gathered buffer: shard s contributes a block of mcp_merge_packed_block_bytes(n_queries, k)
+ * bytes laid out [n_queries*k fp64 scores][n_queries*k int32 ids][pad to 16], blocks back to back -- what one
+ * ncclAllGather of each rank's block leaves behind (a search_device call can write its outputs straight into the
+ * rank's block).  One collective per search instead of two.                                                   */
+int64_t mcp_merge_packed_block_bytes(int n_queries, int k);
+int mcp_merge_topk_packed_device(const void *packed_device, int n_shards, int n_queries, int k,
+                                 int32_t *out_ids_device, float *out_scores_device,
+                                 double *out_scores64_device, void *stream);
 
 /* ---- DAG level scheduling --------------------------------------------------------------------
  * Batched replacement for the ordering step of Orchestrator.execute (control_plane.py:104,

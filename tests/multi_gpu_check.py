@@ -1,6 +1,7 @@
-"""Multi-GPU parity check, run under torchrun on a real box (not collected by pytest):
+"""Multi-GPU parity check, run under torchrun on a real box (tests/test_gpu_scale.py launches it when the box has two or
+more GPUs; by hand:
 
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 tests/multi_gpu_check.py
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 tests/multi_gpu_check.py)
 
 Every rank builds its row shard of one seeded table, answers the same queries through ShardedIndex
 (local exact top-k -> NCCL all-gather -> K5 merge); rank 0 also answers them on the whole table with
@@ -36,10 +37,10 @@ def main():
     sh = sharded.ShardedIndex(d, "cosine", local)
     sh.adopt_shard(full[lo:hi], n).set_penalty(pen[lo:hi].contiguous())
     ok = True
-    for path in ("auto", "stream_fp32"):
+    for path in ("auto", "gemm_tf32", "stream_fp32"):
         sh.local.set_option("path", path)
         ids, s32, s64 = sh.search_device(qs, k)
-        assert sh.sync_status()[1] == 0
+        assert sh.check()[1] == 0
         one = pkg.ServiceIndex(d, "cosine", local).adopt(full)
         one.set_penalty(pen)
         wi, w32, w64 = one.search_device(qs, k)

@@ -35,6 +35,13 @@ def _worker(rank, world, port, ret):
         mi, ms = sharded.merge_gathered_cpu(g_sc.numpy(), g_id.numpy())
         gi, gs, _ = oracle.topk(c["rows"], c["queries"], c["k"], 0, c["penalty"], threads=1)
         ok = np.array_equal(mi, gi) and np.array_equal(ms, gs)
+        # the packed exchange the GPU path uses: one all-gather of [scores | ids] blocks
+        blk = torch.from_numpy(sharded.pack_block_cpu(s64, ids))
+        allb = torch.empty(world * blk.numel(), dtype=torch.uint8)
+        dist.all_gather_into_tensor(allb, blk)
+        p_sc, p_id = sharded.unpack_blocks_cpu(allb.numpy(), world, 7, 24)
+        pi, ps = sharded.merge_gathered_cpu(p_sc, p_id)
+        ok = ok and np.array_equal(pi, gi) and np.array_equal(ps, gs) and blk.numel() == sharded.block_bytes(7, 24)
         t = torch.tensor([int(ok)])
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         if rank == 0:

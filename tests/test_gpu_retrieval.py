@@ -363,7 +363,7 @@ def test_query_chunking_paths_agree(mcp, oracle):
     rows = torch.randn((n, d), generator=g, device=dev)
     qs = torch.randn((q, d), generator=g, device=dev)
     idx = mcp.ServiceIndex(d).adopt(rows)
-    idx.set_option("path", "exact_fp64").set_option("max_fallback", 16)
+    idx.set_option("path", "exact_fp64")
     want_i, _, want_s = (t.clone() for t in idx.search_device(qs, k))
     idx.sync_status()
     for path in ("gemm_tf32", "gemm_f16", "stream_fp32"):
