@@ -40,6 +40,7 @@ _vp, _i32, _i64 = C.c_void_p, C.c_int, C.c_int64
 # name -> (restype, argtypes); every symbol include/mcp_b200.h declares
 SIGNATURES = {
     "mcp_index_create": (_i32, [C.POINTER(_vp), _i32, _i32, _i32]),
+    "mcp_index_create_multi": (_i32, [C.POINTER(_vp), C.POINTER(C.c_int), _i32, _i32, _i32]),
     "mcp_index_destroy": (_i32, [_vp]),
     "mcp_index_load": (_i32, [_vp, _vp, _i64, _i64]),
     "mcp_index_adopt_device": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp]),

@@ -50,7 +50,8 @@ SERVICES_PREFIX = "mcp:service:"
 RETRIEVAL_METRIC = os.getenv("MCP_RETRIEVAL_METRIC", "cosine")
 RETRIEVAL_TOP_K = int(os.getenv("MCP_RETRIEVAL_TOP_K", "8"))
 EMBED_DIM = int(os.getenv("MCP_EMBED_DIM", "1536"))
-CUDA_DEVICE = int(os.getenv("MCP_CUDA_DEVICE", "0"))
+_dev = os.getenv("MCP_CUDA_DEVICE", "0")
+CUDA_DEVICE = [int(d) for d in _dev.split(",")] if "," in _dev else int(_dev)   # "0,1,2,3": the registry row-sharded over four GPUs
 
 
 # ---- registry (control_plane.py:26-35) --------------------------------------------------------
@@ -185,8 +186,10 @@ class GraphPlanner:
                  fetch_embeddings: Optional[Callable[[], Sequence]] = None,
                  embed: Optional[Callable[[str], np.ndarray]] = None,
                  llm: Optional[Callable[[str], str]] = None,
-                 top_k: int = RETRIEVAL_TOP_K, metric: str = RETRIEVAL_METRIC, device: int = CUDA_DEVICE,
+                 top_k: int = RETRIEVAL_TOP_K, metric: str = RETRIEVAL_METRIC, device=CUDA_DEVICE,
                  telemetry_client=None, micro_batch: bool = False):
+        """``device``: a GPU ordinal, or a list of them -- the registry is then row-sharded over those GPUs behind the same
+        ``plan`` / ``retrieve`` calls (``mcp_index_create_multi``)."""
         self.registry = registry
         self.pg_dsn = pg_dsn
         self.conn = None                       # opened lazily; the reference connects in __init__ (:48)
@@ -223,9 +226,12 @@ class GraphPlanner:
         table = np.stack([np.asarray(r[1], np.float32) for r in rows]) if rows else np.zeros((0, EMBED_DIM), np.float32)
         with self._lock:
             if self._index is None or self._index.dim != table.shape[1]:
-                if self._index is not None:
-                    self._index.close()
+                # a replaced index is not closed here: a search on another thread may still be inside it.  Searches hold their
+                # own reference (retrieve_batch); the handle is destroyed when the last of them lets go (ServiceIndex.__del__)
                 self._index = ServiceIndex(table.shape[1], self.metric, self.device)
+                if self._batcher is not None:
+                    self._batcher.close()                     # drains what is queued against the old index, then stops
+                    self._batcher = None
             self._index.load(table)
             self._names = names
             if services is None:
@@ -249,17 +255,21 @@ class GraphPlanner:
         k = min(k or self.top_k, max(1, len(self._names)))
         with self._lock:
             if self._batcher is None:
-                self._batcher = MicroBatcher(lambda q, kk: self._index.search(q, kk))
-        ids, scores = self._batcher.search(self._embed(intent), k)
-        return [(self._names[i], float(s)) for i, s in zip(ids, scores) if i >= 0]
+                index = self._index
+                self._batcher = MicroBatcher(lambda q, kk: index.search(q, kk))
+            batcher, names = self._batcher, self._names
+        ids, scores = batcher.search(self._embed(intent), k)
+        return [(names[i], float(s)) for i, s in zip(ids, scores) if i >= 0]
 
     def retrieve_batch(self, intents: Sequence[str], k: Optional[int] = None) -> List[List[tuple]]:
         if self._index is None:
             self.refresh_index()
-        k = min(k or self.top_k, max(1, len(self._names)))
+        with self._lock:
+            index, names = self._index, self._names            # own references: a concurrent refresh may swap both
+        k = min(k or self.top_k, max(1, len(names)))
         q = np.stack([np.asarray(self._embed(t), np.float32) for t in intents])
-        ids, scores, _ = self._index.search(q, k)
-        return [[(self._names[i], float(s)) for i, s in zip(row_i, row_s) if i >= 0]
+        ids, scores, _ = index.search(q, k)
+        return [[(names[i], float(s)) for i, s in zip(row_i, row_s) if i >= 0]
                 for row_i, row_s in zip(ids, scores)]
 
     # ---- plan (same contract as control_plane.py:57-75) -----------------------------------
@@ -298,7 +308,7 @@ class Orchestrator:
 
             client = httpx.AsyncClient()
         self.client = client
-        self.device = device
+        self.device = device[0] if isinstance(device, (list, tuple)) else device   # level scheduling needs one GPU
         logging.basicConfig(level=logging.INFO)
         self.logger = logging.getLogger("orchestrator")
 

@@ -16,8 +16,12 @@
 #include <string.h>
 
 #include <algorithm>
+#include <condition_variable>
+#include <functional>
+#include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/mcp_b200.h"
@@ -124,7 +128,9 @@ static int require_local(const void *p, size_t bytes, int device, const char *wh
     return MCP_OK;
 }
 
+struct mcp_multi;
 struct mcp_index {
+    mcp_multi *multi = nullptr;   // set on a handle made by mcp_index_create_multi: the table is row-sharded over sub-indexes
     int device = 0, dim = 0, metric = 0, n_sm = 148;
     int64_t n_rows = 0, ld = 0, id_base = 0;
     const float *d_rows = nullptr;
@@ -134,6 +140,8 @@ struct mcp_index {
     int64_t ldh = 0;
     bool has_shadow = false;
     int opt_shadow = 1;
+    int kp_boost = 0, clean_looks = 0;   // automatic oversampling: k' = base << kp_boost (note_outcome)
+    int64_t q_since_look = 0;
     bool has_penalty = false;
     TableConsts h_consts{};
     // options
@@ -157,6 +165,18 @@ struct mcp_index {
     std::mutex mu;
     mcp_stats stats{};
 };
+
+// multi-device handles (multi.cuh, included at the end of this file)
+static int multi_destroy(mcp_index *idx);
+static int multi_load(mcp_index *idx, const float *rows_host, int64_t n_rows, int64_t id_base);
+static int multi_set_penalty(mcp_index *idx, const float *penalty_host);
+static int multi_update_rows(mcp_index *idx, int64_t first_row, const float *rows_host, int64_t n_rows);
+static int multi_set_option(mcp_index *idx, const char *name, int64_t value);
+static int multi_get_stats(mcp_index *idx, mcp_stats *out);
+static int multi_search(mcp_index *idx, const float *queries_host, int nq, int k, int32_t *out_ids, float *out_scores, double *out_scores64);
+#define NOT_ON_MULTI(idx, what)                                                                                                  \
+    do { if ((idx)->multi) return fail(MCP_ESTATE, what " is not available on a multi-device handle (device pointers belong to one GPU): " \
+                                       "use the host-buffer entry points, or one index per GPU"); } while (0)
 
 #define SCORE_BUDGET_BYTES (512ull << 20)
 #define XS_SMEM_LIMIT (220u * 1024u)      // dynamic shared memory exact_scan2_kernel may ask for
@@ -197,6 +217,7 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
 
 extern "C" int mcp_index_destroy(mcp_index *idx) {
     if (!idx) return MCP_OK;
+    if (idx->multi) return multi_destroy(idx);
     cudaSetDevice(idx->device);
     cudaDeviceSynchronize();
     Buf *bufs[] = {&idx->own_rows, &idx->norm2, &idx->inv_norm, &idx->penalty, &idx->consts, &idx->q_copy,
@@ -255,6 +276,7 @@ static int prepare_table(mcp_index *idx, cudaStream_t st) {
 
 extern "C" int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_rows, int64_t id_base) {
     if (check_idx(idx)) return MCP_EINVAL;
+    if (idx->multi) return multi_load(idx, rows_host, n_rows, id_base);
     if (!rows_host || n_rows < 1) return fail(MCP_EINVAL, "rows NULL or n_rows < 1");
     if (n_rows >= (1ll << 31) || id_base < 0 || id_base + n_rows > (1ll << 31)) return fail(MCP_EINVAL, "ids must fit int32");
     std::lock_guard<std::mutex> lk(idx->mu);
@@ -274,6 +296,7 @@ extern "C" int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_
 extern "C" int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, int64_t n_rows, int64_t ld,
                                       int64_t id_base, void *stream) {
     if (check_idx(idx)) return MCP_EINVAL;
+    NOT_ON_MULTI(idx, "adopt_device");
     if (!rows_device || n_rows < 1) return fail(MCP_EINVAL, "rows NULL or n_rows < 1");
     if (ld < idx->dim || (ld & 3) || (idx->dim & 3)) return fail(MCP_EINVAL, "adopt needs dim %% 4 == 0 and ld %% 4 == 0, ld >= dim");
     if (((uintptr_t)rows_device) & 15) return fail(MCP_EINVAL, "rows must be 16-byte aligned");
@@ -291,6 +314,7 @@ extern "C" int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, 
 // Registry refresh without a reload: rows [first_row, first_row + n_rows) changed.
 extern "C" int mcp_index_update_rows(mcp_index *idx, int64_t first_row, const float *rows_host, int64_t n_rows) {
     if (check_idx(idx)) return MCP_EINVAL;
+    if (idx->multi) return multi_update_rows(idx, first_row, rows_host, n_rows);
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!idx->n_rows) return fail(MCP_ESTATE, "update_rows before load");
     if (first_row < 0 || n_rows < 1 || first_row + n_rows > idx->n_rows) return fail(MCP_EINVAL, "row range [%lld, %lld) outside the table", (long long)first_row, (long long)(first_row + n_rows));
@@ -351,6 +375,7 @@ static int clear_penalty(mcp_index *idx, cudaStream_t st) {
 
 extern "C" int mcp_index_set_penalty(mcp_index *idx, const float *penalty_host) {
     if (check_idx(idx)) return MCP_EINVAL;
+    if (idx->multi) return multi_set_penalty(idx, penalty_host);
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!idx->n_rows) return fail(MCP_ESTATE, "set_penalty before load");
     CU(cudaSetDevice(idx->device));
@@ -365,6 +390,7 @@ extern "C" int mcp_index_set_penalty(mcp_index *idx, const float *penalty_host) 
 
 extern "C" int mcp_index_set_penalty_device(mcp_index *idx, const float *penalty_device, void *stream) {
     if (check_idx(idx)) return MCP_EINVAL;
+    NOT_ON_MULTI(idx, "set_penalty_device");
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!idx->n_rows) return fail(MCP_ESTATE, "set_penalty before load");
     CU(cudaSetDevice(idx->device));
@@ -382,6 +408,7 @@ extern "C" int mcp_index_set_penalty_device(mcp_index *idx, const float *penalty
 extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t value) {
     if (check_idx(idx)) return MCP_EINVAL;
     if (!name) return fail(MCP_EINVAL, "option name is NULL");
+    if (idx->multi) return multi_set_option(idx, name, value);
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!strcmp(name, "path")) {
         if (value < MCP_PATH_AUTO || value > MCP_PATH_GEMM_F16) return fail(MCP_EINVAL, "path %lld", (long long)value);
@@ -423,6 +450,7 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
 extern "C" int mcp_index_get_stats(mcp_index *idx, mcp_stats *out) {
     if (check_idx(idx)) return MCP_EINVAL;
     if (!out) return fail(MCP_EINVAL, "out is NULL");
+    if (idx->multi) return multi_get_stats(idx, out);
     std::lock_guard<std::mutex> lk(idx->mu);
     *out = idx->stats;
     return MCP_OK;
@@ -550,17 +578,32 @@ static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64
 }
 
 static int choose_kprime(const mcp_index *idx, int k) {
-    int kp = idx->opt_kprime ? std::max(idx->opt_kprime, k) : std::max(2 * k, k + 32);
+    int kp = idx->opt_kprime ? std::max(idx->opt_kprime, k) : std::max(2 * k, k + 32) << idx->kp_boost;
     kp = (kp + 31) & ~31;
     return std::min(kp, FINAL_MAX);
+}
+
+// Automatic oversampling follows the data: when more than 1 in 200 queries since the last look needed the fp64 scan (tight
+// clusters, near-duplicates: the gap between rank k and rank k' is inside the coarse error band), the next searches keep twice
+// as many candidates (up to 4x, within the kernels' limits) -- rescoring 2k' rows costs microseconds, a full scan a table
+// read.  64 clean looks in a row step it back down.  Exactness never depends on this; only how often the fallback runs does.
+static void note_outcome(mcp_index *idx, int failures) {
+    const int64_t queries = idx->q_since_look;
+    idx->q_since_look = 0;
+    if (queries <= 0) return;
+    if ((int64_t)failures * 200 > queries) { if (idx->kp_boost < 2) idx->kp_boost++; idx->clean_looks = 0; }
+    else if (failures == 0 && idx->kp_boost > 0 && ++idx->clean_looks >= 64) { idx->kp_boost--; idx->clean_looks = 0; }
 }
 
 static int choose_path(const mcp_index *idx, int nq) {
     if (idx->h_consts.odd_rows) return MCP_PATH_EXACT_FP64;   // rows the fp32 coarse pass cannot bound
     if (idx->opt_path == MCP_PATH_GEMM_F16 && !idx->has_shadow) return MCP_PATH_GEMM_TF32;   // no shadow: the fp32 rows themselves
     if (idx->opt_path != MCP_PATH_AUTO) return idx->opt_path;
+    // With a shadow the fp16 scan reads half the bytes, which wins at every batch size once the table is large enough for the
+    // scan (not the launches) to be the cost: 1 query over 1 M rows 0.64 ms against 0.90 ms for the fp32 streaming kernel.
+    if (idx->has_shadow && (nq >= 8 || idx->n_rows >= 8192)) return MCP_PATH_GEMM_F16;
     if (nq < 8) return MCP_PATH_STREAM_FP32;
-    return idx->has_shadow ? MCP_PATH_GEMM_F16 : MCP_PATH_GEMM_TF32;
+    return MCP_PATH_GEMM_TF32;
 }
 static bool is_gemm_path(int path) { return path == MCP_PATH_GEMM_TF32 || path == MCP_PATH_GEMM_F16; }
 
@@ -667,6 +710,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     }
 
     idx->stats.searches++; idx->stats.queries += nq; idx->stats.last_path = path; idx->stats.last_kprime = kprime;
+    if (path != MCP_PATH_EXACT_FP64) idx->q_since_look += nq;
 
     if (path == MCP_PATH_EXACT_FP64) {
         const int slots = 256;                     // flag list entries per round (the scan takes them scan_slots() at a time)
@@ -826,6 +870,7 @@ extern "C" int mcp_index_search_device(mcp_index *idx, const float *queries_devi
                                        int32_t *out_ids_device, float *out_scores_device,
                                        double *out_scores64_device, void *stream) {
     if (check_idx(idx)) return MCP_EINVAL;
+    NOT_ON_MULTI(idx, "search_device");
     std::lock_guard<std::mutex> lk(idx->mu);
     int rc = validate_search(idx, queries_device, n_queries, k, out_ids_device, out_scores_device);
     if (rc) return rc;
@@ -843,6 +888,11 @@ extern "C" int mcp_index_search_device(mcp_index *idx, const float *queries_devi
 
 extern "C" int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_failures, int32_t *n_unresolved) {
     if (check_idx(idx)) return MCP_EINVAL;
+    if (idx->multi) {                                  // host-buffer searches only: nothing is ever pending
+        if (n_certificate_failures) *n_certificate_failures = 0;
+        if (n_unresolved) *n_unresolved = 0;
+        return MCP_OK;
+    }
     std::lock_guard<std::mutex> lk(idx->mu);
     CU(cudaSetDevice(idx->device));
     int fails = 0, unresolved = 0;
@@ -853,6 +903,7 @@ extern "C" int mcp_index_sync_status(mcp_index *idx, int32_t *n_certificate_fail
         idx->h_status[0] = idx->h_status[1] = 0;      // the device rewrites them from its own (now cleared) counters
         idx->stats.certificate_failures += fails;
         idx->stats.exact_scans += fails - unresolved;
+        note_outcome(idx, fails);
         CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), idx->last_stream));
         CU(cudaStreamSynchronize(idx->last_stream));
     }
@@ -867,6 +918,7 @@ extern "C" int mcp_index_repair_device(mcp_index *idx, const float *queries_devi
                                        int32_t *out_ids_device, float *out_scores_device, double *out_scores64_device,
                                        void *stream) {
     if (check_idx(idx)) return MCP_EINVAL;
+    NOT_ON_MULTI(idx, "repair_device");
     std::lock_guard<std::mutex> lk(idx->mu);
     int rc = validate_search(idx, queries_device, n_queries, k, out_ids_device, out_scores_device);
     if (rc) return rc;
@@ -884,6 +936,7 @@ extern "C" int mcp_index_repair_device(mcp_index *idx, const float *queries_devi
 extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n_queries, int k, int32_t *out_ids,
                                 float *out_scores, double *out_scores64) {
     if (check_idx(idx)) return MCP_EINVAL;
+    if (idx->multi) return multi_search(idx, queries_host, n_queries, k, out_ids, out_scores, out_scores64);
     std::unique_lock<std::mutex> lk(idx->mu);
     int rc = validate_search(idx, queries_host, n_queries, k, out_ids, out_scores);
     if (rc) return rc;
@@ -894,6 +947,7 @@ extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n
         idx->pending = false;
         idx->stats.certificate_failures += idx->h_status[0];
         idx->stats.exact_scans += idx->h_status[0] - idx->h_status[1];
+        note_outcome(idx, idx->h_status[0]);
         CU(cudaMemsetAsync(idx->flags.as<int>() + 1, 0, 2 * sizeof(int), st));
     }
     idx->h_status[0] = idx->h_status[1] = 0;      // device counters are zero here (cleared after every host-buffer search)
@@ -925,6 +979,7 @@ extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n
     idx->h_status[0] = idx->h_status[1] = 0;
     idx->stats.certificate_failures += hs[0];
     idx->stats.exact_scans += hs[0] - hs[1];
+    note_outcome(idx, hs[0]);
     if (hs[1] > 0) {
         // Queries whose fallback list overflowed (thousands of rows inside the coarse error band of the k-th score): exactly
         // those are re-answered by the dense fp64 scan, each into its own rows of the result; nothing else is recomputed.
@@ -944,6 +999,7 @@ extern "C" int mcp_index_search(mcp_index *idx, const float *queries_host, int n
 extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const float *queries_device, int n_queries,
                                               float *out_scores_device, void *stream) {
     if (check_idx(idx)) return MCP_EINVAL;
+    NOT_ON_MULTI(idx, "coarse_scores_device");
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!idx->n_rows) return fail(MCP_ESTATE, "coarse_scores before load");
     if (!queries_device || !out_scores_device || n_queries < 1 || n_queries > G_MAX_QBLOCKS * G_BM) return fail(MCP_EINVAL, "bad arguments");
@@ -1155,6 +1211,7 @@ extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float
                                                      int32_t *out_ids_device, float *out_scores_device,
                                                      double *out_scores64_device, void *stream) {
     if (check_idx(idx)) return MCP_EINVAL;
+    NOT_ON_MULTI(idx, "search_exact_noalloc_device");
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!idx->n_rows) return fail(MCP_ESTATE, "search before load");
     if (!queries_device || !out_ids_device || !out_scores_device) return fail(MCP_EINVAL, "NULL buffer");
@@ -1198,3 +1255,5 @@ extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float
     }
     return MCP_OK;
 }
+
+#include "multi.cuh"

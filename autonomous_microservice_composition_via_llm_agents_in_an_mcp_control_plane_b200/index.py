@@ -35,12 +35,23 @@ def _stream_ptr() -> C.c_void_p:
 
 
 class ServiceIndex:
-    def __init__(self, dim: int, metric="cosine", device: int = 0):
+    def __init__(self, dim: int, metric="cosine", device=0):
+        """``device``: one GPU ordinal, or a list of them -- then the table is row-sharded over those GPUs behind this one
+        handle (``mcp_index_create_multi``): ``load`` / ``set_penalty`` / ``update_rows`` / ``search`` work as usual, the
+        device-pointer calls (``adopt``, ``search_device`` ...) do not."""
         self._lib = nat.lib()
         self._h = C.c_void_p()
-        self.dim, self.device = int(dim), int(device)
+        self.dim = int(dim)
         self.metric = _METRICS[metric]
-        nat.check(self._lib.mcp_index_create(C.byref(self._h), self.device, self.dim, self.metric))
+        if isinstance(device, (list, tuple)):
+            self.devices = [int(d) for d in device]
+            self.device = self.devices[0]
+            arr = (C.c_int * len(self.devices))(*self.devices)
+            nat.check(self._lib.mcp_index_create_multi(C.byref(self._h), arr, len(self.devices), self.dim, self.metric))
+        else:
+            self.devices = [int(device)]
+            self.device = int(device)
+            nat.check(self._lib.mcp_index_create(C.byref(self._h), self.device, self.dim, self.metric))
         self._keep = []  # adopted tensors must outlive the handle
 
     # ---- lifetime -----------------------------------------------------------------------

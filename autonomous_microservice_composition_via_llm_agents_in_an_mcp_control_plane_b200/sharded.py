@@ -83,6 +83,7 @@ class ShardedIndex:
         self.local = ServiceIndex(dim, metric, self.device)
         self._gather = None
         self._last = None
+        self._host = None
 
     def adopt_shard(self, rows, n_total: int):
         lo, hi = shard_bounds(n_total, self.world, self.rank)
@@ -146,6 +147,30 @@ class ShardedIndex:
             fixed = merge_topk_packed_device(allb, self.world, queries.shape[0], k)
             torch.cuda.synchronize()
         return tot_f, tot_u, fixed
+
+    def search_host(self, q_host, k: int):
+        """Pinned host queries in, pinned host results out, every copy inside: H2D, local search, one all-gather, merge, D2H,
+        then ``check`` (a stream synchronisation and a two-word all-reduce of the status).  -> (ids, scores32, scores64) pinned
+        CPU tensors, finished and certified, identical on every rank."""
+        import torch
+
+        q, dim = q_host.shape
+        dev = torch.device("cuda", self.device)
+        if self._host is None or self._host[0] != (q, k):
+            self._host = ((q, k), torch.empty((q, dim), dtype=torch.float32, device=dev),
+                          tuple(torch.empty((q, k), dtype=dt, pin_memory=True) for dt in (torch.int32, torch.float32, torch.float64)))
+        _, qd, outs = self._host
+        qd.copy_(q_host, non_blocking=True)
+        res = self.search_device(qd, k)
+        for o, r in zip(outs, res):
+            o.copy_(r, non_blocking=True)
+        _, unres, fixed = self.check()
+        if fixed is not None:
+            for o, r in zip(outs, fixed):
+                o.copy_(r)
+        else:
+            torch.cuda.current_stream().synchronize()
+        return outs
 
     def search(self, queries, k: int):
         """search_device + check: finished, certified results."""

@@ -1,15 +1,18 @@
 #!/usr/bin/env python
 """bench.py -- top-k retrieval queries/sec on B200 (BASELINE.json metric), one process per GPU.
 
-  python bench.py --gpus 1 --steps K --warmup W            config 2: 100K x 1536, 256 queries, top-32 cosine + telemetry
-  torchrun ... bench.py --gpus N --steps K --warmup W      config 3: 10M x 1536 row-sharded over N GPUs, 1024 queries,
-                                                           top-64, NCCL all-gather merge (strong scaling: the table is fixed)
+  python bench.py --gpus 1 --steps K --warmup W            config 3 on ONE GPU: 10M x 1536 fp32 (61.4 GB + 30.7 GB fp16 shadow),
+                                                           1024 queries per step, top-64 cosine + telemetry
+  torchrun ... bench.py --gpus N --steps K --warmup W      the same table row-sharded over N GPUs, one NCCL all-gather + merge
+                                                           per step (strong scaling: table and batch are fixed at every N)
   python bench.py --impl reference ...                     the CPU path (numpy restatement of the pgvector exact scan,
                                                            BASELINE.md section 3) on the host cores, same config
 
-A "step" is one batch of queries answered over the whole table through the C ABI.  `value` is timed with
-CUDA events with everything resident in HBM; `e2e` is the same metric through the host-buffer API with the
-H2D / D2H copies inside the timed region.  One JSON line on stdout (rank 0).
+A "step" is one batch of 1024 queries answered over the whole table.  `value` is timed with CUDA events with everything
+resident in HBM; `e2e` is the same metric with pinned HOST buffers in and out through the public API, copies and the
+certification check inside the timed region.  One JSON line on stdout (rank 0).  At N = 1 the line also carries, under
+`extra`, the other BASELINE.json configs (2: 100K x 256 with its own roofline block; 4: 1M plan DAGs beside NetworkX on the
+host cores; 5: single-intent latency over 1M services), a batch sweep and a clustered-registry run.
 """
 from __future__ import annotations
 
@@ -36,6 +39,8 @@ CONFIGS = {
 }
 METRIC_NAME = "top-k retrieval queries/sec"
 UNIT = "queries/s"
+PATH_KERNEL = {1: "scan_fp32_kernel", 2: "gemm_tf32_kernel (kind::tf32)", 3: "exact_scan2_kernel", 4: "gemm_tf32_kernel (kind::f16 over the fp16 shadow)"}
+MIN_WARM_S = 0.7          # steps run before the timed region until the part has been under load this long (clocks settle)
 
 
 def peaks():
@@ -101,7 +106,7 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------
 def measure_tf32_peak(torch, dev):
     """cuBLAS TF32 8192^3 on this GPU, this run: (burst TFLOP/s = best of 5, sustained = 1 s loop).
-    MEASURED_PEAKS.json only records bf16; north_star asks for the tensor-pipe fraction of a TF32 kernel."""
+    MEASURED_PEAKS.json only records bf16; this is the denominator for the tf32 scan (option shadow = 0)."""
     old = torch.backends.cuda.matmul.allow_tf32
     torch.backends.cuda.matmul.allow_tf32 = True
     try:
@@ -159,12 +164,31 @@ def make_queries(torch, dev, q, dim, seed):
     return (x / x.norm(dim=1, keepdim=True)).contiguous()
 
 
+def make_clustered(torch, dev, n, dim, seed, n_centres=2000):
+    """A registry that is not isotropic noise: 2000 unit centres, members = centre + sigma * noise / sqrt(dim) with
+    sigma ~ U(0.02, 0.1) per cluster, 1 % of the rows exact or last-bit copies of other rows (tests/test_gpu_scale.py)."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    c = torch.randn((n_centres, dim), generator=g, device=dev)
+    c /= c.norm(dim=1, keepdim=True)
+    which = torch.randint(0, n_centres, (n,), generator=g, device=dev)
+    sigma = (torch.rand(n_centres, generator=g, device=dev) * 0.08 + 0.02)[which, None]
+    rows = c[which] + sigma * torch.randn((n, dim), generator=g, device=dev) / dim ** 0.5
+    nd = max(2, n // 100)
+    src = torch.randint(0, n, (nd,), generator=g, device=dev)
+    dst = torch.randint(0, n, (nd,), generator=g, device=dev)
+    rows[dst[: nd // 2]] = rows[src[: nd // 2]]
+    rows[dst[nd // 2:]] = rows[src[nd // 2:]] * (1.0 + torch.randn((nd - nd // 2, dim), generator=g, device=dev) * 1e-6)
+    q = c[torch.randint(0, n_centres, (256,), generator=g, device=dev)] + 0.01 * torch.randn((256, dim), generator=g, device=dev)
+    return rows.contiguous(), q.contiguous()
+
+
 # ---------------------------------------------------------------------------------------------
 # the CPU arm (numpy restatement; pgvector / Postgres do not exist on either machine)
 # ---------------------------------------------------------------------------------------------
 def cpu_arm(cfg, steps, warmup, sample_rows=None, rows=None, queries=None, penalty=None):
-    """-> dict(value=q/s, ms_per_step, cores, sample).  Times `steps` batches on a bounded row sample and scales
-    linearly in rows to the config's table (the scan is linear in N)."""
+    """-> dict(value=q/s, ms_per_step, cores, sample, steps).  Times `steps` batches on a bounded row sample and scales
+    linearly in rows to the config's table (the scan is linear in N).  The sample is walked in blocks of 64K rows, the
+    running top-k carried along, so the score matrix stays cache- and RAM-friendly at 1024 queries."""
     import numpy as np
 
     import oracle
@@ -184,28 +208,45 @@ def cpu_arm(cfg, steps, warmup, sample_rows=None, rows=None, queries=None, penal
     mid = 0 if cfg["metric"] == "cosine" else 1
     n2 = np.einsum("ij,ij->i", rows, rows).astype(np.float32) if mid else None
     for _ in range(warmup):
-        oracle.numpy_topk_baseline(rows, inv, queries, k, mid, penalty, n2)
+        oracle.numpy_topk_blocked(rows, inv, queries, k, mid, penalty, n2)
     t0 = time.perf_counter()
     for _ in range(steps):
-        oracle.numpy_topk_baseline(rows, inv, queries, k, mid, penalty, n2)
+        oracle.numpy_topk_blocked(rows, inv, queries, k, mid, penalty, n2)
     dt = (time.perf_counter() - t0) / steps
     scale = n / m
-    return dict(value=q / (dt * scale), ms_per_step=dt * scale * 1e3, cores=oracle.cpu_oracle.cpu_count(),
-                sample=(f"{steps} batches of {q} queries over {m} of {n} rows" + (f", time scaled x{scale:g} (scan is linear in rows)" if m < n else "")
-                        + "; numpy/OpenBLAS sgemm + argpartition, all host threads"))
+    return dict(value=q / (dt * scale), ms_per_step=dt * scale * 1e3, cores=oracle.cpu_oracle.cpu_count(), steps=steps,
+                sample=(f"{steps} batches of {q} queries over {m} of {n} rows" + (f", time scaled x{scale:g} (the scan is linear in rows)" if m < n else "")
+                        + "; numpy/OpenBLAS sgemm + argpartition in 64K-row blocks, all host threads"))
+
+
+def one_thread_cpu(cfg, sample_rows):
+    """The same arm with OPENBLAS_NUM_THREADS=1 (a pgvector sequential scan is one core per query), in a subprocess because
+    the BLAS thread count is fixed at import.  -> queries/s scaled to the config's table, or None."""
+    code = ("import sys, json; sys.path.insert(0, %r); import bench; "
+            "r = bench.cpu_arm(bench.CONFIGS[%r] | %r, 1, 1, sample_rows=%d); print(json.dumps(r))" % (str(ROOT), cfg["_name"], cfg.get("_over", {}), sample_rows))
+    env = dict(os.environ, OPENBLAS_NUM_THREADS="1", OMP_NUM_THREADS="1", MKL_NUM_THREADS="1")
+    try:
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=240, env=env)
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+        return {"value": d["value"], "unit": UNIT, "cores": 1, "sample": d["sample"].replace("all host threads", "OPENBLAS_NUM_THREADS=1")}
+    except Exception as ex:  # noqa: BLE001
+        return {"error": str(ex)[:200]}
 
 
 def run_reference(args, world, rank):
+    """The reference arm: rank 0 alone, the numpy restatement with every host thread on a bounded row sample of the SAME
+    config the GPU arm runs (250K of the 10M rows per step, scaled x40: a step then takes a few seconds and the K + W steps
+    the driver asks for end within minutes)."""
     if rank != 0:
         return
-    cfg = CONFIGS["config2" if (args.workload == "auto" and world == 1) or args.workload == "config2" else "config3"]
-    cfg = override(cfg, args)
-    sample = 100_000 if cfg["n"] > 100_000 else None
-    r = cpu_arm(cfg, max(1, min(args.steps, 5)), min(args.warmup, 1), sample_rows=sample)
+    name = "config3" if args.workload in ("auto", "config3") else "config2"
+    cfg = override(dict(CONFIGS[name], _name=name), args)
+    sample = min(cfg["n"], 250_000)
+    r = cpu_arm(cfg, max(1, args.steps), max(0, args.warmup), sample_rows=sample)
     line = {
-        "impl": "reference", "metric": METRIC_NAME, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "impl": "reference", "metric": METRIC_NAME, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": r["steps"],
         "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-        "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": cfg["label"], "rows": cfg["n"], "queries": cfg["q"], "k": cfg["k"], "dim": cfg["dim"]},
         "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -217,15 +258,151 @@ def run_reference(args, world, rank):
 
 def override(cfg, args):
     cfg = dict(cfg)
+    over = {}
     for key in ("n", "q", "k"):
         v = getattr(args, {"n": "rows", "q": "queries", "k": "topk"}[key])
         if v:
             cfg[key] = v
+            over[key] = v
             cfg["label"] += f" [{key}={v} override]"
     if getattr(args, "metric", None):
         cfg["metric"] = args.metric
+        over["metric"] = args.metric
         cfg["label"] = cfg["label"].replace("cosine", args.metric) + f" [metric={args.metric} override]"
+    cfg["_over"] = over
     return cfg
+
+
+# ---------------------------------------------------------------------------------------------
+# helpers of the GPU arm
+# ---------------------------------------------------------------------------------------------
+def alg_bytes_flops(n_loc, q, k, dim, path):
+    """bytes the coarse scan must move per batch, flops of the contraction.  The fp16 shadow scan reads
+    2 bytes per element (+ one more fp32 per row, its scale): the bytes actually read are what is reported."""
+    if path == 4:
+        ldh = (dim + 7) // 8 * 8
+        return n_loc * ldh * 2 + n_loc * 12 + q * ldh * 2 + q * k * 8, 2.0 * q * n_loc * dim
+    return n_loc * dim * 4 + n_loc * 8 + q * dim * 4 + q * k * 8, 2.0 * q * n_loc * dim
+
+
+def traffic_lookup(n_loc, q, path):
+    tp = ROOT / "profiles" / "traffic.json"
+    if not tp.exists():
+        return None
+    return json.loads(tp.read_text()).get(f"rows{n_loc}_q{q}_path{path}")
+
+
+def roofline_blocks(pk, n_loc, q, k, dim, path, kernel_ms, tf32=None):
+    """(primary, alternate) roofline blocks of the coarse kernel: whichever floor is higher for this launch is the bound."""
+    b, fl = alg_bytes_flops(n_loc, q, k, dim, path)
+    hbm_ach = b / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+    tf_ach = fl / (kernel_ms * 1e-3) / 1e12 if kernel_ms > 0 else 0.0
+    long_run = kernel_ms > 2.0          # a kernel timed inside a long, power-capped step is held against the sustained figure
+    if path == 4:
+        t_peak = pk["bf16_sus"] if long_run else pk["bf16"]
+        t_src = f"{pk['source']}: bf16 {'sustained' if long_run else 'burst'} (fp16 and bf16 MMAs run at the same rate)"
+    elif tf32:
+        t_peak = tf32[1] if long_run else tf32[0]
+        t_src = (f"cuBLAS TF32 8192^3 measured at the end of this run: burst {tf32[0]:.0f}, sustained {tf32[1]:.0f} TFLOP/s; half of the driver's bf16 "
+                 f"{'sustained' if long_run else 'burst'} figure would be {(pk['bf16_sus'] if long_run else pk['bf16']) / 2:.0f}")
+    else:
+        t_peak = (pk["bf16_sus"] if long_run else pk["bf16"]) / 2.0
+        t_src = "half of the measured bf16 figure (MEASURED_PEAKS.json holds no tf32 entry)"
+    traffic = traffic_lookup(n_loc, q, path)
+    kern = PATH_KERNEL.get(path)
+    hbm = {"bound": "hbm", "achieved": round(hbm_ach, 1), "peak": pk["hbm"], "unit": "GB/s", "frac": round(hbm_ach / pk["hbm"], 4),
+           "traffic": traffic, "kernel": kern, "kernel_ms": round(kernel_ms, 4), "algorithmic_bytes": b, "peak_source": pk["source"]}
+    ten = {"bound": "tensor", "achieved": round(tf_ach, 2), "peak": round(t_peak, 1), "unit": "TFLOP/s", "frac": round(tf_ach / t_peak, 4),
+           "traffic": traffic, "kernel": kern, "kernel_ms": round(kernel_ms, 4), "flops": fl, "peak_source": t_src}
+    use_tensor = path in (2, 4) and fl / (t_peak * 1e12) > b / (pk["hbm"] * 1e9)
+    return (ten, hbm) if use_tensor else (hbm, ten)
+
+
+def time_steps(torch, fn, steps):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def kernel_pass(torch, idx, fn, steps=5):
+    """Coarse-kernel time from a separate pass with the library's CUDA events on (kept out of the headline loop)."""
+    idx.set_option("time_coarse", 1)
+    idx.sync_status()
+    s0 = idx.stats()
+    for _ in range(steps):
+        fn()
+    torch.cuda.synchronize()
+    idx.sync_status()
+    s1 = idx.stats()
+    idx.set_option("time_coarse", 0)
+    return (s1["coarse_ms"] - s0["coarse_ms"]) / max(1, s1["coarse_timed"] - s0["coarse_timed"]), s1["last_path"], s1["last_kprime"]
+
+
+def dag_extra(torch, np, pkg, dev, n_dags):
+    """Config 4: K6 on n_dags synthetic plan DAGs with and without the topological_sort order, beside
+    nx.topological_generations on graphs built as control_plane.py:94-100 builds them (single core and all cores, on
+    subsets, scaled)."""
+    import oracle
+
+    out = {}
+    enc = pkg.dag.synthetic_dags(n_dags, seed=4004)
+    nn = torch.from_numpy(enc.n_nodes).to(dev)
+    off = torch.from_numpy(enc.edge_off.view(np.int32)).to(dev)
+    ed = torch.from_numpy(enc.edges).to(dev).contiguous()
+    byts = enc.n_nodes.size * (1 + 4 + 64 + 2) + enc.edges.size
+    for order in (True, False):
+        outb = pkg.dag.levels_device(nn, off, ed, with_order=order)
+        torch.cuda.synchronize()
+        ms = time_steps(torch, lambda: pkg.dag.levels_device(nn, off, ed, out=outb, with_order=order), 10)
+        b = byts + (enc.n_nodes.size * 64 if order else 0)
+        out["with_order" if order else "levels_only"] = {"ms": round(ms, 4), "dags_per_s": round(n_dags / ms * 1e3), "GBps": round(b / (ms * 1e-3) / 1e9, 1)}
+    out["dags"] = n_dags
+    # CPU: NetworkX, graph build included (the reference builds the DiGraph per request)
+    import multiprocessing as mp
+
+    sub1 = min(n_dags, 5_000)
+    graphs = [pkg.dag.to_graph_dict(enc, i) for i in range(sub1)]
+    t0 = time.perf_counter()
+    for gdict in graphs:
+        oracle.nx_levels(gdict)
+    dt1 = time.perf_counter() - t0
+    out["networkx_1_core"] = {"dags_per_s": round(sub1 / dt1, 1), "sample": f"{sub1} DAGs, graph build + topological_generations, scaled linearly",
+                              "ms_for_all": round(dt1 / sub1 * n_dags * 1e3, 1)}
+    cores = oracle.cpu_oracle.cpu_count()
+    subn = min(n_dags, 5_000 * cores)
+    try:
+        ctx = mp.get_context("fork")
+        chunks = [(i, min(i + 1250, subn)) for i in range(0, subn, 1250)]
+        t0 = time.perf_counter()
+        with ctx.Pool(cores, initializer=_nx_init, initargs=(enc,)) as pool:
+            pool.map(_nx_chunk, chunks)
+        dtn = time.perf_counter() - t0
+        out["networkx_all_cores"] = {"cores": cores, "dags_per_s": round(subn / dtn, 1), "sample": f"{subn} DAGs over a {cores}-process pool (pool start-up included)",
+                                     "ms_for_all": round(dtn / subn * n_dags * 1e3, 1)}
+    except Exception as ex:  # noqa: BLE001
+        out["networkx_all_cores"] = {"error": str(ex)[:200]}
+    return out
+
+
+_NX_ENC = None
+
+
+def _nx_init(enc):
+    global _NX_ENC
+    _NX_ENC = enc
+
+
+def _nx_chunk(lohi):
+    import oracle
+    import autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 as pkg
+
+    for i in range(*lohi):
+        oracle.nx_levels(pkg.dag.to_graph_dict(_NX_ENC, i))
+    return lohi[1] - lohi[0]
 
 
 # ---------------------------------------------------------------------------------------------
@@ -235,17 +412,16 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="auto", choices=["auto", "config2", "config3"])
+    ap.add_argument("--workload", default="auto", choices=["auto", "config2", "config3"], help="auto = config 3 at every N")
     ap.add_argument("--rows", type=int, default=0)
     ap.add_argument("--queries", type=int, default=0)
     ap.add_argument("--topk", type=int, default=0)
     ap.add_argument("--metric", choices=["cosine", "l2"], default=None, help="override the workload's distance (SURVEY 8d: config 3 is also run with L2)")
     ap.add_argument("--path", default="auto", choices=["auto", "stream_fp32", "gemm_tf32", "gemm_f16"])
-    ap.add_argument("--opt", action="append", default=[], help="library option name=value (repeatable), e.g. gemm_wide=0")
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value (repeatable), e.g. gemm_sync=2; shadow=0 is applied before the load")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
-    ap.add_argument("--dag", type=int, default=100_000, help="also time the Kahn-level kernel on this many synthetic DAGs (extra; 0 = skip)")
-    ap.add_argument("--no-config3-ref", action="store_true", help="skip the single-GPU run of the multi-GPU workload (extra)")
+    ap.add_argument("--dag", type=int, default=1_000_000, help="config 4: Kahn levels of this many synthetic DAGs (extra; 0 = skip)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -274,35 +450,56 @@ def main():
         os.dup2(2, 1)
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    wl = "config2" if (args.workload == "auto" and world == 1) or args.workload == "config2" else "config3"
-    cfg = override(CONFIGS[wl], args)
+    wl = "config2" if args.workload == "config2" else "config3"
+    cfg = override(dict(CONFIGS[wl], _name=wl), args)
     n, q, k, dim = cfg["n"], cfg["q"], cfg["k"], cfg["dim"]
     pk = peaks()
 
     lo, hi = sharded.shard_bounds(n, world, rank)
+    n_loc = hi - lo
     rows = make_shard(torch, dev, lo, hi, dim, cfg["seeds"][0] + 7919 * rank)
-    pen = make_penalty(torch, dev, hi - lo, cfg["seeds"][2] + 7919 * rank)
+    pen = make_penalty(torch, dev, n_loc, cfg["seeds"][2] + 7919 * rank)
     qs = make_queries(torch, dev, q, dim, cfg["seeds"][1])
     sh = sharded.ShardedIndex(dim, cfg["metric"], local)
+    late_opts = []
+    for o in args.opt:
+        name, val = o.split("=")
+        if name == "shadow":
+            sh.local.set_option(name, int(val))          # must precede the load
+        else:
+            late_opts.append((name, int(val)))
     sh.adopt_shard(rows, n).set_penalty(pen)
     if args.path != "auto":
         sh.local.set_option("path", args.path)
-    for o in args.opt:
-        name, val = o.split("=")
-        sh.local.set_option(name, int(val))
-    sh.local.set_option("time_coarse", 1)
+    for name, val in late_opts:
+        sh.local.set_option(name, val)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    def all_max(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     clocks = ClockSampler(local)
     clocks.__enter__()
+    # ---- warm-up: at least W steps, and on until the part has been under load for MIN_WARM_S (the same count on every rank)
+    t0 = time.monotonic()
     for _ in range(args.warmup):
         out = sh.search_device(qs, k)
     barrier()
-    sh.sync_status()
+    per = max(1e-4, (time.monotonic() - t0) / args.warmup)
+    more = int(all_max(max(0.0, MIN_WARM_S / per - args.warmup)))
+    for _ in range(more):
+        sh.search_device(qs, k)
+    barrier()
+    warm_run = args.warmup + more
+    sh.check()
     if saved_stdout is not None:
         t_ = torch.zeros(1, device=dev)
         dist.all_reduce(t_)                      # every kind of collective used later has run once by now
@@ -311,6 +508,7 @@ def main():
         os.dup2(saved_stdout, 1)
         os.close(saved_stdout)
     st0 = sh.local.stats()
+    # ---- the timed region: exactly K steps, device time, max over ranks
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     tw0 = time.monotonic()
@@ -320,18 +518,11 @@ def main():
     e1.record()
     barrier()
     tw1 = time.monotonic()
-    ms_total = e0.elapsed_time(e1)
-    fails, unresolved = sh.sync_status()
+    ms_step = all_max(e0.elapsed_time(e1)) / args.steps
     st1 = sh.local.stats()
-    t = torch.tensor([ms_total], device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = float(t.item()) / args.steps
+    fails, unresolved, _ = sh.check()
     clock_window = "timed region"
-    need = torch.tensor([1.0 if clocks.count(tw0, tw1) < 3 else 0.0], device=dev)
-    if world > 1:
-        dist.all_reduce(need, op=dist.ReduceOp.MAX)
-    if need.item() > 0:
+    if all_max(1.0 if clocks.count(tw0, tw1) < 3 else 0.0) > 0:
         # the timed region is shorter than a few nvidia-smi periods: keep the same step loop running (untimed, the same
         # number of steps on every rank) until the sampler has seen it under load, and report those samples
         n_probe = max(args.steps, min(20000, int(500.0 / ms_step) + 1))
@@ -340,40 +531,19 @@ def main():
             sh.search_device(qs, k)
         barrier()
         tw1 = time.monotonic()
-        sh.sync_status()
+        sh.check()
         clock_window = "the same step loop continued untimed for about 0.5 s (timed region shorter than the sampling period)"
     clocks.__exit__(None, None, None)
     clock_summary = clocks.summary(tw0, tw1, clock_window)
     value = q / (ms_step * 1e-3)
-
-    # ---- roofline of the dominant kernel (the coarse scan), timed by CUDA events inside the library on the launch stream
     launches = st1["kernel_launches"] - st0["kernel_launches"] + (args.steps if world > 1 else 0)   # + K5 merge per step
-    coarse_n = max(1, st1["coarse_timed"] - st0["coarse_timed"])
-    coarse_ms = (st1["coarse_ms"] - st0["coarse_ms"]) / coarse_n
-    n_loc = hi - lo
-    alg_bytes = n_loc * dim * 4 + n_loc * 8 + q * dim * 4 + q * k * 8
-    flops = 2.0 * q * n_loc * dim
-    path = st1["last_path"]
-    hbm_ach = alg_bytes / (coarse_ms * 1e-3) / 1e9 if coarse_ms > 0 else 0.0
-    tf_ach = flops / (coarse_ms * 1e-3) / 1e12 if coarse_ms > 0 else 0.0
-    # cuBLAS TF32 is measured at the very end of the run (it heats the part); until then use half of bf16
-    tf32_burst, tf32_sus = pk["bf16"] / 2.0, pk["bf16_sus"] / 2.0
-    tf32_peak = tf32_sus if coarse_ms > 2.0 else tf32_burst
-    traffic = None
-    tp = ROOT / "profiles" / "traffic.json"
-    if tp.exists():
-        traffic = json.loads(tp.read_text()).get(f"{wl}_path{path}")
-    hbm_roof = {"bound": "hbm", "achieved": round(hbm_ach, 1), "peak": pk["hbm"], "unit": "GB/s", "frac": round(hbm_ach / pk["hbm"], 4),
-                "traffic": traffic, "kernel": {1: "scan_fp32_kernel", 2: "gemm_tf32_kernel", 3: "exact_scan_kernel"}.get(path),
-                "kernel_ms": round(coarse_ms, 4), "algorithmic_bytes": alg_bytes, "peak_source": pk["source"]}
-    tensor_roof = {"bound": "tensor", "achieved": round(tf_ach, 2), "peak": round(tf32_peak, 1), "unit": "TFLOP/s",
-                   "frac": round(tf_ach / tf32_peak, 4), "traffic": traffic, "kernel": hbm_roof["kernel"], "kernel_ms": round(coarse_ms, 4),
-                   "flops": flops, "peak_source": "half of measured bf16"}
-    # the bound is whichever floor is higher for this launch (SURVEY.md section 7.2a ridge)
-    use_tensor = path == 2 and flops / (tf32_peak * 1e12) > alg_bytes / (pk["hbm"] * 1e9)
-    roofline, roofline_alt = (tensor_roof, hbm_roof) if use_tensor else (hbm_roof, tensor_roof)
 
-    # ---- e2e: host buffers through the public API, copies inside the timed region
+    # ---- roofline of the dominant kernel (the coarse scan): its own CUDA-event time, from a separate pass
+    coarse_ms, path, kprime = kernel_pass(torch, sh.local, lambda: sh.search_device(qs, k))
+    coarse_ms = all_max(coarse_ms)
+    roofline, roofline_alt = roofline_blocks(pk, n_loc, q, k, dim, path, coarse_ms)
+
+    # ---- e2e: pinned host buffers in and out through the public API, copies and the certification check inside
     q_host = torch.empty((q, dim), dtype=torch.float32, pin_memory=True)
     q_host.copy_(qs)
     e2e_steps = max(3, min(args.steps, 10))
@@ -387,135 +557,150 @@ def main():
         for _ in range(e2e_steps):
             ids_h, s_h, s64_h = sh.local.search(qn, k)
         e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
+        api = "ServiceIndex.search = mcp_index_search (host buffers; certified answers)"
     else:
-        outs_h = [torch.empty((q, k), dtype=dt, pin_memory=True) for dt in (torch.int32, torch.float32, torch.float64)]
-
-        def e2e_step():
-            qd = q_host.to(dev, non_blocking=True)
-            res = sh.search_device(qd, k)
-            for o, r in zip(outs_h, res):
-                o.copy_(r, non_blocking=True)
-            torch.cuda.synchronize()
-
         for _ in range(2):
-            e2e_step()
+            sh.search_host(q_host, k)
         barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
-            e2e_step()
+            sh.search_host(q_host, k)
         barrier()
-        e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
-        t = torch.tensor([e2e_ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t.item())
+        e2e_ms = all_max((time.perf_counter() - t0) / e2e_steps * 1e3)
+        api = "ShardedIndex.search_host: pinned host queries -> H2D -> local search -> one all-gather -> merge -> D2H -> status all-reduce"
     e2e = {"value": q / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-           "ms_per_step": round(e2e_ms, 4), "api": "ServiceIndex.search (mcp_index_search, host buffers)" if world == 1
-           else "pinned host -> ShardedIndex.search_device -> pinned host"}
+           "ms_per_step": round(e2e_ms, 4), "api": api}
 
-    extra = {"certificate_failures": fails, "unresolved": unresolved, "kprime": st1["last_kprime"], "path": path,
-             "roofline_alt": roofline_alt}
+    extra = {"certificate_failures": fails, "unresolved": unresolved, "kprime": kprime, "path": path, "warmup_steps_run": warm_run,
+             "roofline_alt": roofline_alt,
+             "north_star_hbm_target": {"fp32_table_GBps_aggregate": round(n * dim * 4 / (ms_step * 1e-3) / 1e9, 1),
+                                       "frac_of_aggregate_measured_hbm": round(n * dim * 4 / (ms_step * 1e-3) / 1e9 / (pk["hbm"] * world), 4),
+                                       "note": "the 10M-row fp32 table's bytes per whole step over N x measured HBM; at 1024 queries per batch the scan is tensor-bound "
+                                               "(3.93 TFLOP per GPU at N = 8 would need 2.7 PFLOP/s dense to meet 80 % of HBM; DESIGN.md section 4)"}}
     cpu_baseline = None
-    if rank == 0 and world == 1:
-        if not args.no_extras:
+    if rank == 0 and not args.no_cpu_baseline:
+        # the oracle's numpy port on this box's host cores, on a bounded slice of THIS rank's rows (same queries), scaled to the table
+        m = min(n_loc, 250_000)
+        cb = cpu_arm(cfg, 2, 1, sample_rows=m, rows=rows[:m].cpu().numpy(), queries=qs.cpu().numpy(), penalty=pen[:m].cpu().numpy())
+        cpu_baseline = {"value": cb["value"], "unit": UNIT, "cores": cb["cores"], "kind": "port", "sample": cb["sample"]}
+
+    if rank == 0 and world == 1 and not args.no_extras:
+        def guarded(name, fn):
+            try:
+                extra[name] = fn()
+            except Exception as ex:  # noqa: BLE001 -- an extra must never take the headline line down
+                extra[name] = {"error": f"{type(ex).__name__}: {str(ex)[:300]}"}
+
+        # ---- config 2 (BASELINE.json configs[1]) on the first 100K rows of the same table, with its own roofline block
+        def config2_block():
+            c2 = dict(CONFIGS["config2"], _name="config2", _over={})
+            n2, q2, k2 = min(c2["n"], n_loc), c2["q"], c2["k"]
+            idx = pkg.ServiceIndex(dim, c2["metric"], local).adopt(rows[:n2])
+            idx.set_penalty(pen[:n2].contiguous())
+            if args.path != "auto":
+                idx.set_option("path", args.path)
+            q2d = make_queries(torch, dev, q2, dim, c2["seeds"][1])
+            for _ in range(200):
+                idx.search_device(q2d, k2)
+            torch.cuda.synchronize()
+            ms = time_steps(torch, lambda: idx.search_device(q2d, k2), 500)
+            f2, u2 = idx.sync_status()
+            kms, p2, kp2 = kernel_pass(torch, idx, lambda: idx.search_device(q2d, k2), 50)
+            r_main, r_alt = roofline_blocks(pk, n2, q2, k2, dim, p2, kms)
+            qn2 = q2d.cpu().numpy()
+            for _ in range(3):
+                idx.search(qn2, k2)
+            t0 = time.perf_counter()
+            for _ in range(50):
+                idx.search(qn2, k2)
+            e_ms = (time.perf_counter() - t0) / 50 * 1e3
+            blk = {"workload": c2["label"], "ms_per_step": round(ms, 4), "queries_per_s": round(q2 / ms * 1e3, 1), "path": p2, "kprime": kp2,
+                   "certificate_failures": f2, "unresolved": u2, "roofline": r_main, "roofline_alt": r_alt,
+                   "whole_search_frac_of_hbm_floor": round((alg_bytes_flops(n2, q2, k2, dim, p2)[0] / (pk["hbm"] * 1e9)) / (ms * 1e-3), 4),
+                   "e2e": {"value": round(q2 / e_ms * 1e3, 1), "unit": UNIT, "ms_per_step": round(e_ms, 4), "h2d_bytes_per_step": q2 * dim * 4,
+                           "d2h_bytes_per_step": q2 * k2 * 16, "api": "mcp_index_search (host buffers)"}}
+            if not args.no_cpu_baseline:
+                cb2 = cpu_arm(c2, 3, 1, rows=rows[:n2].cpu().numpy(), queries=qn2, penalty=pen[:n2].cpu().numpy())
+                blk["cpu_baseline"] = {"value": cb2["value"], "unit": UNIT, "cores": cb2["cores"], "kind": "port", "sample": cb2["sample"]}
+                blk["cpu_baseline_1_thread"] = one_thread_cpu(c2, n2)
             sweep = {}
             for b in (1, 8, 64, 256, 1024):
                 qb = make_queries(torch, dev, b, dim, 99 + b)
-                for _ in range(3):
-                    sh.local.search_device(qb, k)
+                for _ in range(20):
+                    idx.search_device(qb, k2)
                 torch.cuda.synchronize()
-                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a0.record()
-                for _ in range(10):
-                    sh.local.search_device(qb, k)
-                a1.record()
-                torch.cuda.synchronize()
-                ms = a0.elapsed_time(a1) / 10
-                sweep[str(b)] = {"ms": round(ms, 4), "qps": round(b / ms * 1e3, 1),
-                                 "table_GBps": round(n * dim * 4 / (ms * 1e-3) / 1e9, 1)}
-            sh.sync_status()
-            extra["batch_sweep_whole_search"] = sweep
-        if args.dag:
-            enc = pkg.dag.synthetic_dags(args.dag, seed=4004)
-            nn = torch.from_numpy(enc.n_nodes).to(dev)
-            off = torch.from_numpy(enc.edge_off.view(np.int32)).to(dev)
-            ed = torch.from_numpy(enc.edges).to(dev).contiguous()
-            outb = pkg.dag.levels_device(nn, off, ed)
-            torch.cuda.synchronize()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record()
-            for _ in range(10):
-                pkg.dag.levels_device(nn, off, ed, out=outb)
-            a1.record()
-            torch.cuda.synchronize()
-            ms = a0.elapsed_time(a1) / 10
-            byts = enc.n_nodes.size * (1 + 4 + 128 + 2) + enc.edges.size
-            extra["dag_levels"] = {"dags": args.dag, "ms": round(ms, 4), "dags_per_s": round(args.dag / ms * 1e3),
-                                   "GBps": round(byts / (ms * 1e-3) / 1e9, 1), "with_order": True}
-        if wl == "config2" and not args.no_config3_ref and not args.no_extras and not (args.rows or args.queries or args.topk):
-            # the multi-GPU workload (config 3) on this one GPU, so that the N = 2, 4, 8 lines (strong scaling over a fixed
-            # 10M-row table) have an N = 1 point; the headline N = 1 line above is config 2 as BASELINE.json quotes it
-            try:
-                c3 = CONFIGS["config3"]
-                sh.close()
-                del rows, pen
-                torch.cuda.empty_cache()
-                rows3 = make_shard(torch, dev, 0, c3["n"], dim, c3["seeds"][0])
-                pen3 = make_penalty(torch, dev, c3["n"], c3["seeds"][2])
-                q3 = make_queries(torch, dev, c3["q"], dim, c3["seeds"][1])
-                sh = sharded.ShardedIndex(dim, c3["metric"], local)
-                sh.adopt_shard(rows3, c3["n"]).set_penalty(pen3)
-                for _ in range(2):
-                    sh.search_device(q3, c3["k"])
-                torch.cuda.synchronize()
-                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a0.record()
-                for _ in range(5):
-                    sh.search_device(q3, c3["k"])
-                a1.record()
-                torch.cuda.synchronize()
-                ms3 = a0.elapsed_time(a1) / 5
-                f3, u3 = sh.sync_status()
-                extra["config3_on_1_gpu"] = {"workload": c3["label"], "ms_per_step": round(ms3, 3), "queries_per_s": round(c3["q"] / ms3 * 1e3, 1),
-                                             "TFLOPs": round(2.0 * c3["q"] * c3["n"] * dim / (ms3 * 1e-3) / 1e12, 1),
-                                             "certificate_failures": f3, "unresolved": u3}
-                rows, pen, qs = rows3[:n], pen3[:n].contiguous(), make_queries(torch, dev, q, dim, cfg["seeds"][1])   # for the CPU baseline below
-            except Exception as ex:  # noqa: BLE001 -- an extra must never take the headline line down
-                extra["config3_on_1_gpu"] = {"error": str(ex)[:200]}
-        if not args.no_cpu_baseline:
-            import oracle
+                msb = time_steps(torch, lambda: idx.search_device(qb, k2), 100)
+                sweep[str(b)] = {"ms": round(msb, 4), "qps": round(b / msb * 1e3, 1), "path": idx.stats()["last_path"],
+                                 "fp32_table_GBps": round(n2 * dim * 4 / (msb * 1e-3) / 1e9, 1)}
+            idx.sync_status()
+            blk["batch_sweep_whole_search"] = sweep
+            idx.close()
+            return blk
 
-            rows_np, qs_np, pen_np = rows.cpu().numpy(), qs.cpu().numpy(), pen.cpu().numpy()
-            sample = 100_000 if n > 100_000 else None
-            cb = cpu_arm(cfg, 3, 1, sample_rows=sample, rows=rows_np, queries=qs_np, penalty=pen_np)
-            cpu_baseline = {"value": cb["value"], "unit": UNIT, "cores": cb["cores"], "kind": "port", "sample": cb["sample"]}
-            del rows_np
+        # ---- a registry that is not isotropic noise: clusters + duplicates (certificate failure rate, throughput kept)
+        def clustered_block():
+            rc, qc = make_clustered(torch, dev, 100_000, dim, 77)
+            idx = pkg.ServiceIndex(dim, "cosine", local).adopt(rc)
+            if args.path != "auto":
+                idx.set_option("path", args.path)
+            for _ in range(50):
+                idx.search_device(qc, 32)
+            idx.sync_status()
+            ms = time_steps(torch, lambda: idx.search_device(qc, 32), 200)
+            f, u = idx.sync_status()
+            ids = idx.search_device(qc, 32)[0].clone()
+            idx.set_option("path", "exact_fp64")
+            same = bool(torch.equal(ids, idx.search_device(qc, 32)[0]))
+            idx.sync_status()
+            idx.close()
+            return {"workload": "100K x 1536: 2000 clusters (sigma 0.02-0.1), 1 % exact / last-bit duplicates; 256 queries near centres, top-32",
+                    "ms_per_step": round(ms, 4), "queries_per_s": round(256 / ms * 1e3, 1), "certificate_failures_per_query": round(f / (200 * 256), 5),
+                    "unresolved": u, "ids_equal_fp64_scan": same}
+
+        # ---- config 5: single-intent latency over 1M services (first 1M rows of the same table)
+        def config5_block():
+            sys.path.insert(0, str(ROOT / "tools"))
+            import config5_e2e
+
+            n5 = min(1_000_000, n_loc)
+            return config5_e2e.run(pkg, rows[:n5], pen[:n5].contiguous(), requests=2000, clients=32, k=8, endpoint_requests=100)
+
+        guarded("config2", config2_block)
+        guarded("clustered_registry", clustered_block)
+        guarded("config5_single_intent_1M", config5_block)
+        if args.dag:
+            guarded("config4_dag_levels", lambda: dag_extra(torch, np, pkg, dev, args.dag))
+        if not args.no_cpu_baseline:
+            guarded("cpu_baseline_1_thread", lambda: one_thread_cpu(cfg, 50_000))
 
     if rank == 0:
-        # the tensor denominator, measured now that every timed region is over
-        tf32_burst, tf32_sus = measure_tf32_peak(torch, dev)
-        # a kernel timed inside a long, power-capped step is held against the sustained figure, a short one against the burst
-        tf32_peak = tf32_sus if coarse_ms > 2.0 else tf32_burst
-        for rf in (roofline, roofline_alt):
-            if rf["bound"] == "tensor":
-                rf["peak"] = round(tf32_peak, 1)
-                rf["frac"] = round(tf_ach / tf32_peak, 4)
-                rf["peak_source"] = (f"cuBLAS TF32 8192^3 measured at the end of this run: burst {tf32_burst:.0f}, sustained {tf32_sus:.0f} "
-                                     "TFLOP/s (MEASURED_PEAKS.json holds bf16 only)")
+        tf32 = None
+        if path == 2:
+            # the tf32 denominator, measured now that every timed region is over (it heats the part)
+            tf32 = measure_tf32_peak(torch, dev)
+            roofline, roofline_alt = roofline_blocks(pk, n_loc, q, k, dim, path, coarse_ms, tf32)
+            extra["roofline_alt"] = roofline_alt
+        dtype = {4: "f16 (fp16 shadow of the fp32 table on the tensor cores; candidates rescored in f64 from the fp32 rows, certified exact)",
+                 2: "tf32 (fp32 table read by kind::tf32 MMAs; candidates rescored in f64, certified exact)",
+                 1: "f32 (CUDA-core streaming scan; candidates rescored in f64, certified exact)", 3: "f64"}.get(path, "f32")
         line = {
             "metric": METRIC_NAME, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if wl == "config3" else "weak",
-            "vs_baseline": None, "dtype": "f32 table; tf32 tensor-core coarse pass + f64 exact rescoring" if path == 2 else "f32 coarse pass + f64 exact rescoring",
-            "data": "synthetic",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": dtype, "data": "synthetic",
             "config": {"workload": cfg["label"], "rows": n, "rows_per_gpu": n_loc, "queries": q, "k": k, "dim": dim,
-                       "parallelism": f"row-shard x{world}" + (" + NCCL all-gather merge" if world > 1 else ""),
-                       "l2": f"table shard {n_loc * dim * 4 / 1e6:.0f} MB > 126 MB L2, streamed once per step (no flush needed)"},
+                       "parallelism": f"row-shard x{world}" + (" + one NCCL all-gather + merge per step" if world > 1 else ""),
+                       "l2": f"table shard {n_loc * dim * (2 if path == 4 else 4) / 1e6:.0f} MB > 126 MB L2, streamed once per step (no flush needed)"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clock_summary, "extra": extra,
         }
+        if unresolved:
+            line["invalid"] = f"{unresolved} queries were left uncertified inside the timed region"
         print(json.dumps(line), flush=True)
     sh.close()
     if world > 1:
         dist.destroy_process_group()
+    if unresolved:
+        sys.exit(3)
 
 
 if __name__ == "__main__":

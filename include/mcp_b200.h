@@ -47,7 +47,8 @@ extern "C" {
 #define MCP_PATH_GEMM_TF32 2   /* K2: tcgen05 / TMEM TF32 distance GEMM                    */
 #define MCP_PATH_EXACT_FP64 3  /* full fp64 scan (the certificate's fallback, also a checker) */
 #define MCP_PATH_GEMM_F16 4    /* K2 over the fp16 shadow table: kind::f16 MMAs, half the bytes, twice the tensor rate.
-                                  AUTO takes it for batches of 8 and more whenever the index holds a shadow            */
+                                  AUTO takes it whenever the index holds a shadow (for fewer than 8 queries: from 8192 rows
+                                  on; below that the streaming kernel)                                                   */
 
 typedef struct mcp_index mcp_index;
 
@@ -72,6 +73,16 @@ typedef struct mcp_stats {
  * the handle is the "connection" to the embedding table, now resident in HBM.              */
 int mcp_index_create(mcp_index **out, int device_id, int dim, int metric);
 int mcp_index_destroy(mcp_index *idx);
+/* The same "connection" over a table too large (or too hot) for one GPU: the reference is ONE process whose planner makes
+ * plain method calls (control_plane.py:135-138, :57-75), so the sharding of SURVEY.md section 8e has to fit behind one
+ * handle.  The handle owns one single-device index per entry of device_ids (contiguous row ranges, global ids) and one
+ * worker thread per shard; mcp_index_load / _set_penalty / _update_rows split their host arrays by rows, mcp_index_search
+ * fans the queries out, every GPU answers them on its shard (certified exact, like a single-device index), the packed
+ * (score, id) lists are copied device-to-device to device_ids[0] and merged there with the same (score, id) key, so the
+ * answer is identical to the unsharded search.  Kernels only ever read their own GPU's memory.  Entry points that take
+ * device pointers (adopt, search_device, ...) belong to one GPU and return MCP_ESTATE on such a handle.  A device may be
+ * listed more than once (several shards on one GPU).                                                                   */
+int mcp_index_create_multi(mcp_index **out, const int *device_ids, int n_devices, int dim, int metric);
 
 /* ---- table load ----------------------------------------------------------------------------
  * Replaces GraphPlanner._fetch_embeddings_metadata (control_plane.py:51-55), the only read of
@@ -162,7 +173,8 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
                                           double *out_scores64_device, void *stream);
 
 /* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
- * query before exact rescoring, >= k), "max_fallback" (queries one pass of the fp64 scan serves at a time, 1 .. 8; default 8),
+ * query before exact rescoring, >= k; automatic starts at max(2k, k + 32) and doubles, up to 4x, while more than 1 in 200
+ * queries need the fp64 scan -- clustered registries -- and steps back after 64 clean status reads), "max_fallback" (queries one pass of the fp64 scan serves at a time, 1 .. 8; default 8),
  * "shadow" (default 1: load / adopt also build an fp16 image of the table (each row scaled by a power of two), +50 % device memory, which the batched scan
  * reads instead of the fp32 rows; the answer stays exact -- candidates are rescored in fp64 from the fp32 rows and certified
  * with a bound computed from the actual rounding residuals.  0 = no shadow, the batched scan reads the fp32 rows as tf32.

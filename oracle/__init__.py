@@ -14,6 +14,7 @@ from .cpu_oracle import (  # noqa: F401
     merge,
     nx_levels,
     numpy_topk_baseline,
+    numpy_topk_blocked,
     scores,
     telemetry_penalty,
     topk,

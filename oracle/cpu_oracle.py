@@ -246,5 +246,27 @@ def numpy_topk_baseline(rows, inv_norm_rows, queries, k, metric=COSINE, penalty=
     return ids, np.take_along_axis(ps, order, axis=1)
 
 
+def numpy_topk_blocked(rows, inv_norm_rows, queries, k, metric=COSINE, penalty=None, row_norm2=None, block=65536):
+    """``numpy_topk_baseline`` over row blocks of ``block`` rows, the running top-k carried from block to block (the
+    [Q, N] score matrix of a 1024-query batch over a million rows would not fit the caches, or comfortably in RAM).
+    Same arithmetic per element; the timed CPU arm of ``bench.py``."""
+    n = rows.shape[0]
+    if n <= block:
+        return numpy_topk_baseline(rows, inv_norm_rows, queries, k, metric, penalty, row_norm2)
+    best_i = best_s = None
+    for lo in range(0, n, block):
+        hi = min(n, lo + block)
+        ids, sc = numpy_topk_baseline(rows[lo:hi], inv_norm_rows[lo:hi], queries, k, metric,
+                                      None if penalty is None else penalty[lo:hi], None if row_norm2 is None else row_norm2[lo:hi])
+        ids = ids + np.int32(lo)
+        if best_i is None:
+            best_i, best_s = ids, sc
+        else:
+            ci, cs = np.concatenate([best_i, ids], axis=1), np.concatenate([best_s, sc], axis=1)
+            order = np.lexsort((ci, cs), axis=1)[:, :k]
+            best_i, best_s = np.take_along_axis(ci, order, axis=1), np.take_along_axis(cs, order, axis=1)
+    return best_i, best_s
+
+
 def cpu_count() -> int:
     return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)

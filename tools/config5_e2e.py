@@ -42,27 +42,15 @@ def pct(a, p):
     return float(np.percentile(np.asarray(a) * 1e3, p))
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--rows", type=int, default=1_000_000)
-    ap.add_argument("--requests", type=int, default=10_000)
-    ap.add_argument("--clients", type=int, default=32)
-    ap.add_argument("--k", type=int, default=8)
-    args = ap.parse_args()
-
+def run(pkg, rows, pen, requests=10_000, clients=32, k=8, endpoint_requests=300):
+    """rows / pen: CUDA tensors (the table is adopted in place).  -> dict of latencies (milliseconds)."""
     import httpx
-    import torch
     from fastapi.testclient import TestClient
 
-    import autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 as pkg
     from autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 import control_plane as cp
-    import bench
 
-    dev = torch.device("cuda:0")
-    n = args.rows
-    rows = bench.make_shard(torch, dev, 0, n, 1536, 1005)
-    pen = bench.make_penalty(torch, dev, n, 2005)
-    idx = pkg.ServiceIndex(1536, "cosine", 0).adopt(rows)
+    n = rows.shape[0]
+    idx = pkg.ServiceIndex(rows.shape[1], "cosine", rows.device.index or 0).adopt(rows)
     idx.set_penalty(pen)
     names = [f"svc{i:07d}" for i in range(n)]
     redis = LazyRedis(n, np.full(n, 0.005, np.float32))
@@ -73,12 +61,12 @@ def main():
         edges = [{"from": a, "to": b} for a, b in zip(svc, svc[1:])]
         return json.dumps({"nodes": nodes, "edges": edges})
 
-    planner = cp.GraphPlanner(cp.ServiceRegistry(client=redis), llm=llm, top_k=args.k)
+    planner = cp.GraphPlanner(cp.ServiceRegistry(client=redis), llm=llm, top_k=k)
     planner.attach_index(idx, names)
     orch = cp.Orchestrator(client=httpx.AsyncClient(transport=httpx.MockTransport(lambda r: httpx.Response(200, json={"ok": True}))))
     app = cp.create_app(registry=planner.registry, planner=planner, orch=orch)
 
-    intents = [f"intent number {i}: book, translate, summarise and notify" for i in range(args.requests)]
+    intents = [f"intent number {i}: book, translate, summarise and notify" for i in range(requests)]
     for t in intents[:50]:
         planner.retrieve(t)
     # (a) sequential retrieval calls
@@ -92,7 +80,7 @@ def main():
     lat_abi = []
     for i in range(q.shape[0]):
         t0 = time.perf_counter()
-        idx.search(q[i:i + 1], args.k)
+        idx.search(q[i:i + 1], k)
         lat_abi.append(time.perf_counter() - t0)
     # (b) concurrent clients (threads; the index serialises calls on its lock, the GIL is released inside)
     lat_c, lock = [], threading.Lock()
@@ -106,16 +94,16 @@ def main():
         with lock:
             lat_c.extend(loc)
 
-    per = max(1, len(intents) // args.clients)
-    threads = [threading.Thread(target=worker, args=(intents[i * per:(i + 1) * per],)) for i in range(args.clients)]
+    per = max(1, len(intents) // clients)
+    threads = [threading.Thread(target=worker, args=(intents[i * per:(i + 1) * per],)) for i in range(clients)]
     t0 = time.perf_counter()
     for th in threads:
         th.start()
     for th in threads:
         th.join()
     wall_c = time.perf_counter() - t0
-    # (b2) the same 32 clients through the micro-batcher: concurrent requests share launches
-    planner_mb = cp.GraphPlanner(cp.ServiceRegistry(client=redis), llm=llm, top_k=args.k, micro_batch=True)
+    # (b2) the same clients through the micro-batcher: concurrent requests share launches
+    planner_mb = cp.GraphPlanner(cp.ServiceRegistry(client=redis), llm=llm, top_k=k, micro_batch=True)
     planner_mb.attach_index(idx, names)
     lat_m = []
 
@@ -128,7 +116,7 @@ def main():
         with lock:
             lat_m.extend(loc)
 
-    threads = [threading.Thread(target=worker_mb, args=(intents[i * per:(i + 1) * per],)) for i in range(args.clients)]
+    threads = [threading.Thread(target=worker_mb, args=(intents[i * per:(i + 1) * per],)) for i in range(clients)]
     t0 = time.perf_counter()
     for th in threads:
         th.start()
@@ -137,33 +125,54 @@ def main():
     wall_m = time.perf_counter() - t0
     # (c) batched retrieval of the same intents (what request micro-batching would reach)
     t0 = time.perf_counter()
-    planner.retrieve_batch(intents[:1024], args.k)
+    planner.retrieve_batch(intents[:1024], k)
     batch_1024 = time.perf_counter() - t0
     # (d) the endpoint, end to end
     client = TestClient(app, raise_server_exceptions=True)
     lat_e = []
-    for t in intents[:300]:
+    for t in intents[:endpoint_requests]:
         t0 = time.perf_counter()
         r = client.post("/plan_and_execute", json={"intent": t})
         lat_e.append(time.perf_counter() - t0)
         assert r.status_code == 200 and len(r.json()["results"]) == 3
     out = {
-        "config": f"{n} services x 1536-d, top-{args.k} cosine + telemetry, single-intent requests",
+        "config": f"{n} services x {rows.shape[1]}-d, top-{k} cosine + telemetry, single-intent requests",
         "retrieve_sequential_ms": {"p50": pct(lat, 50), "p99": pct(lat, 99), "mean": float(np.mean(lat) * 1e3), "n": len(lat),
                                    "note": "GraphPlanner.retrieve: hash embedding (numpy) + mcp_index_search + name lookup"},
         "mcp_index_search_ms": {"p50": pct(lat_abi, 50), "p99": pct(lat_abi, 99), "n": len(lat_abi),
-                                "hbm_floor_ms": n * 6144 / 6541.5e9 * 1e3},
-        "retrieve_concurrent_ms": {"clients": args.clients, "p50": pct(lat_c, 50), "p99": pct(lat_c, 99),
+                                "hbm_floor_ms": n * rows.shape[1] * 4 / 6551.4e9 * 1e3, "path": idx.stats()["last_path"]},
+        "retrieve_concurrent_ms": {"clients": clients, "p50": pct(lat_c, 50), "p99": pct(lat_c, 99),
                                    "throughput_rps": len(lat_c) / wall_c},
-        "retrieve_concurrent_microbatched_ms": {"clients": args.clients, "p50": pct(lat_m, 50), "p99": pct(lat_m, 99),
+        "retrieve_concurrent_microbatched_ms": {"clients": clients, "p50": pct(lat_m, 50), "p99": pct(lat_m, 99),
                                                 "throughput_rps": len(lat_m) / wall_m, "launches": planner_mb._batcher.launches,
                                                 "requests": planner_mb._batcher.requests},
         "retrieve_batch_1024_ms": batch_1024 * 1e3,
         "plan_and_execute_ms": {"p50": pct(lat_e, 50), "p99": pct(lat_e, 99), "n": len(lat_e),
                                 "note": "FastAPI TestClient, stub LLM, 3 mocked services per plan"},
-        "stats": idx.stats(),
     }
-    print(json.dumps(out))
+    if planner_mb._batcher is not None:
+        planner_mb._batcher.close()
+    idx.close()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=1_000_000)
+    ap.add_argument("--requests", type=int, default=10_000)
+    ap.add_argument("--clients", type=int, default=32)
+    ap.add_argument("--k", type=int, default=8)
+    args = ap.parse_args()
+
+    import torch
+
+    import autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 as pkg
+    import bench
+
+    dev = torch.device("cuda:0")
+    rows = bench.make_shard(torch, dev, 0, args.rows, 1536, 1005)
+    pen = bench.make_penalty(torch, dev, args.rows, 2005)
+    print(json.dumps(run(pkg, rows, pen, args.requests, args.clients, args.k)))
 
 
 if __name__ == "__main__":
