@@ -17,6 +17,7 @@ METRIC_COSINE, METRIC_L2 = 0, 1
 PATH_AUTO, PATH_STREAM_FP32, PATH_GEMM_TF32, PATH_EXACT_FP64, PATH_GEMM_F16 = 0, 1, 2, 3, 4
 MAX_K = 256
 MAX_DAG_NODES = 64
+MAX_WIDE_DAG_NODES = 255
 NOALLOC_MAX_ROWS, NOALLOC_MAX_QUERIES = 1 << 20, 64
 
 
@@ -45,6 +46,7 @@ SIGNATURES = {
     "mcp_index_load": (_i32, [_vp, _vp, _i64, _i64]),
     "mcp_index_adopt_device": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp]),
     "mcp_index_update_rows": (_i32, [_vp, _i64, _vp, _i64]),
+    "mcp_index_upsert_rows": (_i32, [_vp, _vp, _vp, _i64]),
     "mcp_index_set_penalty": (_i32, [_vp, _vp]),
     "mcp_index_set_penalty_device": (_i32, [_vp, _vp, _vp]),
     "mcp_index_search": (_i32, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
@@ -61,6 +63,8 @@ SIGNATURES = {
     "mcp_merge_topk_packed_device": (_i32, [_vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp]),
     "mcp_dag_levels": (_i32, [_i32, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "mcp_dag_levels_device": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "mcp_dag_levels_wide": (_i32, [_i32, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
+    "mcp_dag_levels_wide_device": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "mcp_last_error": (C.c_char_p, []),
     "mcp_device_count": (_i32, []),
     "mcp_build_info": (C.c_char_p, []),

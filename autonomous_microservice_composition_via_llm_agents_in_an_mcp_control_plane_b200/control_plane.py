@@ -329,7 +329,8 @@ class Orchestrator:
             nodes.setdefault(edge["from"], {})
             nodes.setdefault(edge["to"], {})
             first_in_edge.setdefault(edge["to"], edge)
-        enc, res = self.schedule_batch([graph])
+        # the ordering step (:104) on the GPU, off the event loop: the call blocks its thread until the kernel's answer is back
+        enc, res = await asyncio.to_thread(self.schedule_batch, [graph])
         _, order, status = _dag.decode(enc, res, 0)
 
         results, errors = {}, {}

@@ -38,6 +38,12 @@ kahn_levels_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__
     const uchar2 *ed = reinterpret_cast<const uchar2 *>(edges);
     for (int64_t b = (int64_t)blockIdx.x * KAHN_WARPS + warp; b < n_dags; b += (int64_t)gridDim.x * KAHN_WARPS) {
         const int n = n_nodes[b];
+        if (n > 64) {                                    // not this kernel's DAG (kahn_levels_wide_kernel takes up to 255 nodes): say so
+            out_level[b * 64 + lane] = 0xFF; out_level[b * 64 + 32 + lane] = 0xFF;
+            if (WITH_ORDER) { out_order[b * 64 + lane] = 0xFF; out_order[b * 64 + 32 + lane] = 0xFF; }
+            if (lane == 0) { out_n_levels[b] = 0; out_status[b] = 2; }
+            continue;
+        }
         const uint32_t e0 = edge_off[b], e1 = edge_off[b + 1];
         w.pred[lane] = 0; w.pred[lane + 32] = 0;
         __syncwarp();
@@ -116,6 +122,118 @@ kahn_levels_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__
             out_order[b * 64 + lane] = w.order[lane];
             out_order[b * 64 + 32 + lane] = w.order[lane + 32];
             __syncwarp();
+        }
+    }
+}
+
+
+// ---- plans with 65 .. 255 nodes: one CTA per DAG, thread = node, 256-bit predecessor masks ----------------------------
+// Same rules as the warp kernel above (duplicate edges collapse, a self loop never becomes ready, generation order by
+// (position of the zeroing parent, index of the first edge parent -> node)); outputs have a pitch of 256 per DAG.  These
+// are single oversized plans on the /execute path, not the batched million-DAG case, so the kernel is written for
+// clarity: a block barrier per step, the edge list rescanned once per generation for the order.
+#define KAHNW_THREADS 256
+struct KahnWide {
+    u64 pred[256][4];
+    u64 done[4], fm[256][4];
+    u64 key[256];
+    uint32_t firste[256];
+    uint32_t piece[8];
+    unsigned char lvl[256], pos[256], ustar[256], order[256];
+    int any;
+};
+
+template <bool WITH_ORDER>
+__global__ void __launch_bounds__(KAHNW_THREADS)
+kahn_levels_wide_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__restrict__ edge_off,
+                        const unsigned char *__restrict__ edges, int64_t n_dags,
+                        unsigned char *__restrict__ out_level, unsigned char *__restrict__ out_order,
+                        unsigned char *__restrict__ out_n_levels, unsigned char *__restrict__ out_status) {
+    __shared__ KahnWide w;
+    const int v = threadIdx.x, lane = v & 31, warp = v >> 5;
+    const uchar2 *ed = reinterpret_cast<const uchar2 *>(edges);
+    for (int64_t b = blockIdx.x; b < n_dags; b += gridDim.x) {
+        const int n = n_nodes[b];
+        const uint32_t e0 = edge_off[b], e1 = edge_off[b + 1];
+        __syncthreads();                                  // the previous DAG has left shared memory
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w.pred[v][j] = 0;
+        if (v < 4) w.done[v] = 0;
+        w.lvl[v] = 0xFF; w.order[v] = 0xFF;
+        __syncthreads();
+        for (uint32_t e = e0 + v; e < e1; e += KAHNW_THREADS) {
+            const uchar2 uv = ed[e];
+            if (uv.x < n && uv.y < n) atomicOr(&w.pred[uv.y][uv.x >> 6], 1ull << (uv.x & 63));
+        }
+        __syncthreads();
+        u64 p[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) p[j] = w.pred[v][j];
+        int level = 0, n_done = 0;
+        unsigned char mylvl = 0xFF;
+        for (;;) {
+            const bool isdone = (w.done[v >> 6] >> (v & 63)) & 1ull;
+            const bool ready = v < n && !isdone && !((p[0] & ~w.done[0]) | (p[1] & ~w.done[1]) | (p[2] & ~w.done[2]) | (p[3] & ~w.done[3]));
+            const uint32_t bal = __ballot_sync(MCP_FULL, ready);
+            if (lane == 0) w.piece[warp] = bal;
+            __syncthreads();
+            uint32_t anyb = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) anyb |= w.piece[j];
+            if (anyb == 0) break;                         // block-uniform
+            if (ready) mylvl = (unsigned char)level;
+            __syncthreads();                              // everyone has read `done` and the pieces
+            if (v < 4) {
+                const u64 f = (u64)w.piece[2 * v] | ((u64)w.piece[2 * v + 1] << 32);
+                w.done[v] |= f;
+                if (WITH_ORDER) w.fm[level][v] = f;
+            }
+            for (int j = 0; j < 8; ++j) n_done += __popc(w.piece[j]);
+            ++level;
+            __syncthreads();
+        }
+        out_level[b * 256 + v] = mylvl;
+        if (v == 0) { out_n_levels[b] = (unsigned char)level; out_status[b] = (unsigned char)(n_done != n); }
+        if (WITH_ORDER) {
+            w.lvl[v] = mylvl;
+            __syncthreads();
+            int base = 0;
+            for (int L = 0; L < level; ++L) {
+                const bool in = mylvl == L;
+                u64 k = (u64)v;                           // generation 0: node order
+                if (L > 0) {
+                    int bp = -1, bu = 0;
+                    if (in) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            u64 c = p[j] & w.fm[L - 1][j];
+                            while (c) { const int u = j * 64 + __ffsll((long long)c) - 1; c &= c - 1; const int q = w.pos[u]; if (q > bp) { bp = q; bu = u; } }
+                        }
+                        w.ustar[v] = (unsigned char)bu; w.firste[v] = 0xFFFFFFFFu;
+                    }
+                    __syncthreads();
+                    for (uint32_t e = e0 + v; e < e1; e += KAHNW_THREADS) {
+                        const uchar2 uv = ed[e];
+                        if (uv.x < n && uv.y < n && w.lvl[uv.y] == L && w.ustar[uv.y] == uv.x) atomicMin(&w.firste[uv.y], e - e0);
+                    }
+                    __syncthreads();
+                    if (in) k = ((u64)bp << 32) | w.firste[v];
+                }
+                if (in) w.key[v] = k;
+                __syncthreads();
+                int rk = 0, cnt = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    u64 m = w.fm[L][j];
+                    cnt += __popcll(m);
+                    if (in) for (; m; m &= m - 1) rk += w.key[j * 64 + __ffsll((long long)m) - 1] < k;
+                }
+                __syncthreads();                          // keys read before pos (same bytes are not shared, but order[] below is)
+                if (in) { w.pos[v] = (unsigned char)(base + rk); w.order[base + rk] = (unsigned char)v; }
+                base += cnt;
+                __syncthreads();
+            }
+            out_order[b * 256 + v] = w.order[v];
         }
     }
 }

@@ -16,6 +16,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <cmath>
 #include <condition_variable>
 #include <functional>
 #include <memory>
@@ -159,6 +160,13 @@ struct mcp_index {
     cudaEvent_t done = nullptr;
     bool pending = false;
     cudaStream_t last_stream = nullptr;
+    // row upserts are enqueued on `stream`, after whatever search is in flight and ahead of the next one
+    unsigned char *h_up = nullptr;   // pinned staging: rows, then ids
+    size_t h_up_cap = 0;
+    Buf d_up;                        // the same on the device
+    cudaEvent_t up_copied = nullptr; // the staging buffer has been read (it may be refilled)
+    cudaEvent_t up_done = nullptr;   // the upsert kernel has run: searches on other streams wait for it on the device
+    bool up_pending = false;
     std::vector<cudaEvent_t> ev;   // pairs bracketing coarse scans when opt_time_coarse
     int ev_used = 0;
     GemmPlan gemm;
@@ -171,6 +179,7 @@ static int multi_destroy(mcp_index *idx);
 static int multi_load(mcp_index *idx, const float *rows_host, int64_t n_rows, int64_t id_base);
 static int multi_set_penalty(mcp_index *idx, const float *penalty_host);
 static int multi_update_rows(mcp_index *idx, int64_t first_row, const float *rows_host, int64_t n_rows);
+static int multi_upsert_rows(mcp_index *idx, const int64_t *row_ids, const float *rows_host, int64_t n_rows);
 static int multi_set_option(mcp_index *idx, const char *name, int64_t value);
 static int multi_get_stats(mcp_index *idx, mcp_stats *out);
 static int multi_search(mcp_index *idx, const float *queries_host, int nq, int k, int32_t *out_ids, float *out_scores, double *out_scores64);
@@ -178,6 +187,7 @@ static int multi_search(mcp_index *idx, const float *queries_host, int nq, int k
     do { if ((idx)->multi) return fail(MCP_ESTATE, what " is not available on a multi-device handle (device pointers belong to one GPU): " \
                                        "use the host-buffer entry points, or one index per GPU"); } while (0)
 
+#define NOALLOC_MAX_DEVICES_ 64
 #define SCORE_BUDGET_BYTES (512ull << 20)
 #define XS_SMEM_LIMIT (220u * 1024u)      // dynamic shared memory exact_scan2_kernel may ask for
 #define UNRES_MAX 4096
@@ -200,6 +210,8 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     if (prop.major != 10) { delete idx; return fail(MCP_ECUDA, "device %d is sm_%d%d; this library holds sm_100a code only", device_id, prop.major, prop.minor); }
     CU(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&idx->done, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&idx->up_copied, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&idx->up_done, cudaEventDisableTiming));
     CU(cudaHostAlloc(&idx->h_status, 4 * sizeof(int), cudaHostAllocMapped));
     idx->h_status[0] = idx->h_status[1] = 0;
     CU(cudaHostGetDevicePointer(&idx->h_status_dev, idx->h_status, 0));
@@ -228,6 +240,10 @@ extern "C" int mcp_index_destroy(mcp_index *idx) {
     for (cudaEvent_t e : idx->ev) cudaEventDestroy(e);
     if (idx->h_status) cudaFreeHost(idx->h_status);
     if (idx->h_stage) cudaFreeHost(idx->h_stage);
+    if (idx->h_up) cudaFreeHost(idx->h_up);
+    idx->d_up.release();
+    if (idx->up_copied) cudaEventDestroy(idx->up_copied);
+    if (idx->up_done) cudaEventDestroy(idx->up_done);
     if (idx->done) cudaEventDestroy(idx->done);
     if (idx->stream) cudaStreamDestroy(idx->stream);
     delete idx;
@@ -311,6 +327,8 @@ extern "C" int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, 
     return prepare_table(idx, (cudaStream_t)stream);
 }
 
+static int upsert_locked(mcp_index *idx, const int64_t *row_ids, int64_t first_row, const float *rows_host, int64_t n);
+
 // Registry refresh without a reload: rows [first_row, first_row + n_rows) changed.
 extern "C" int mcp_index_update_rows(mcp_index *idx, int64_t first_row, const float *rows_host, int64_t n_rows) {
     if (check_idx(idx)) return MCP_EINVAL;
@@ -318,6 +336,7 @@ extern "C" int mcp_index_update_rows(mcp_index *idx, int64_t first_row, const fl
     std::lock_guard<std::mutex> lk(idx->mu);
     if (!idx->n_rows) return fail(MCP_ESTATE, "update_rows before load");
     if (first_row < 0 || n_rows < 1 || first_row + n_rows > idx->n_rows) return fail(MCP_EINVAL, "row range [%lld, %lld) outside the table", (long long)first_row, (long long)(first_row + n_rows));
+    if (rows_host && idx->d_rows == idx->own_rows.as<float>()) return upsert_locked(idx, nullptr, first_row, rows_host, n_rows);   // stream-ordered, no host wait
     CU(cudaSetDevice(idx->device));
     if (idx->pending) { CU(cudaEventSynchronize(idx->done)); }      // searches in flight read the rows
     cudaStream_t st = idx->stream;
@@ -345,6 +364,63 @@ extern "C" int mcp_index_update_rows(mcp_index *idx, int64_t first_row, const fl
     CU(cudaStreamSynchronize(st));
     if (idx->h_consts.bad_rows) return fail(MCP_EINVAL, "%u updated rows hold NaN/Inf elements; the table now contains them -- update again", idx->h_consts.bad_rows);
     return MCP_OK;
+}
+
+// Registry ingest that does not stop queries.  Rows are checked on the host (non-finite values,
+// norms the coarse kernels cannot bound), staged in pinned memory and handed to ONE kernel on the index's own stream: copy into
+// the table, exact norms, shadow rows, residual maxima.  Nothing is read back, so the call returns as soon as the work is
+// enqueued; searches already in flight finish on the old rows, later ones see the new rows (a search on another stream is made
+// to wait on the device, not on the host).
+static int upsert_locked(mcp_index *idx, const int64_t *row_ids, int64_t first_row, const float *rows_host, int64_t n) {
+    if (!idx->n_rows) return fail(MCP_ESTATE, "upsert before load");
+    if (!rows_host || n < 1) return fail(MCP_EINVAL, "rows NULL or n < 1");
+    if (idx->d_rows != idx->own_rows.as<float>()) return fail(MCP_ESTATE, "the table is adopted device memory: change it in place and call mcp_index_update_rows with rows_host = NULL");
+    const int dim = idx->dim;
+    unsigned int odd = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        const int64_t r = row_ids ? row_ids[i] : first_row + i;
+        if (r < 0 || r >= idx->n_rows) return fail(MCP_EINVAL, "row %lld outside the table of %lld rows", (long long)r, (long long)idx->n_rows);
+        const float *v = rows_host + i * dim;
+        double n2 = 0.0;
+        for (int c = 0; c < dim; ++c) n2 += (double)v[c] * (double)v[c];
+        if (!std::isfinite(n2)) return fail(MCP_EINVAL, "row %lld holds NaN/Inf elements (pgvector rejects these at input); nothing was changed", (long long)i);
+        if (n2 != 0.0 && (n2 < 1e-30 || n2 > 1e30)) ++odd;
+    }
+    CU(cudaSetDevice(idx->device));
+    const size_t row_bytes = sizeof(float) * (size_t)n * dim, id_bytes = row_ids ? sizeof(int64_t) * (size_t)n : 0;
+    const size_t ids_off = (row_bytes + 15) & ~(size_t)15, total = ids_off + id_bytes;
+    if (total > idx->h_up_cap) {
+        if (idx->up_pending) CU(cudaEventSynchronize(idx->up_copied));
+        if (idx->h_up) cudaFreeHost(idx->h_up);
+        idx->h_up = nullptr; idx->h_up_cap = 0;
+        CU(cudaMallocHost(&idx->h_up, total * 2));
+        idx->h_up_cap = total * 2;
+    } else if (idx->up_pending) CU(cudaEventSynchronize(idx->up_copied));   // the previous upsert's copy has left the staging buffer
+    int rc = idx->d_up.ensure(total);
+    if (rc) return rc;
+    memcpy(idx->h_up, rows_host, row_bytes);
+    if (row_ids) memcpy(idx->h_up + ids_off, row_ids, id_bytes);
+    cudaStream_t st = idx->stream;
+    if (idx->pending && idx->last_stream != st) CU(cudaStreamWaitEvent(st, idx->done, 0));   // behind the search in flight, on the device
+    CU(cudaMemcpyAsync(idx->d_up.p, idx->h_up, total, cudaMemcpyHostToDevice, st));
+    CU(cudaEventRecord(idx->up_copied, st));
+    upsert_rows_kernel<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(idx->d_up.as<float>(), dim, row_ids ? reinterpret_cast<const int64_t *>(idx->d_up.as<unsigned char>() + ids_off) : nullptr,
+                                                               first_row, n, idx->own_rows.as<float>(), dim, idx->ld, idx->norm2.as<double>(), idx->inv_norm.as<float>(),
+                                                               idx->has_shadow ? idx->shadow.as<__half>() : nullptr, idx->ldh,
+                                                               idx->has_shadow ? idx->shadow_scale.as<float>() : nullptr, idx->consts.as<TableConsts>());
+    KCHECK();
+    CU(cudaEventRecord(idx->up_done, st));
+    idx->up_pending = true;
+    idx->h_consts.odd_rows += odd;                   // rows of extreme norm send every later search to the fp64 scan (choose_path)
+    return MCP_OK;
+}
+
+extern "C" int mcp_index_upsert_rows(mcp_index *idx, const int64_t *row_ids, const float *rows_host, int64_t n_rows) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    if (!row_ids) return fail(MCP_EINVAL, "row_ids is NULL");
+    if (idx->multi) return multi_upsert_rows(idx, row_ids, rows_host, n_rows);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    return upsert_locked(idx, row_ids, 0, rows_host, n_rows);
 }
 
 static int penalty_stats(mcp_index *idx, cudaStream_t st) {
@@ -493,6 +569,7 @@ static int coarse_event(mcp_index *idx, cudaStream_t st) {
 }
 // the workspace is shared by all searches of an index: same-stream calls queue, others wait
 static int order_after_previous(mcp_index *idx, cudaStream_t st) {
+    if (idx->up_pending && st != idx->stream) CU(cudaStreamWaitEvent(st, idx->up_done, 0));   // a row upsert ahead of this call: device-side wait
     if (idx->pending && idx->last_stream != st) CU(cudaEventSynchronize(idx->done));
     idx->last_stream = st;
     return MCP_OK;
@@ -735,16 +812,13 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     CertParams cp;
     cp.metric = idx->metric; cp.path = path; cp.complete = (n <= kprime);
     const double u = 5.9604644775390625e-08;   // 2^-24
-    cp.kind = 0; cp.rho_e = 0.0;
+    cp.kind = 0;
     if (path == MCP_PATH_STREAM_FP32) cp.rel = 2.0 * (dim / 32.0 + 32.0) * u;   // + the fp32 tree-summed query norm
     else {
         // operand rounding enters per query through rho_q and the table's rho_e (rescore.cuh); what is left is the fp32
         // accumulation inside the tensor core and the rounding of the two fp32 inverse norms (the query's is a tree sum)
         cp.rel = dim * 4.0 * u + 128.0 * u;
-        cp.kind = path == MCP_PATH_GEMM_F16 ? 2 : 1;
-        const unsigned int rb = path == MCP_PATH_GEMM_F16 ? idx->h_consts.rho_f16 : idx->h_consts.rho_tf32;
-        float rf; memcpy(&rf, &rb, sizeof rf);
-        cp.rho_e = (double)rf;
+        cp.kind = path == MCP_PATH_GEMM_F16 ? 2 : 1;     // the table's rho_e is read on the device (TableConsts)
     }
     cp.abs_pen = 8.0 * u;
     cp.debug = idx->gemm.debug >> 8;
@@ -1095,9 +1169,8 @@ extern "C" int mcp_merge_topk_packed_device(const void *packed_device, int n_sha
 // ---------------------------------------------------------------------------------------------
 // DAG levels
 // ---------------------------------------------------------------------------------------------
-extern "C" int mcp_dag_levels_device(const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
-                                     int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels,
-                                     uint8_t *out_status, void *stream) {
+static int dag_launch(int pitch, const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges, int64_t n_dags,
+                      uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels, uint8_t *out_status, cudaStream_t st) {
     if (!n_nodes || !edge_off || !out_level || !out_n_levels || !out_status) return fail(MCP_EINVAL, "NULL buffer");
     if (n_dags < 0) return fail(MCP_EINVAL, "n_dags < 0");
     if (n_dags == 0) return MCP_OK;
@@ -1105,54 +1178,120 @@ extern "C" int mcp_dag_levels_device(const uint8_t *n_nodes, const uint32_t *edg
     int dev = 0, n_sm = 148;
     CU(cudaGetDevice(&dev));
     CU(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-    int64_t want = (n_dags + KAHN_WARPS - 1) / KAHN_WARPS;
-    int grid = (int)std::min<int64_t>((int64_t)n_sm * 8, want);
-    if (out_order)
-        kahn_levels_kernel<true><<<grid, KAHN_THREADS, 0, (cudaStream_t)stream>>>(n_nodes, edge_off, edges, n_dags, out_level,
-                                                                                 out_order, out_n_levels, out_status);
-    else
-        kahn_levels_kernel<false><<<grid, KAHN_THREADS, 0, (cudaStream_t)stream>>>(n_nodes, edge_off, edges, n_dags, out_level,
-                                                                                  nullptr, out_n_levels, out_status);
+    if (pitch == 64) {
+        int64_t want = (n_dags + KAHN_WARPS - 1) / KAHN_WARPS;
+        int grid = (int)std::min<int64_t>((int64_t)n_sm * 8, want);
+        if (out_order)
+            kahn_levels_kernel<true><<<grid, KAHN_THREADS, 0, st>>>(n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
+        else
+            kahn_levels_kernel<false><<<grid, KAHN_THREADS, 0, st>>>(n_nodes, edge_off, edges, n_dags, out_level, nullptr, out_n_levels, out_status);
+    } else {
+        int grid = (int)std::min<int64_t>((int64_t)n_sm * 4, n_dags);
+        if (out_order)
+            kahn_levels_wide_kernel<true><<<grid, KAHNW_THREADS, 0, st>>>(n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
+        else
+            kahn_levels_wide_kernel<false><<<grid, KAHNW_THREADS, 0, st>>>(n_nodes, edge_off, edges, n_dags, out_level, nullptr, out_n_levels, out_status);
+    }
     KCHECK();
+    return MCP_OK;
+}
+
+extern "C" int mcp_dag_levels_device(const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
+                                     int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels,
+                                     uint8_t *out_status, void *stream) {
+    return dag_launch(64, n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status, (cudaStream_t)stream);
+}
+extern "C" int mcp_dag_levels_wide_device(const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
+                                          int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels,
+                                          uint8_t *out_status, void *stream) {
+    return dag_launch(256, n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status, (cudaStream_t)stream);
+}
+
+// The host variants keep one workspace per device: device buffers and a pinned staging buffer that only grow, and a
+// non-blocking stream of their own.  A call therefore allocates nothing once the workspace has seen its size (Orchestrator.execute
+// sends one small graph per request: cudaMalloc / cudaFree there would serialise against a retrieval scan running on another
+// stream) and never touches the legacy default stream.  Calls on one device take turns (the lock is held for the call).
+struct DagWorkspace {
+    std::mutex mu;
+    cudaStream_t st = nullptr;
+    Buf in, out;
+    unsigned char *h = nullptr;
+    size_t h_cap = 0;
+};
+static DagWorkspace g_dag_ws[NOALLOC_MAX_DEVICES_];
+#define DAG_PINNED_MAX (8u << 20)      // larger batches are copied straight from / to the caller's memory
+
+static int dag_levels_host(int pitch, int max_nodes, int device_id, const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
+                           int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels, uint8_t *out_status) {
+    if (!n_nodes || !edge_off || !out_level || !out_n_levels || !out_status) return fail(MCP_EINVAL, "NULL buffer");
+    if (n_dags < 0) return fail(MCP_EINVAL, "n_dags < 0");
+    if (n_dags == 0) return MCP_OK;
+    if (device_id < 0 || device_id >= NOALLOC_MAX_DEVICES_) return fail(MCP_EINVAL, "device %d out of range", device_id);
+    for (int64_t b = 0; b < n_dags; ++b) {
+        if (n_nodes[b] > max_nodes) return fail(MCP_EINVAL, "DAG %lld has %d nodes (max %d)", (long long)b, n_nodes[b], max_nodes);
+        if (edge_off[b + 1] < edge_off[b]) return fail(MCP_EINVAL, "edge_off not monotone at %lld", (long long)b);
+    }
+    const size_t n_edges = edge_off[n_dags];
+    if (n_edges && !edges) return fail(MCP_EINVAL, "edges is NULL");
+    CU(cudaSetDevice(device_id));
+    DagWorkspace &w = g_dag_ws[device_id];
+    std::lock_guard<std::mutex> lk(w.mu);
+    if (!w.st) CU(cudaStreamCreateWithFlags(&w.st, cudaStreamNonBlocking));
+    // device layout in: [edge_off | edges | n_nodes], out: [level | order | n_levels | status]
+    const size_t B = (size_t)n_dags, off_bytes = sizeof(uint32_t) * (B + 1), ed_bytes = (2 * n_edges + 3) & ~(size_t)3;
+    const size_t in_bytes = off_bytes + ed_bytes + B, lv_bytes = B * (size_t)pitch;
+    const size_t out_bytes = lv_bytes * (out_order ? 2 : 1) + 2 * B;
+    int rc;
+    if ((rc = w.in.ensure(in_bytes + 16))) return rc;
+    if ((rc = w.out.ensure(out_bytes + 16))) return rc;
+    unsigned char *di = w.in.as<unsigned char>(), *d_o = w.out.as<unsigned char>();
+    uint8_t *d_level = d_o, *d_order = out_order ? d_o + lv_bytes : nullptr, *d_nl = d_o + lv_bytes * (out_order ? 2 : 1), *d_st = d_nl + B;
+    const bool staged = in_bytes + out_bytes <= DAG_PINNED_MAX;
+    if (staged && in_bytes + out_bytes > w.h_cap) {
+        if (w.h) cudaFreeHost(w.h);
+        w.h = nullptr; w.h_cap = 0;
+        const size_t want = std::max<size_t>(in_bytes + out_bytes, 64u << 10) * 2;
+        CU(cudaMallocHost(&w.h, std::min<size_t>(want, DAG_PINNED_MAX)));
+        w.h_cap = std::min<size_t>(want, DAG_PINNED_MAX);
+    }
+    if (staged) {
+        memcpy(w.h, edge_off, off_bytes);
+        if (n_edges) memcpy(w.h + off_bytes, edges, 2 * n_edges);
+        memcpy(w.h + off_bytes + ed_bytes, n_nodes, B);
+        CU(cudaMemcpyAsync(di, w.h, in_bytes, cudaMemcpyHostToDevice, w.st));
+    } else {
+        CU(cudaMemcpyAsync(di, edge_off, off_bytes, cudaMemcpyHostToDevice, w.st));
+        if (n_edges) CU(cudaMemcpyAsync(di + off_bytes, edges, 2 * n_edges, cudaMemcpyHostToDevice, w.st));
+        CU(cudaMemcpyAsync(di + off_bytes + ed_bytes, n_nodes, B, cudaMemcpyHostToDevice, w.st));
+    }
+    if ((rc = dag_launch(pitch, di + off_bytes + ed_bytes, reinterpret_cast<const uint32_t *>(di), di + off_bytes, n_dags, d_level, d_order, d_nl, d_st, w.st))) return rc;
+    if (staged) {
+        unsigned char *ho = w.h + in_bytes;
+        CU(cudaMemcpyAsync(ho, d_o, out_bytes, cudaMemcpyDeviceToHost, w.st));
+        CU(cudaStreamSynchronize(w.st));
+        memcpy(out_level, ho, lv_bytes);
+        if (out_order) memcpy(out_order, ho + lv_bytes, lv_bytes);
+        memcpy(out_n_levels, ho + lv_bytes * (out_order ? 2 : 1), B);
+        memcpy(out_status, ho + lv_bytes * (out_order ? 2 : 1) + B, B);
+    } else {
+        CU(cudaMemcpyAsync(out_level, d_level, lv_bytes, cudaMemcpyDeviceToHost, w.st));
+        if (out_order) CU(cudaMemcpyAsync(out_order, d_order, lv_bytes, cudaMemcpyDeviceToHost, w.st));
+        CU(cudaMemcpyAsync(out_n_levels, d_nl, B, cudaMemcpyDeviceToHost, w.st));
+        CU(cudaMemcpyAsync(out_status, d_st, B, cudaMemcpyDeviceToHost, w.st));
+        CU(cudaStreamSynchronize(w.st));
+    }
     return MCP_OK;
 }
 
 extern "C" int mcp_dag_levels(int device_id, const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
                               int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels,
                               uint8_t *out_status) {
-    if (!n_nodes || !edge_off || !out_level || !out_n_levels || !out_status) return fail(MCP_EINVAL, "NULL buffer");
-    if (n_dags < 0) return fail(MCP_EINVAL, "n_dags < 0");
-    if (n_dags == 0) return MCP_OK;
-    for (int64_t b = 0; b < n_dags; ++b) {
-        if (n_nodes[b] > MCP_MAX_DAG_NODES) return fail(MCP_EINVAL, "DAG %lld has %d nodes (max %d)", (long long)b, n_nodes[b], MCP_MAX_DAG_NODES);
-        if (edge_off[b + 1] < edge_off[b]) return fail(MCP_EINVAL, "edge_off not monotone at %lld", (long long)b);
-    }
-    size_t n_edges = edge_off[n_dags];
-    if (n_edges && !edges) return fail(MCP_EINVAL, "edges is NULL");
-    CU(cudaSetDevice(device_id));
-    Buf dn, doff, de, dl, dord, dnl, dst;
-    int rc = MCP_OK;
-    cudaStream_t st = nullptr;
-    auto cleanup = [&]() { dn.release(); doff.release(); de.release(); dl.release(); dord.release(); dnl.release(); dst.release(); };
-#define TRY(x) do { rc = (x); if (rc) { cleanup(); return rc; } } while (0)
-#define CUT(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { cleanup(); return fail(MCP_ECUDA, "%s -> %s", #x, cudaGetErrorString(e_)); } } while (0)
-    TRY(dn.ensure((size_t)n_dags)); TRY(doff.ensure(sizeof(uint32_t) * (size_t)(n_dags + 1))); TRY(de.ensure(2 * n_edges + 2));
-    TRY(dl.ensure((size_t)n_dags * 64)); TRY(dnl.ensure((size_t)n_dags)); TRY(dst.ensure((size_t)n_dags));
-    if (out_order) TRY(dord.ensure((size_t)n_dags * 64));
-    CUT(cudaMemcpyAsync(dn.p, n_nodes, (size_t)n_dags, cudaMemcpyHostToDevice, st));
-    CUT(cudaMemcpyAsync(doff.p, edge_off, sizeof(uint32_t) * (size_t)(n_dags + 1), cudaMemcpyHostToDevice, st));
-    if (n_edges) CUT(cudaMemcpyAsync(de.p, edges, 2 * n_edges, cudaMemcpyHostToDevice, st));
-    TRY(mcp_dag_levels_device(dn.as<uint8_t>(), doff.as<uint32_t>(), de.as<uint8_t>(), n_dags, dl.as<uint8_t>(),
-                              out_order ? dord.as<uint8_t>() : nullptr, dnl.as<uint8_t>(), dst.as<uint8_t>(), st));
-    CUT(cudaMemcpyAsync(out_level, dl.p, (size_t)n_dags * 64, cudaMemcpyDeviceToHost, st));
-    if (out_order) CUT(cudaMemcpyAsync(out_order, dord.p, (size_t)n_dags * 64, cudaMemcpyDeviceToHost, st));
-    CUT(cudaMemcpyAsync(out_n_levels, dnl.p, (size_t)n_dags, cudaMemcpyDeviceToHost, st));
-    CUT(cudaMemcpyAsync(out_status, dst.p, (size_t)n_dags, cudaMemcpyDeviceToHost, st));
-    CUT(cudaStreamSynchronize(st));
-    cleanup();
-#undef TRY
-#undef CUT
-    return MCP_OK;
+    return dag_levels_host(64, MCP_MAX_DAG_NODES, device_id, n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
+}
+extern "C" int mcp_dag_levels_wide(int device_id, const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
+                                   int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels,
+                                   uint8_t *out_status) {
+    return dag_levels_host(256, MCP_MAX_WIDE_DAG_NODES, device_id, n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1182,13 +1321,14 @@ extern "C" int mcp_dag_levels(int device_id, const uint8_t *n_nodes, const uint3
 // not an address the GPU can use.  The first call on each device therefore asks the runtime for the real
 // device address (cudaGetSymbolAddress, with that device current) and remembers it.  Make that first call
 // before starting any stream capture.
-#define MCP_NOALLOC_MAX_ROWS_ (1 << 20)
-#define MCP_NOALLOC_MAX_QUERIES_ 64
-#define NOALLOC_SCORES_BYTES ((size_t)MCP_NOALLOC_MAX_ROWS_ * sizeof(u64))   // one fp64 score image per row
+#define NOALLOC_SCORES_BYTES ((size_t)MCP_NOALLOC_MAX_ROWS * sizeof(u64))   // one fp64 score image per row
 #define NOALLOC_TAIL_BYTES 4096                                               // norms, flags
 static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCORES_BYTES + NOALLOC_TAIL_BYTES];
+static_assert(NOALLOC_SCORES_BYTES + NOALLOC_TAIL_BYTES == MCP_NOALLOC_SCRATCH_BYTES, "the header's scratch size and the array drifted apart");
+static_assert(MCP_NOALLOC_MAX_QUERIES * (sizeof(double) + sizeof(float) + 1) <= 1024 && (8 + MCP_NOALLOC_MAX_QUERIES) * sizeof(int) <= NOALLOC_TAIL_BYTES - 1024,
+              "the tail of the scratch array holds the query norms and the flag list");
 
-#define NOALLOC_MAX_DEVICES 64
+#define NOALLOC_MAX_DEVICES NOALLOC_MAX_DEVICES_
 static std::mutex g_noalloc_mu;
 static unsigned char *g_noalloc_addr[NOALLOC_MAX_DEVICES] = {nullptr};
 
@@ -1216,12 +1356,12 @@ extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float
     if (!idx->n_rows) return fail(MCP_ESTATE, "search before load");
     if (!queries_device || !out_ids_device || !out_scores_device) return fail(MCP_EINVAL, "NULL buffer");
     if (k < 1 || k > MCP_MAX_K) return fail(MCP_EINVAL, "k %d outside [1, %d]", k, MCP_MAX_K);
-    if (n_queries < 1 || n_queries > MCP_NOALLOC_MAX_QUERIES_)
+    if (n_queries < 1 || n_queries > MCP_NOALLOC_MAX_QUERIES)
         return fail(MCP_EINVAL, "n_queries %d outside [1, %d]: the fixed scratch array holds norms for at most %d queries",
-                    n_queries, MCP_NOALLOC_MAX_QUERIES_, MCP_NOALLOC_MAX_QUERIES_);
-    if (idx->n_rows > MCP_NOALLOC_MAX_ROWS_)
+                    n_queries, MCP_NOALLOC_MAX_QUERIES, MCP_NOALLOC_MAX_QUERIES);
+    if (idx->n_rows > MCP_NOALLOC_MAX_ROWS)
         return fail(MCP_EINVAL, "table has %lld rows; the fixed scratch array holds one score per row for at most %d rows",
-                    (long long)idx->n_rows, MCP_NOALLOC_MAX_ROWS_);
+                    (long long)idx->n_rows, MCP_NOALLOC_MAX_ROWS);
     CU(cudaSetDevice(idx->device));
     unsigned char *base = nullptr;
     int rc = noalloc_scratch_for(idx->device, &base);

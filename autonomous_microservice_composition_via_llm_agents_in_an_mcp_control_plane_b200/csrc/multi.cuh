@@ -158,6 +158,28 @@ static int multi_update_rows(mcp_index *idx, int64_t first_row, const float *row
     });
 }
 
+static int multi_upsert_rows(mcp_index *idx, const int64_t *row_ids, const float *rows_host, int64_t n_rows) {
+    mcp_multi *m = idx->multi;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!idx->n_rows) return fail(MCP_ESTATE, "upsert before load");
+    if (!rows_host || n_rows < 1) return fail(MCP_EINVAL, "rows NULL or n < 1");
+    const int dim = idx->dim;
+    for (int64_t i = 0; i < n_rows; ++i)
+        if (row_ids[i] < 0 || row_ids[i] >= idx->n_rows) return fail(MCP_EINVAL, "row %lld outside the table of %lld rows", (long long)row_ids[i], (long long)idx->n_rows);
+    // split by owner: every shard gets its rows gathered into a contiguous host block with shard-local ids
+    return multi_fanout(m, m->active, [&](int g) {
+        std::vector<int64_t> ids;
+        std::vector<float> rows;
+        for (int64_t i = 0; i < n_rows; ++i)
+            if (row_ids[i] >= m->lo[g] && row_ids[i] < m->lo[g + 1]) {
+                ids.push_back(row_ids[i] - m->lo[g]);
+                rows.insert(rows.end(), rows_host + i * dim, rows_host + (i + 1) * dim);
+            }
+        if (ids.empty()) return (int)MCP_OK;
+        return mcp_index_upsert_rows(m->sub[g], ids.data(), rows.data(), (int64_t)ids.size());
+    });
+}
+
 static int multi_set_option(mcp_index *idx, const char *name, int64_t value) {
     for (mcp_index *s : idx->multi->sub) { int rc = mcp_index_set_option(s, name, value); if (rc) return rc; }
     return MCP_OK;

@@ -246,6 +246,55 @@ shadow_rows_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int6
     }
 }
 
+// ---- row upsert: staged rows -> table, norms, shadow, residual maxima, in one kernel --------------------------------
+// One warp per updated row i (target row ids[i], or first_row + i when ids is NULL).  The warp copies the staged row into
+// the table, lane 0 walks it in index order for the fp64 squared norm (the oracle's order; the row is in L1 by then), and
+// the shadow row, its scale and the residual maxima follow as in shadow_rows_kernel.  Runs on the stream the searches use:
+// a search enqueued before it sees the old row and its old norms, one enqueued after it the new ones, nobody waits on the host.
+__global__ void __launch_bounds__(256)
+upsert_rows_kernel(const float *__restrict__ stage, int64_t lds, const int64_t *__restrict__ ids, int64_t first_row, int64_t n_upd,
+                   float *__restrict__ rows, int dim, int64_t ld, double *__restrict__ norm2, float *__restrict__ inv_norm,
+                   __half *__restrict__ shadow /* or NULL */, int64_t ldh, float *__restrict__ scale_inv, TableConsts *consts) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (i >= n_upd) return;
+    const int64_t r = ids ? ids[i] : first_row + i;
+    const float *src = stage + i * lds;
+    float *dst = rows + r * ld;
+    float vmax = 0.f, dt = 0.f;
+    for (int c = lane; c < (int)ld; c += 32) {
+        const float v = c < dim ? src[c] : 0.f;                  // pad columns of the table stay zero
+        dst[c] = v;
+        vmax = fmaxf(vmax, fabsf(v));
+        const float et = v - tf32_trunc(v);
+        dt = fmaf(et, et, dt);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(MCP_FULL, vmax, o));
+    const float sc = pow2_scale_for(vmax), sci = 1.0f / sc;
+    float dh = 0.f;
+    for (int c = lane; c < (int)ldh; c += 32) {
+        const float x = (c < dim ? src[c] : 0.f) * sc;
+        const __half h = __float2half_rn(x);
+        const float eh = (x - __half2float(h)) * sci;
+        dh = fmaf(eh, eh, dh);
+        if (shadow) shadow[r * ldh + c] = h;
+    }
+    dh = warp_sum(dh); dt = warp_sum(dt);
+    double n2 = 0.0;
+    if (lane == 0) {
+        for (int c = 0; c < dim; ++c) { const double v = (double)src[c]; n2 = fma(v, v, n2); }
+        norm2[r] = n2;
+        inv_norm[r] = (float)(1.0 / sqrt(n2));
+        if (scale_inv) scale_inv[r] = sci;
+        atomicMax(&consts->max_norm2_bits, (u64)__double_as_longlong(n2));
+        if (isfinite(dh) && isfinite(dt)) {
+            atomicMax(&consts->rho_f16, __float_as_uint(rho_up(dh, n2)));
+            atomicMax(&consts->rho_tf32, __float_as_uint(rho_up(dt, n2)));
+        }
+    }
+}
+
 __global__ void penalty_stats_kernel(const float *__restrict__ pen, int64_t n, TableConsts *consts) {
     float mx = -CUDART_INF_F, amx = 0.f;
     bool bad = false;

@@ -25,7 +25,6 @@ struct CertParams {
     int complete;          // candidate set == all rows: nothing was dropped
     double rel;            // relative coarse error bound of the dot product / squared distance that does not depend on the query
     int kind;              // tensor-core scans: 1 tf32, 2 fp16 operands (0: the fp32 streaming scan, `rel` is the whole bound)
-    double rho_e;          // tensor-core scans: largest rounding residual ratio of a table row in that format (TableConsts::rho_*)
     double abs_pen;        // multiplier of pen_absmax for fp32 rounding of the final add
     int debug;             // option gemm_debug >> 8 (timing experiments, wrong results): 1 no chain, 2 no gathers
 };
@@ -305,8 +304,10 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
             // rounding of the two inverse norms.
             double rel = cp.rel;
             if (cp.kind && rho_q) {
+                // read from the device copy of the table constants: a row upsert enqueued ahead of this search may have raised it
                 const double rq = (double)rho_q[2 * q + (cp.kind - 1)];
-                rel += 1.001 * (rq + (1.0 + rq) * cp.rho_e);
+                const double re = (double)__uint_as_float(cp.kind == 2 ? consts->rho_f16 : consts->rho_tf32);
+                rel += 1.001 * (rq + (1.0 + rq) * re);
             }
             double eps;
             if (cp.metric == 0) {

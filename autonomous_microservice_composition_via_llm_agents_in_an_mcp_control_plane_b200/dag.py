@@ -23,7 +23,8 @@ import numpy as np
 
 from . import _native as nat
 
-MAX_NODES = nat.MAX_DAG_NODES
+MAX_NODES = nat.MAX_DAG_NODES            # the batched warp-per-DAG kernel
+MAX_WIDE_NODES = nat.MAX_WIDE_DAG_NODES  # single oversized plans: the CTA-per-DAG kernel
 
 
 @dataclass
@@ -55,8 +56,8 @@ def encode_graphs(graphs: Iterable[dict]) -> EncodedDags:
             u = index.setdefault(e["from"], len(index))
             v = index.setdefault(e["to"], len(index))
             edges.append((u, v))
-        if len(index) > MAX_NODES:
-            raise ValueError(f"graph {gi} has {len(index)} nodes; the level kernel handles at most {MAX_NODES}")
+        if len(index) > MAX_WIDE_NODES:
+            raise ValueError(f"graph {gi} has {len(index)} nodes; the level kernels handle at most {MAX_WIDE_NODES}")
         n_nodes.append(len(index))
         offs.append(len(edges))
         names.append(list(index))
@@ -68,23 +69,52 @@ def encode_graphs(graphs: Iterable[dict]) -> EncodedDags:
     )
 
 
-def levels(enc: EncodedDags, device: int = 0, with_order: bool = True) -> DagLevels:
-    """Host arrays in, host arrays out, through ``mcp_dag_levels`` (copies inside)."""
-    b = len(enc)
-    level = np.empty((b, 64), np.uint8)
-    order = np.empty((b, 64), np.uint8) if with_order else None
+def _levels_call(fn, pitch, nn, off, ed, device, with_order):
+    b = nn.shape[0]
+    level = np.empty((b, pitch), np.uint8)
+    order = np.empty((b, pitch), np.uint8) if with_order else None
     nlev = np.empty(b, np.uint8)
     status = np.empty(b, np.uint8)
+    nat.check(fn(int(device), C.c_void_p(nn.ctypes.data), C.c_void_p(off.ctypes.data),
+                 C.c_void_p(ed.ctypes.data) if ed.size else None, b, C.c_void_p(level.ctypes.data),
+                 C.c_void_p(order.ctypes.data) if with_order else None, C.c_void_p(nlev.ctypes.data),
+                 C.c_void_p(status.ctypes.data)))
+    return level, order, nlev, status
+
+
+def levels(enc: EncodedDags, device: int = 0, with_order: bool = True) -> DagLevels:
+    """Host arrays in, host arrays out, through ``mcp_dag_levels`` (copies inside).  Graphs of more than 64 nodes (up to
+    255) go through ``mcp_dag_levels_wide``; the result arrays are then 256 wide instead of 64."""
+    b = len(enc)
     nn = np.ascontiguousarray(enc.n_nodes, np.uint8)
     off = np.ascontiguousarray(enc.edge_off, np.uint32)
     ed = np.ascontiguousarray(enc.edges, np.uint8)
-    if b:
-        nat.check(nat.lib().mcp_dag_levels(
-            int(device), C.c_void_p(nn.ctypes.data), C.c_void_p(off.ctypes.data),
-            C.c_void_p(ed.ctypes.data) if ed.size else None, b, C.c_void_p(level.ctypes.data),
-            C.c_void_p(order.ctypes.data) if with_order else None, C.c_void_p(nlev.ctypes.data),
-            C.c_void_p(status.ctypes.data)))
-    return DagLevels(level, order if with_order else np.zeros((b, 0), np.uint8), nlev, status)
+    lib = nat.lib()
+    wide = nn > MAX_NODES
+    if not b:
+        return DagLevels(np.empty((0, 64), np.uint8), np.empty((0, 64 if with_order else 0), np.uint8), np.empty(0, np.uint8), np.empty(0, np.uint8))
+    if not wide.any():
+        level, order, nlev, status = _levels_call(lib.mcp_dag_levels, 64, nn, off, ed, device, with_order)
+        return DagLevels(level, order if with_order else np.zeros((b, 0), np.uint8), nlev, status)
+    # mixed batch: the oversized graphs are pulled out into a batch of their own
+    pitch = 256
+    level = np.full((b, pitch), 0xFF, np.uint8)
+    order = np.full((b, pitch), 0xFF, np.uint8) if with_order else np.zeros((b, 0), np.uint8)
+    nlev = np.zeros(b, np.uint8)
+    status = np.zeros(b, np.uint8)
+    off64 = off.astype(np.int64)
+    for sel, fn, p in ((np.flatnonzero(~wide), lib.mcp_dag_levels, 64), (np.flatnonzero(wide), lib.mcp_dag_levels_wide, 256)):
+        if not sel.size:
+            continue
+        cnt = off64[sel + 1] - off64[sel]
+        sub_off = np.concatenate([[0], np.cumsum(cnt)]).astype(np.uint32)
+        sub_ed = np.concatenate([ed[off64[i]:off64[i + 1]] for i in sel]) if cnt.sum() else np.zeros((0, 2), np.uint8)
+        lv, od, nl, st = _levels_call(fn, p, np.ascontiguousarray(nn[sel]), sub_off, np.ascontiguousarray(sub_ed), device, with_order)
+        level[sel, :p] = lv
+        if with_order:
+            order[sel, :p] = od
+        nlev[sel], status[sel] = nl, st
+    return DagLevels(level, order, nlev, status)
 
 
 def levels_device(n_nodes, edge_off, edges, out=None, with_order: bool = True):

@@ -111,6 +111,16 @@ class ServiceIndex:
             nat.check(self._lib.mcp_index_update_rows(self._h, int(first_row), None, int(n_rows)))
         return self
 
+    def upsert_rows(self, row_ids, rows: np.ndarray) -> "ServiceIndex":
+        """Replace the scattered rows ``row_ids`` (row numbers) of a loaded table without stopping queries
+        (``mcp_index_upsert_rows``): returns once the update is enqueued behind the searches in flight."""
+        ids = np.ascontiguousarray(row_ids, dtype=np.int64)
+        rows = np.ascontiguousarray(rows, dtype=np.float32)
+        if rows.ndim != 2 or rows.shape != (ids.shape[0], self.dim):
+            raise ValueError(f"rows must be [{ids.shape[0]}, {self.dim}] float32")
+        nat.check(self._lib.mcp_index_upsert_rows(self._h, _np_ptr(ids), _np_ptr(rows), ids.shape[0]))
+        return self
+
     # ---- flat-file table format (SURVEY.md section 8f item 4) ------------------------------------------------
     # <path>: 64-byte header (magic "MCPTBL01", dim, n_rows, id_base, metric as little-endian int64) + N x dim fp32 rows,
     # row-major -- mmap-able, so a registry loads at file-system speed instead of through Postgres rows (control_plane.py:54).

@@ -40,6 +40,7 @@ extern "C" {
 
 #define MCP_MAX_K 256       /* largest k a search accepts                                   */
 #define MCP_MAX_DAG_NODES 64
+#define MCP_MAX_WIDE_DAG_NODES 255 /* mcp_dag_levels_wide: single oversized plans                */
 
 /* which coarse-scan kernel a search uses (mcp_index_set_option "path") */
 #define MCP_PATH_AUTO 0
@@ -103,8 +104,15 @@ int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, int64_t n_r
 
 /* Registry refresh without a reload: rows [first_row, first_row + n_rows) are replaced by
  * rows_host (tables made by mcp_index_load), or -- rows_host = NULL -- were changed in place by the owner of an adopted
- * table; their norms are recomputed.  Blocks until searches in flight have finished.                                  */
+ * table; their norms are recomputed (that in-place variant blocks until searches in flight have finished).           */
 int mcp_index_update_rows(mcp_index *idx, int64_t first_row, const float *rows_host, int64_t n_rows);
+/* The same for scattered rows, without stopping queries: rows_host [n_rows x dim] replace the table rows row_ids[i] (row
+ * numbers, not service ids; tables made by mcp_index_load).  The rows are validated on the host, staged in pinned memory and
+ * applied by one kernel on the index's own stream -- copy, exact norms, shadow rows -- so the call returns once the work is
+ * enqueued: searches in flight finish on the old rows, later searches see the new ones (searches on another stream wait on
+ * the device, not the host).  mcp_index_update_rows with rows_host != NULL takes the same route.  A failed validation
+ * (NaN / Inf) changes nothing.                                                                                          */
+int mcp_index_upsert_rows(mcp_index *idx, const int64_t *row_ids, const float *rows_host, int64_t n_rows);
 
 /* ---- telemetry fold --------------------------------------------------------------------------
  * One fp32 penalty per service, added to the distance before ranking.  The reference names the
@@ -164,7 +172,9 @@ int mcp_index_coarse_scores_device(mcp_index *idx, int path, const float *querie
  * allocated).  The array is shared by every call on a device and keeps the previous call's contents; each
  * call rewrites what it reads, but calls whose GPU work overlaps (other streams, other indexes on the same
  * device) race on it -- keep them ordered.  The first call on a device looks up the array's device address
- * (one-time set-up): make that first call before starting any stream capture.                            */
+ * (one-time set-up): make that first call before starting any stream capture.  Ordering: mcp_index_update_rows,
+ * _set_penalty, _load and _adopt_device wait for searches issued through the ordinary entry points, but NOT for a scan
+ * issued through this one (it leaves no mark on the index) -- order those calls behind it yourself.                   */
 #define MCP_NOALLOC_MAX_ROWS (1 << 20)
 #define MCP_NOALLOC_MAX_QUERIES 64
 #define MCP_NOALLOC_SCRATCH_BYTES ((8u << 20) + 4096u)
@@ -223,14 +233,25 @@ int mcp_merge_topk_packed_device(const void *packed_device, int n_shards, int n_
  *   out_level   [n_dags*64]  generation of each node; 0xFF = no such node / never emitted (cycle)
  *   out_order   [n_dags*64]  nodes in the order nx.topological_sort yields them; may be NULL
  *   out_n_levels[n_dags]     generations yielded
- *   out_status  [n_dags]     0 ok, 1 = NetworkXUnfeasible (cycle)
- * The host variant copies in/out on `device_id`; the device variant enqueues on `stream`.    */
+ *   out_status  [n_dags]     0 ok, 1 = NetworkXUnfeasible (cycle), 2 = more nodes than the kernel takes (device variants;
+ *                            the host variants refuse such a batch with MCP_EINVAL)
+ * The host variant copies in/out on `device_id` through a per-device workspace that only grows and a stream of its own:
+ * once the workspace has seen a size a call allocates nothing, so the one-graph-per-request use in Orchestrator.execute
+ * does not stall scans running on other streams.  The device variant enqueues on `stream`.
+ * The _wide pair is the same for plans of 65 .. MCP_MAX_WIDE_DAG_NODES nodes (the reference's topological_sort takes any
+ * size): one CTA per DAG, outputs with a pitch of 256 entries per DAG instead of 64.                                    */
 int mcp_dag_levels(int device_id, const uint8_t *n_nodes, const uint32_t *edge_off,
                    const uint8_t *edges, int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
                    uint8_t *out_n_levels, uint8_t *out_status);
 int mcp_dag_levels_device(const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
                           int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
                           uint8_t *out_n_levels, uint8_t *out_status, void *stream);
+int mcp_dag_levels_wide(int device_id, const uint8_t *n_nodes, const uint32_t *edge_off,
+                        const uint8_t *edges, int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
+                        uint8_t *out_n_levels, uint8_t *out_status);
+int mcp_dag_levels_wide_device(const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
+                               int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
+                               uint8_t *out_n_levels, uint8_t *out_status, void *stream);
 
 /* ---- misc ------------------------------------------------------------------------------------ */
 const char *mcp_last_error(void);

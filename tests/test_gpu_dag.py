@@ -88,3 +88,93 @@ def test_device_api_and_invariants(mcp):
     n_emitted = (ordn != 0xFF).sum(1)
     assert (n_emitted[acyc] == enc.n_nodes[acyc]).all()
     assert (nlev.cpu().numpy()[acyc] == lv[acyc].astype(np.int32).max(1, initial=-1, where=lv[acyc] != 0xFF) + 1).all()
+
+
+def test_wide_plans_against_live_networkx(mcp, oracle):
+    """Plans of 65 .. 255 nodes (the reference's topological_sort takes any size) go through the CTA-per-DAG kernel: levels,
+    execution order and cycle status equal NetworkX's, alone and mixed into a batch of ordinary plans."""
+    rng = np.random.default_rng(65)
+    graphs = []
+    for n in (65, 100, 128, 200, 255, 255, 70, 12, 64):
+        names = [f"s{i}" for i in rng.permutation(n)]
+        p = rng.uniform(0.01, 0.08)
+        edges = [{"from": names[i], "to": names[j]} for i in range(n) for j in range(i + 1, n) if rng.random() < p]
+        rng.shuffle(edges)
+        edges += edges[:3]                                                                 # duplicate edges collapse
+        graphs.append({"nodes": [{"name": x} for x in sorted(names)], "edges": edges})
+    graphs.append({"nodes": [{"name": f"c{i}"} for i in range(254)],                        # 254-level chain + an implicit endpoint
+                   "edges": [{"from": f"c{i}", "to": f"c{i + 1}"} for i in range(254)]})
+    cyc = {"nodes": [{"name": f"k{i}"} for i in range(90)],
+           "edges": [{"from": f"k{i}", "to": f"k{i + 1}"} for i in range(89)] + [{"from": "k60", "to": "k30"}]}
+    graphs.append(cyc)
+    enc = mcp.dag.encode_graphs(graphs)
+    res = mcp.dag.levels(enc)
+    assert res.level.shape[1] == 256
+    for i, g in enumerate(graphs):
+        assert mcp.dag.decode(enc, res, i) == oracle.nx_levels(g), i
+    lv_only = mcp.dag.levels(enc, with_order=False)
+    assert np.array_equal(lv_only.level, res.level) and np.array_equal(lv_only.status, res.status)
+    with pytest.raises(ValueError):
+        mcp.dag.encode_graphs([{"nodes": [{"name": f"x{i}"} for i in range(256)], "edges": []}])
+
+
+def test_device_variant_flags_oversized_dags(mcp):
+    import torch
+
+    dev = torch.device("cuda:0")
+    nn = torch.tensor([3, 200, 2], dtype=torch.uint8, device=dev)
+    off = torch.tensor([0, 2, 2, 3], dtype=torch.int32, device=dev)
+    ed = torch.tensor([[0, 1], [1, 2], [0, 1]], dtype=torch.uint8, device=dev)
+    level, order, nlev, status = mcp.dag.levels_device(nn, off, ed)
+    torch.cuda.synchronize()
+    assert status.cpu().tolist() == [0, 2, 0] and nlev.cpu().tolist() == [3, 0, 2]
+    assert (level[1] == 0xFF).all() and level[0, :3].cpu().tolist() == [0, 1, 2]
+
+
+def test_single_graph_calls_do_not_disturb_a_running_scan(mcp):
+    """Orchestrator.execute sends one graph per request through the host entry point.  It must not allocate (a cudaFree
+    synchronises the device) or touch the legacy stream: 1000 such calls on one thread while another thread runs a
+    search loop leave the searches' p99 where it was."""
+    import threading
+    import time
+
+    import torch
+
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev).manual_seed(3)
+    rows = torch.randn((100_000, 1536), generator=g, device=dev)
+    qs = torch.randn((256, 1536), generator=g, device=dev)
+    idx = mcp.ServiceIndex(1536).adopt(rows)
+    enc = mcp.dag.synthetic_dags(1, seed=9)
+    mcp.dag.levels(enc)                                                                    # the workspace has seen the size
+
+    def loop(n, lat):
+        stream = torch.cuda.Stream()
+        with torch.cuda.stream(stream):
+            for _ in range(n):
+                t0 = time.perf_counter()
+                idx.search_device(qs, 32)
+                stream.synchronize()
+                lat.append(time.perf_counter() - t0)
+
+    warm, quiet, busy = [], [], []
+    loop(200, warm)
+    loop(1500, quiet)
+    stop = threading.Event()
+    calls = [0]
+
+    def dag_caller():
+        while not stop.is_set() and calls[0] < 1000:
+            mcp.dag.levels(enc)
+            calls[0] += 1
+
+    th = threading.Thread(target=dag_caller)
+    th.start()
+    loop(1500, busy)
+    stop.set()
+    th.join()
+    idx.sync_status()
+    idx.close()
+    p99q, p99b = np.percentile(quiet, 99), np.percentile(busy, 99)
+    assert calls[0] >= 200, calls
+    assert p99b <= p99q * 1.10 + 20e-6, f"search p99 {p99q * 1e6:.0f} us alone, {p99b * 1e6:.0f} us beside {calls[0]} DAG calls"

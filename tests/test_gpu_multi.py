@@ -64,6 +64,12 @@ def test_multi_handle_updates_ragged_tables_and_refusals(mcp, oracle):
         want_ids, want_s64, _ = oracle.topk(new, qs, 8, 0, None, id_base=500)
         got = multi.search(qs, 8)
         assert np.array_equal(got[0], want_ids) and np.array_equal(got[2], want_s64)
+        ids = np.array([8_999, 3, 4_500, 2_999, 3_000], np.int64)          # scattered over every shard
+        new[ids] = rng.standard_normal((5, d), dtype=np.float32) + qs[1] * 3.0
+        multi.upsert_rows(ids, new[ids])
+        want_ids, want_s64, _ = oracle.topk(new, qs, 8, 0, None, id_base=500)
+        got = multi.search(qs, 8)
+        assert np.array_equal(got[0], want_ids) and np.array_equal(got[2], want_s64)
         with pytest.raises(mcp.McpError):
             multi.adopt(torch.zeros((4, d), device="cuda:0"))          # device pointers belong to one GPU
         with pytest.raises(mcp.McpError):

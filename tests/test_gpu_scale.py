@@ -150,3 +150,65 @@ def test_sharded_search_on_all_gpus_equals_unsharded():
                         "--master-addr", "127.0.0.1", "--master-port", "29517", str(ROOT / "tests" / "multi_gpu_check.py")],
                        capture_output=True, text=True, timeout=900, env=env)
     assert r.returncode == 0 and "MULTI_GPU_CHECK PASS" in r.stdout, r.stdout[-2000:] + r.stderr[-3000:]
+
+
+def test_scattered_upsert_does_not_stop_queries(mcp, oracle):
+    """Registry ingest while serving: 1000 scattered rows are replaced in the middle of a search
+    loop.  The searches' p99 stays where it was, every search returns either the old or the new exact answer, and after the
+    update the table answers like a freshly loaded one (all coarse paths, oracle-checked)."""
+    import threading
+    import time
+
+    rng = np.random.default_rng(88)
+    n, d, q, k = 120_000, 512, 64, 16
+    rows = rng.standard_normal((n, d), dtype=np.float32)
+    qs = rng.standard_normal((q, d), dtype=np.float32)
+    ids = rng.choice(n, 1000, replace=False).astype(np.int64)
+    new_rows = rng.standard_normal((1000, d), dtype=np.float32)
+    new_rows[:q] = qs * 2.5                                            # every query gets a parallel row somewhere in the table
+    after = rows.copy()
+    after[ids] = new_rows
+    old_ids, old_s64, _ = oracle.topk(rows, qs, k, 0, None)
+    new_ids, new_s64, _ = oracle.topk(after, qs, k, 0, None)
+    assert np.array_equal(new_ids[:, 0], ids[:q])
+    with mcp.ServiceIndex(d, "cosine") as idx:
+        idx.load(rows)
+        lat, answers = [], []
+
+        def loop(n_iter):
+            for _ in range(n_iter):
+                t0 = time.perf_counter()
+                got = idx.search(qs, k)
+                lat.append(time.perf_counter() - t0)
+                answers.append(got[0])
+
+        loop(100)
+        lat.clear(); answers.clear()
+        loop(1000)
+        quiet = np.percentile(lat, 99)
+        lat.clear(); answers.clear()
+        th = threading.Thread(target=loop, args=(1000,))
+        th.start()
+        time.sleep(0.02)
+        t0 = time.perf_counter()
+        idx.upsert_rows(ids, new_rows)
+        t_call = time.perf_counter() - t0
+        th.join()
+        busy = np.percentile(lat, 99)
+        assert busy <= quiet * 1.10 + 30e-6, f"search p99 {quiet * 1e6:.0f} us alone, {busy * 1e6:.0f} us with the upsert"
+        kinds = [0 if np.array_equal(a, old_ids) else 1 if np.array_equal(a, new_ids) else 2 for a in answers]
+        assert 2 not in kinds, "a search saw a half-applied update"
+        assert kinds == sorted(kinds) and kinds[-1] == 1              # old answers, then new ones, never back
+        for path in ("gemm_f16", "gemm_tf32", "stream_fp32", "exact_fp64"):
+            idx.set_option("path", path)
+            got = idx.search(qs, k)
+            assert np.array_equal(got[0], new_ids) and np.array_equal(got[2], new_s64), path
+        with pytest.raises(mcp.McpError):
+            idx.upsert_rows(np.array([n], np.int64), new_rows[:1])     # outside the table
+        bad = new_rows[:2].copy()
+        bad[1, 3] = np.nan
+        with pytest.raises(mcp.McpError):
+            idx.upsert_rows(ids[:2], bad)                              # rejected before anything is touched
+        idx.set_option("path", "auto")
+        assert np.array_equal(idx.search(qs, k)[0], new_ids)
+        print(f"upsert of 1000 scattered rows: call returned in {t_call * 1e3:.2f} ms; search p99 {quiet * 1e6:.0f} -> {busy * 1e6:.0f} us")

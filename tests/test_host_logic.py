@@ -73,7 +73,8 @@ def test_encode_graphs_follows_digraph_insertion_rules(mcp):
     assert enc.n_nodes.tolist() == [4, 0]
     assert enc.edge_off.tolist() == [0, 3, 3]
     assert enc.edges.tolist() == [[2, 1], [1, 3], [2, 1]]     # the duplicate edge stays; the kernel collapses it
-    big = {"nodes": [{"name": f"n{i}"} for i in range(65)], "edges": []}
+    assert mcp.dag.encode_graphs([{"nodes": [{"name": f"n{i}"} for i in range(65)], "edges": []}]).n_nodes.tolist() == [65]   # the wide kernel's
+    big = {"nodes": [{"name": f"n{i}"} for i in range(256)], "edges": []}
     with pytest.raises(ValueError):
         mcp.dag.encode_graphs([big])
 
