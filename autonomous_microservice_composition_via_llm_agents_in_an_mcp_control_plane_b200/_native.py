@@ -44,6 +44,7 @@ SIGNATURES = {
     "mcp_index_create_multi": (_i32, [C.POINTER(_vp), C.POINTER(C.c_int), _i32, _i32, _i32]),
     "mcp_index_destroy": (_i32, [_vp]),
     "mcp_index_load": (_i32, [_vp, _vp, _i64, _i64]),
+    "mcp_index_load_file": (_i32, [_vp, C.c_char_p, _i64, _i64]),
     "mcp_index_adopt_device": (_i32, [_vp, _vp, _i64, _i64, _i64, _vp]),
     "mcp_index_update_rows": (_i32, [_vp, _i64, _vp, _i64]),
     "mcp_index_upsert_rows": (_i32, [_vp, _vp, _vp, _i64]),

@@ -11,7 +11,9 @@
 // There is no CPU implementation of any of these in the library: without a device every entry
 // point fails with MCP_ECUDA.
 #include <cuda_runtime.h>
+#include <fcntl.h>
 #include <stdarg.h>
+#include <unistd.h>
 #include <stdio.h>
 #include <string.h>
 
@@ -38,6 +40,8 @@
 #include "merge.cuh"
 #include "kahn.cuh"
 #include "gemm_tf32.cuh"
+#define XS_SMEM_LIMIT (224u * 1024u)      // dynamic shared memory exact_scan2_kernel is launched with
+#include "exact_scan.cuh"
 
 // ---------------------------------------------------------------------------------------------
 // errors
@@ -180,6 +184,7 @@ static int multi_load(mcp_index *idx, const float *rows_host, int64_t n_rows, in
 static int multi_set_penalty(mcp_index *idx, const float *penalty_host);
 static int multi_update_rows(mcp_index *idx, int64_t first_row, const float *rows_host, int64_t n_rows);
 static int multi_upsert_rows(mcp_index *idx, const int64_t *row_ids, const float *rows_host, int64_t n_rows);
+static int multi_load_file(mcp_index *idx, const char *path, int64_t first_row, int64_t n_rows);
 static int multi_set_option(mcp_index *idx, const char *name, int64_t value);
 static int multi_get_stats(mcp_index *idx, mcp_stats *out);
 static int multi_search(mcp_index *idx, const float *queries_host, int nq, int k, int32_t *out_ids, float *out_scores, double *out_scores64);
@@ -189,7 +194,6 @@ static int multi_search(mcp_index *idx, const float *queries_host, int nq, int k
 
 #define NOALLOC_MAX_DEVICES_ 64
 #define SCORE_BUDGET_BYTES (512ull << 20)
-#define XS_SMEM_LIMIT (220u * 1024u)      // dynamic shared memory exact_scan2_kernel may ask for
 #define UNRES_MAX 4096
 
 static int check_idx(const mcp_index *idx) { return idx ? MCP_OK : fail(MCP_EINVAL, "index handle is NULL"); }
@@ -307,6 +311,117 @@ extern "C" int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_
     idx->d_rows = idx->own_rows.as<float>();
     idx->n_rows = n_rows; idx->ld = ld; idx->id_base = id_base;
     return prepare_table(idx, idx->stream);
+}
+
+// ---- table file -> HBM at storage speed (stands where control_plane.py:54 fetches the rows) ----------
+// File: 64-byte header (int64 x 8: magic "MCPTBL01", dim, n_rows, id_base, metric, 0, 0, 0) + n_rows x dim fp32, row-major.
+// Rows [first_row, first_row + n_rows) are read (a rank of a sharded registry reads only its own range) by two reader threads
+// into a ring of pinned chunks while the previous chunks are on their way to the device: one cudaMemcpyAsync per chunk, the
+// reads, the copies and the page-cache / NVMe traffic overlap.  K0 (norms, shadow) then runs over the resident rows as after
+// mcp_index_load; it costs 0.6 ms per GB, which is why there is no norms sidecar to skip it.
+#define LF_CHUNK_BYTES ((size_t)32 << 20)
+#define LF_NBUF 4
+struct TableFileHeader { int64_t magic, dim, n_rows, id_base, metric, r0, r1, r2; };
+
+static int load_file_locked(mcp_index *idx, const char *path, int64_t first_row, int64_t n_rows) {
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return fail(MCP_EINVAL, "cannot open %s", path);
+    TableFileHeader h;
+    int64_t magic;
+    memcpy(&magic, "MCPTBL01", 8);
+    if (pread(fd, &h, sizeof h, 0) != (ssize_t)sizeof h || h.magic != magic) { close(fd); return fail(MCP_EINVAL, "%s is not an MCPTBL01 table file", path); }
+    if (h.dim != idx->dim) { close(fd); return fail(MCP_EINVAL, "%s holds dim %lld, the index has dim %d", path, (long long)h.dim, idx->dim); }
+    if (n_rows < 0) n_rows = h.n_rows - first_row;
+    if (first_row < 0 || n_rows < 1 || first_row + n_rows > h.n_rows) { close(fd); return fail(MCP_EINVAL, "rows [%lld, %lld) outside the file's %lld rows", (long long)first_row, (long long)(first_row + n_rows), (long long)h.n_rows); }
+    const int64_t id_base = h.id_base + first_row;
+    if (id_base < 0 || id_base + n_rows > (1ll << 31)) { close(fd); return fail(MCP_EINVAL, "ids must fit int32"); }
+    cudaError_t ce = cudaSetDevice(idx->device);
+    if (ce != cudaSuccess) { close(fd); return fail(MCP_ECUDA, "cudaSetDevice: %s", cudaGetErrorString(ce)); }
+    if (idx->pending) { cudaEventSynchronize(idx->done); }
+    const int dim = idx->dim;
+    const int64_t ld = (dim + 3) & ~3;
+    int rc = idx->own_rows.ensure(sizeof(float) * (size_t)n_rows * (size_t)ld);
+    if (rc) { close(fd); return rc; }
+    cudaStream_t st = idx->stream;
+    if (ld != dim) cudaMemsetAsync(idx->own_rows.p, 0, sizeof(float) * (size_t)n_rows * (size_t)ld, st);
+    const size_t row_bytes = sizeof(float) * (size_t)dim;
+    const int64_t rows_per_chunk = std::max<int64_t>(1, (int64_t)(LF_CHUNK_BYTES / row_bytes));
+    const int64_t n_chunks = (n_rows + rows_per_chunk - 1) / rows_per_chunk;
+    unsigned char *buf[LF_NBUF] = {nullptr};
+    cudaEvent_t freed[LF_NBUF] = {nullptr};
+    for (int b = 0; b < LF_NBUF && ce == cudaSuccess; ++b) {
+        ce = cudaMallocHost(&buf[b], (size_t)rows_per_chunk * row_bytes);
+        if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&freed[b], cudaEventDisableTiming);
+    }
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<int> state(n_chunks, 0);             // 0 not read, 1 read into its buffer, 2 copy issued
+    int64_t copied = 0;                              // chunks whose copy has been issued (buffer c % LF_NBUF is reusable once freed[] fires)
+    bool failed = ce != cudaSuccess;
+    std::string io_err;
+    auto reader = [&](int tid) {
+        for (int64_t c = tid; c < n_chunks; c += 2) {
+            {   // the buffer's previous tenant (chunk c - LF_NBUF) must have been handed to the copy engine
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return failed || copied > c - LF_NBUF; });
+                if (failed) return;
+            }
+            if (c >= LF_NBUF) cudaEventSynchronize(freed[c % LF_NBUF]);      // ... and the copy must have read it
+            const int64_t r0 = c * rows_per_chunk, nr = std::min(rows_per_chunk, n_rows - r0);
+            size_t want = (size_t)nr * row_bytes, got = 0;
+            const off_t off = (off_t)(sizeof h + (size_t)(first_row + r0) * row_bytes);
+            while (got < want) {
+                const ssize_t k = pread(fd, buf[c % LF_NBUF] + got, want - got, off + (off_t)got);
+                if (k <= 0) break;
+                got += (size_t)k;
+            }
+            std::lock_guard<std::mutex> lk(mu);
+            if (got != want) { failed = true; io_err = "short read"; }
+            state[c] = 1;
+            cv.notify_all();
+        }
+    };
+    std::thread t0, t1;
+    if (!failed) { t0 = std::thread(reader, 0); t1 = std::thread(reader, 1); }
+    for (int64_t c = 0; c < n_chunks && !failed; ++c) {
+        {
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait(lk, [&] { return failed || state[c] == 1; });
+            if (failed) break;
+        }
+        const int64_t r0 = c * rows_per_chunk, nr = std::min(rows_per_chunk, n_rows - r0);
+        float *dst = idx->own_rows.as<float>() + r0 * ld;
+        ce = (ld == dim) ? cudaMemcpyAsync(dst, buf[c % LF_NBUF], (size_t)nr * row_bytes, cudaMemcpyHostToDevice, st)
+                         : cudaMemcpy2DAsync(dst, sizeof(float) * ld, buf[c % LF_NBUF], row_bytes, row_bytes, (size_t)nr, cudaMemcpyHostToDevice, st);
+        if (ce == cudaSuccess) ce = cudaEventRecord(freed[c % LF_NBUF], st);
+        std::lock_guard<std::mutex> lk(mu);
+        if (ce != cudaSuccess) failed = true;
+        state[c] = 2; copied = c + 1;
+        cv.notify_all();
+    }
+    { std::lock_guard<std::mutex> lk(mu); if (ce != cudaSuccess) failed = true; }
+    cv.notify_all();
+    if (t0.joinable()) t0.join();
+    if (t1.joinable()) t1.join();
+    cudaStreamSynchronize(st);
+    for (int b = 0; b < LF_NBUF; ++b) { if (buf[b]) cudaFreeHost(buf[b]); if (freed[b]) cudaEventDestroy(freed[b]); }
+    close(fd);
+    if (failed) {
+        idx->n_rows = 0;
+        if (ce != cudaSuccess) return fail(ce == cudaErrorMemoryAllocation ? MCP_ENOMEM : MCP_ECUDA, "load_file: %s", cudaGetErrorString(ce));
+        return fail(MCP_EINVAL, "load_file: %s reading %s", io_err.c_str(), path);
+    }
+    idx->d_rows = idx->own_rows.as<float>();
+    idx->n_rows = n_rows; idx->ld = ld; idx->id_base = id_base;
+    return prepare_table(idx, st);
+}
+
+extern "C" int mcp_index_load_file(mcp_index *idx, const char *path, int64_t first_row, int64_t n_rows) {
+    if (check_idx(idx)) return MCP_EINVAL;
+    if (!path) return fail(MCP_EINVAL, "path is NULL");
+    if (idx->multi) return multi_load_file(idx, path, first_row, n_rows);
+    std::lock_guard<std::mutex> lk(idx->mu);
+    return load_file_locked(idx, path, first_row, n_rows);
 }
 
 extern "C" int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, int64_t n_rows, int64_t ld,
@@ -504,6 +619,11 @@ extern "C" int mcp_index_set_option(mcp_index *idx, const char *name, int64_t va
         if (value < 0 || value > 64) return fail(MCP_EINVAL, "gemm_sync must be in [0, 64]");
         idx->gemm.sync_tiles = (int)value;
     } else if (!strcmp(name, "gemm_coop")) {
+        // Without the cooperative attribute nothing guarantees that the CTAs K2's two spin-waits depend on are co-resident: on a
+        // busy GPU the kernel can hang.  It exists so that Nsight Compute can replay the launch, and is honoured only together
+        // with the profiling bit of gemm_debug.
+        if (value == 0 && !(idx->gemm.debug & 4096))
+            return fail(MCP_EINVAL, "gemm_coop = 0 is for profiler captures only (co-residency is no longer guaranteed: K2 may hang on a busy GPU); set gemm_debug = 4096 first");
         idx->gemm.coop_attr = value != 0;
     } else if (!strcmp(name, "gemm_pair")) {
         idx->gemm.allow_pair = value != 0;
@@ -655,7 +775,9 @@ static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64
 }
 
 static int choose_kprime(const mcp_index *idx, int k) {
-    int kp = idx->opt_kprime ? std::max(idx->opt_kprime, k) : std::max(2 * k, k + 32) << idx->kp_boost;
+    // automatic: half as many again as asked for, at least 32 more (the residual-based certificate bound is a quarter of the
+    // worst-case one this used to be sized for, when it was 2k)
+    int kp = idx->opt_kprime ? std::max(idx->opt_kprime, k) : std::max(k + k / 2, k + 32) << idx->kp_boost;
     kp = (kp + 31) & ~31;
     return std::min(kp, FINAL_MAX);
 }
@@ -694,6 +816,12 @@ static int scan_grid(const mcp_index *idx) {
     const int64_t tiles = (idx->n_rows + XS_ROWS - 1) / XS_ROWS;
     return (int)std::max<int64_t>(1, std::min<int64_t>(idx->n_sm, tiles));
 }
+// the fp64 scan's TMA view of the fp32 table: boxes of XS_ROWS rows x 32 columns (host-side encode, no allocation)
+static int scan_tensor_map(mcp_index *idx, CUtensorMap *tm) {
+    if (!gemm_supported(0, idx->d_rows, idx->ld)) return fail(MCP_EINVAL, "the fp64 scan needs a 16-byte aligned table with ld %% 4 == 0");
+    if (gemm_encode_2d(idx->gemm, tm, 0, idx->d_rows, idx->n_rows, idx->dim, idx->ld, XS_ROWS)) return fail(MCP_ECUDA, "%s", idx->gemm.err);
+    return MCP_OK;
+}
 
 // path = exact_fp64: flag_list holds `c` queries (flag_all_kernel); dense fp64 scan S slots at a time + exact select
 static int run_exact_dense(mcp_index *idx, cudaStream_t st, const float *d_q, const double *nq2, int k, int c,
@@ -703,10 +831,12 @@ static int run_exact_dense(mcp_index *idx, cudaStream_t st, const float *d_q, co
     if ((rc = idx->exact_all.ensure(sizeof(u64) * (size_t)S * (size_t)idx->n_rows))) return rc;
     int *flag_list = idx->flags.as<int>() + 8, *n_flag = idx->flags.as<int>();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
+    CUtensorMap tm;
+    if ((rc = scan_tensor_map(idx, &tm))) return rc;
     for (int s0 = 0; s0 < c; s0 += S) {
         const int sc = std::min(S, c - s0);
         exact_scan2_kernel<<<scan_grid(idx), XS_THREADS, XS_SMEM_BYTES(idx->dim, S), st>>>(
-            idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag, s0, S,
+            tm, idx->n_rows, idx->dim, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag, s0, S,
             idx->exact_all.as<u64>(), XsSparse{});
         KL();
         exact_select_kernel<<<sc, EXSEL_THREADS, 0, st>>>(idx->exact_all.as<u64>(), idx->n_rows, k, idx->id_base, flag_list, n_flag, s0,
@@ -732,8 +862,10 @@ static int run_fallback(mcp_index *idx, cudaStream_t st, const float *d_q, const
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     XsSparse sp{idx->bound_key.as<u64>(), idx->bound_row.as<int>(), idx->sp_keys.as<u64>(), idx->sp_rows.as<int>(), idx->sp_cnt.as<int>(), XS_SPARSE_CAP};
     const int S = scan_slots(idx);
+    CUtensorMap tm;
+    if ((rc = scan_tensor_map(idx, &tm))) return rc;
     CU(launch_pdl(exact_scan2_kernel, dim3(scan_grid(idx)), dim3(XS_THREADS), XS_SMEM_BYTES(idx->dim, S), st,
-                  idx->d_rows, idx->n_rows, idx->dim, idx->ld, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag, 0, S,
+                  tm, idx->n_rows, idx->dim, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag, 0, S,
                   (u64 *)nullptr, sp));
     KL();
     CU(launch_pdl(exact_pick_kernel, dim3(std::min(cq, 2 * idx->n_sm)), dim3(256), 0, st, flag_list, n_flag, sp, k, idx->id_base, q_base,
@@ -1382,10 +1514,12 @@ extern "C" int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float
     prep_rows_kernel<true><<<1, PREP_ROWS, 0, st>>>(queries_device, n_queries, dim, dim, nq2, inv_nq, qflag, nullptr);
     KCHECK();
     const int gx = scan_grid(idx);
+    CUtensorMap tm;                                                        // host-side encode of the table's TMA view: no allocation
+    if ((rc = scan_tensor_map(idx, &tm))) return rc;
     for (int q = 0; q < n_queries; ++q) {
         flag_all_kernel<<<1, 32, 0, st>>>(flag_list, n_flag, q, 1);        // (re)sets the flag word and the one-entry list
         KCHECK();
-        exact_scan2_kernel<<<gx, XS_THREADS, XS_SMEM_BYTES(dim, 1), st>>>(idx->d_rows, idx->n_rows, dim, idx->ld, queries_device,
+        exact_scan2_kernel<<<gx, XS_THREADS, XS_SMEM_BYTES(dim, 1), st>>>(tm, idx->n_rows, dim, queries_device,
                                                                          nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list,
                                                                          n_flag, 0, 1, scores, XsSparse{});   // writes scores[0 .. n_rows)
         KCHECK();

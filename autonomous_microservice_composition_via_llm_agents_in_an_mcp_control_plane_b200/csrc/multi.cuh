@@ -137,6 +137,29 @@ static int multi_load(mcp_index *idx, const float *rows_host, int64_t n_rows, in
     return MCP_OK;
 }
 
+// every shard reads its own row range of the file, all at once
+static int multi_load_file(mcp_index *idx, const char *path, int64_t first_row, int64_t n_rows) {
+    mcp_multi *m = idx->multi;
+    std::lock_guard<std::mutex> lk(idx->mu);
+    TableFileHeader h;
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return fail(MCP_EINVAL, "cannot open %s", path);
+    const bool ok = pread(fd, &h, sizeof h, 0) == (ssize_t)sizeof h;
+    close(fd);
+    if (!ok) return fail(MCP_EINVAL, "%s is not an MCPTBL01 table file", path);
+    if (n_rows < 0) n_rows = h.n_rows - first_row;
+    if (first_row < 0 || n_rows < 1 || first_row + n_rows > h.n_rows) return fail(MCP_EINVAL, "rows [%lld, %lld) outside the file's %lld rows", (long long)first_row, (long long)(first_row + n_rows), (long long)h.n_rows);
+    const int S = (int)m->sub.size();
+    const int64_t per = (n_rows + S - 1) / S;
+    m->active = 0;
+    for (int g = 0; g <= S; ++g) m->lo[g] = std::min<int64_t>((int64_t)g * per, n_rows);
+    for (int g = 0; g < S; ++g) if (m->lo[g + 1] > m->lo[g]) m->active = g + 1;
+    int rc = multi_fanout(m, m->active, [&](int g) { return mcp_index_load_file(m->sub[g], path, first_row + m->lo[g], m->lo[g + 1] - m->lo[g]); });
+    if (rc) { m->active = 0; idx->n_rows = 0; return rc; }
+    idx->n_rows = n_rows; idx->id_base = h.id_base + first_row;
+    return MCP_OK;
+}
+
 static int multi_set_penalty(mcp_index *idx, const float *penalty_host) {
     mcp_multi *m = idx->multi;
     std::lock_guard<std::mutex> lk(idx->mu);

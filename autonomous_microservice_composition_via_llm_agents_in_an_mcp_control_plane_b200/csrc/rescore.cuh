@@ -329,30 +329,8 @@ rescore_finalize_kernel(const float *__restrict__ rows, int dim, int64_t ld, con
     }
 }
 
-// ---- K4c: fp64 scan of every row for the flagged queries ---------------------------------------------------------
-// The certificate's fallback, the explicit path = exact_fp64 and the allocation-free entry point all run this kernel.
-// It streams the table once per pass for up to S flagged queries ("slots") at a time:
-//   * rows come in through a cp.async ring of [XS_ROWS rows][XS_COLS columns] tiles (256 contiguous bytes per row and
-//     chunk), so HBM is read in full lines -- a thread walking its own 6 KB row with loads 6 KB apart, as the first
-//     version did, ran at a fraction of the HBM rate;
-//   * thread = (row of the tile, half of the slots): it walks ITS row in index order, one fp64 chain per slot it owns (the
-//     oracle's arithmetic and order, so scores are bit-equal), reading the queries as fp64 from shared memory (warp-wide
-//     broadcasts) -- up to four independent chains per thread hide the DFMA latency.
-// Output, dense mode: the ordered fp64 image of every score, [slot][n_rows] (exact_select_kernel then picks the top k).
-// Output, sparse mode: only rows whose (score, row) pair is at or below the query's bound -- the k-th best exact pair among
-// the candidates the coarse pass found, which the true k-th pair cannot exceed -- appended to a short per-slot list.  A
-// handful of rows per query instead of n_rows scores, so the fallback needs no n_rows-sized scratch and serves any number
-// of flagged queries in one launch (the kernel loops over them S at a time).
-#define XS_ROWS 128
-#define XS_COLS 64
-#define XS_PITCH (XS_COLS + 4)          // 68 floats = 17 x 16 B: float4 reads of 8 consecutive rows hit 8 different bank groups
-#define XS_STAGES 3
-#define XS_THREADS 256
-#define XS_MAXS 8
+// ---- K4c lives in exact_scan.cuh (it uses the TMA wrappers of gemm_tf32.cuh); its output descriptors: ------------------
 #define XS_SPARSE_CAP 2048
-#define XS_TILE_BYTES (sizeof(float) * XS_STAGES * XS_ROWS * XS_PITCH)
-#define XS_SMEM_BYTES(dim, S) (sizeof(double) * (size_t)(S) * (size_t)(((dim) + 3) & ~3) + XS_TILE_BYTES)
-
 struct XsSparse {
     const u64 *bound_key;      // [query] ordered fp64 image of the bound score (all-ones: no bound)
     const int *bound_row;      // [query] row of the bound pair
@@ -361,116 +339,6 @@ struct XsSparse {
     int *cnt;                  // [slot] appended so far (may exceed cap: the list overflowed); zero on entry
     int cap;
 };
-
-__global__ void __launch_bounds__(XS_THREADS, 1)
-exact_scan2_kernel(const float *__restrict__ rows, int64_t n_rows, int dim, int64_t ld,
-                   const float *__restrict__ queries, const double *__restrict__ nq2,
-                   const double *__restrict__ ne2, const float *__restrict__ penalty, int metric,
-                   const int *__restrict__ flag_list, const int *__restrict__ n_flag, int slot0, int S,
-                   u64 *__restrict__ dense /* [S][n_rows] for slots slot0 .. slot0+S-1, or NULL: sparse */, XsSparse sp) {
-    extern __shared__ __align__(16) unsigned char xs_raw[];
-    pdl_trigger();
-    pdl_wait();                                      // the kernel that flagged queries has completed
-    const int nf_all = *n_flag;
-    const int g_end = dense ? min(nf_all, slot0 + S) : nf_all;
-    if (slot0 >= g_end) return;                      // nothing flagged: the common case
-    const int dimp = (dim + 3) & ~3;
-    double *sq = reinterpret_cast<double *>(xs_raw);                 // [S][dimp] the pass's queries in fp64
-    float *tile = reinterpret_cast<float *>(sq + (size_t)S * dimp);  // [XS_STAGES][XS_ROWS][XS_PITCH]
-    const int row_l = threadIdx.x & (XS_ROWS - 1), half = threadIdx.x / XS_ROWS;
-    const int nchunks = (dimp + XS_COLS - 1) / XS_COLS;
-    const int64_t n_tiles = (n_rows + XS_ROWS - 1) / XS_ROWS;
-    const int my_tiles = (int64_t)blockIdx.x < n_tiles ? (int)((n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
-    const int n_it = my_tiles * nchunks;
-    auto issue = [&](int it) {
-        if (it < n_it) {
-            const int ti = it / nchunks, c = it - ti * nchunks, st = it % XS_STAGES;
-            const int64_t r0 = ((int64_t)blockIdx.x + (int64_t)ti * gridDim.x) * XS_ROWS;
-            float *dst = tile + (size_t)st * XS_ROWS * XS_PITCH;
-#pragma unroll
-            for (int u = 0; u < XS_ROWS * (XS_COLS / 4) / XS_THREADS; ++u) {
-                const int e = threadIdx.x + u * XS_THREADS, r = e / (XS_COLS / 4), ch = e % (XS_COLS / 4);
-                const int col = c * XS_COLS + ch * 4;
-                if (col < dimp) cp_async16(dst + r * XS_PITCH + ch * 4, rows + min(r0 + r, n_rows - 1) * ld + col);
-            }
-        }
-        cp_async_commit();
-    };
-    for (int s0 = slot0; s0 < g_end; s0 += S) {
-        const int sc = min(S, g_end - s0);           // slots of this pass
-        __syncthreads();                             // the previous pass has left sq and the ring
-        for (int u = 0; u < sc; ++u) {
-            const float *qv = queries + (int64_t)flag_list[s0 + u] * dim;
-            for (int i = threadIdx.x; i < dimp; i += XS_THREADS) sq[(size_t)u * dimp + i] = i < dim ? (double)qv[i] : 0.0;
-        }
-        // my slots: half, half + 2, half + 4, half + 6
-        const int myn = sc > half ? (sc - half + 1) / 2 : 0;
-        int myq[4]; double mynq2[4]; u64 mybk[4]; int mybr[4];
-#pragma unroll
-        for (int v = 0; v < 4; ++v) {
-            myq[v] = v < myn ? flag_list[s0 + half + 2 * v] : 0;
-            mynq2[v] = v < myn ? nq2[myq[v]] : 1.0;
-            mybk[v] = (v < myn && !dense) ? sp.bound_key[myq[v]] : ~0ull;
-            mybr[v] = (v < myn && !dense) ? sp.bound_row[myq[v]] : 0x7FFFFFFF;
-        }
-        for (int it = 0; it < XS_STAGES - 1; ++it) issue(it);
-        double acc[4] = {0.0, 0.0, 0.0, 0.0};
-        for (int it = 0; it < n_it; ++it) {
-            issue(it + XS_STAGES - 1);
-            cp_async_wait<XS_STAGES - 1>();
-            __syncthreads();                         // chunk `it` has landed for every thread (and sq is complete on the first turn)
-            const int ti = it / nchunks, c = it - ti * nchunks;
-            const int c0 = c * XS_COLS, w = min(XS_COLS, dimp - c0);
-            const float *e = tile + (size_t)(it % XS_STAGES) * XS_ROWS * XS_PITCH + row_l * XS_PITCH;
-            if (c == 0) { acc[0] = acc[1] = acc[2] = acc[3] = 0.0; }
-            if (myn > 0) {
-                for (int j = 0; j < w; j += 4) {
-                    const float4 x = *reinterpret_cast<const float4 *>(e + j);
-                    const double d0 = (double)x.x, d1 = (double)x.y, d2 = (double)x.z, d3 = (double)x.w;
-#pragma unroll
-                    for (int v = 0; v < 4; ++v) {
-                        if (v < myn) {
-                            const double *qq = sq + (size_t)(half + 2 * v) * dimp + c0 + j;
-                            const double2 qa = *reinterpret_cast<const double2 *>(qq), qb = *reinterpret_cast<const double2 *>(qq + 2);
-                            if (metric == 0) {
-                                acc[v] = fma(qa.x, d0, acc[v]); acc[v] = fma(qa.y, d1, acc[v]);
-                                acc[v] = fma(qb.x, d2, acc[v]); acc[v] = fma(qb.y, d3, acc[v]);
-                            } else {
-                                double t;
-                                t = __dsub_rn(qa.x, d0); acc[v] = __dadd_rn(acc[v], __dmul_rn(t, t));
-                                t = __dsub_rn(qa.y, d1); acc[v] = __dadd_rn(acc[v], __dmul_rn(t, t));
-                                t = __dsub_rn(qb.x, d2); acc[v] = __dadd_rn(acc[v], __dmul_rn(t, t));
-                                t = __dsub_rn(qb.y, d3); acc[v] = __dadd_rn(acc[v], __dmul_rn(t, t));
-                            }
-                        }
-                    }
-                }
-            }
-            if (c == nchunks - 1) {
-                const int64_t row = ((int64_t)blockIdx.x + (int64_t)ti * gridDim.x) * XS_ROWS + row_l;
-                if (row < n_rows && myn > 0) {
-                    const double ne2r = ne2[row], pr = penalty ? (double)penalty[row] : 0.0;
-#pragma unroll
-                    for (int v = 0; v < 4; ++v) {
-                        if (v < myn) {
-                            double sco = exact_finish(acc[v], metric, mynq2[v], ne2r);
-                            if (penalty) sco = sco + pr;
-                            const u64 key = f64_ord(sco);
-                            const int slot = s0 + half + 2 * v;
-                            if (dense) __stcg(dense + (int64_t)(slot - slot0) * n_rows + row, key);
-                            else if (key < mybk[v] || (key == mybk[v] && row <= (int64_t)mybr[v])) {
-                                const int p = atomicAdd(&sp.cnt[slot], 1);
-                                if (p < sp.cap) { sp.keys[(int64_t)slot * sp.cap + p] = key; sp.rows[(int64_t)slot * sp.cap + p] = (int)row; }
-                            }
-                        }
-                    }
-                }
-            }
-            __syncthreads();                         // everyone has left this stage before the next turn refills it
-        }
-        cp_async_wait<0>();
-    }
-}
 
 // ---- sparse lists -> top k, one CTA per flagged query; folds the status words -------------------------------------
 // status: [0] certificate failures, [1] unresolved (a sparse list overflowed: the bound let more than `cap` rows through --

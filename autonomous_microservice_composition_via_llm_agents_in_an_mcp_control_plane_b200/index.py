@@ -154,12 +154,18 @@ class ServiceIndex:
             pass
         return rows, names, id_base, metric
 
-    def load_file(self, path) -> list:
-        """Load a table written by ``save_table``; returns the names sidecar (or None)."""
-        rows, names, id_base, _ = self.open_table(path)
-        if rows.shape[1] != self.dim:
-            raise ValueError(f"{path} holds dim {rows.shape[1]}, index has dim {self.dim}")
-        self.load(rows, id_base)
+    def load_file(self, path, first_row: int = 0, n_rows: Optional[int] = None) -> list:
+        """Load rows ``[first_row, first_row + n_rows)`` of a table written by ``save_table`` (default: all of it) through the
+        library's pinned chunk pipeline (``mcp_index_load_file``); service ids are the file's id_base + row number in the
+        file.  Returns the names sidecar (or None), sliced to the same rows."""
+        nat.check(self._lib.mcp_index_load_file(self._h, str(path).encode(), int(first_row), -1 if n_rows is None else int(n_rows)))
+        self._keep.clear()
+        names = None
+        try:
+            with open(str(path) + ".names", encoding="utf-8") as f:
+                names = f.read().split("\n")[first_row:first_row + self.n_rows]
+        except FileNotFoundError:
+            pass
         return names
 
     def set_penalty(self, penalty) -> "ServiceIndex":
@@ -198,8 +204,8 @@ class ServiceIndex:
         import torch
 
         if not (queries.is_cuda and queries.dtype == torch.float32 and queries.is_contiguous()
-                and queries.dim() == 2 and queries.shape[1] == self.dim):
-            raise ValueError("queries must be contiguous CUDA float32 [Q, dim]")
+                and queries.dim() == 2 and queries.shape[1] == self.dim and queries.device.index == self.device):
+            raise ValueError("queries must be contiguous CUDA float32 [Q, dim] on the index's device")
         nq = queries.shape[0]
         if out is None:
             dev = queries.device
@@ -228,9 +234,16 @@ class ServiceIndex:
         running on another stream, or fail when HBM is fully budgeted).  At most 1,048,576 rows and 64 queries;
         all calls on one device share one fixed scratch array, so keep them on one stream.  The first call on a
         device does a one-time address look-up: make it before starting any stream capture."""
+        import torch
+
         ids, sc, sc64 = out
+        if not (queries.is_cuda and queries.dtype == torch.float32 and queries.is_contiguous() and queries.dim() == 2
+                and queries.shape[1] == self.dim and queries.device.index == self.device):
+            raise ValueError("queries must be contiguous CUDA float32 [Q, dim] on the index's device")
         nq = queries.shape[0]
-        assert tuple(ids.shape) == (nq, k) and ids.is_contiguous() and sc.is_contiguous() and sc64.is_contiguous()
+        for t, dt in ((ids, torch.int32), (sc, torch.float32), (sc64, torch.float64)):
+            if not (t.is_cuda and t.dtype == dt and t.is_contiguous() and tuple(t.shape) == (nq, k) and t.device == queries.device):
+                raise ValueError("out = (ids int32, scores float32, scores float64), contiguous CUDA [Q, k] tensors on the index's device")
         nat.check(self._lib.mcp_index_search_exact_noalloc_device(
             self._h, C.c_void_p(queries.data_ptr()), nq, int(k), C.c_void_p(ids.data_ptr()),
             C.c_void_p(sc.data_ptr()), C.c_void_p(sc64.data_ptr()), _stream_ptr()))

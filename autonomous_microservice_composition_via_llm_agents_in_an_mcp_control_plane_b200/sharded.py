@@ -91,6 +91,16 @@ class ShardedIndex:
         self.local.adopt(rows, id_base=lo)
         return self
 
+    def load_file_shard(self, path, n_total: Optional[int] = None):
+        """Every rank reads only its own row range of the table file (``ServiceIndex.load_file`` window)."""
+        from .index import ServiceIndex
+
+        if n_total is None:
+            n_total = ServiceIndex.open_table(path)[0].shape[0]
+        lo, hi = shard_bounds(n_total, self.world, self.rank)
+        self.local.load_file(path, lo, hi - lo)
+        return self
+
     def set_penalty(self, pen):
         self.local.set_penalty(pen)
         return self

@@ -101,6 +101,12 @@ int mcp_index_create_multi(mcp_index **out, const int *device_ids, int n_devices
 int mcp_index_load(mcp_index *idx, const float *rows_host, int64_t n_rows, int64_t id_base);
 int mcp_index_adopt_device(mcp_index *idx, const float *rows_device, int64_t n_rows, int64_t ld,
                            int64_t id_base, void *stream);
+/* The same read from a flat table file instead of Postgres rows: 64-byte header (int64 x 8:
+ * magic "MCPTBL01", dim, n_rows, id_base, metric, 0, 0, 0) followed by n_rows x dim fp32, row-major.  Rows [first_row,
+ * first_row + n_rows) are loaded (n_rows = -1: to the end; a rank of a sharded registry reads only its own range) through a
+ * ring of pinned chunks: two reader threads, one cudaMemcpyAsync per chunk, reads and copies overlapped.  ids are the
+ * file's id_base + row number in the file.                                                                              */
+int mcp_index_load_file(mcp_index *idx, const char *path, int64_t first_row, int64_t n_rows);
 
 /* Registry refresh without a reload: rows [first_row, first_row + n_rows) are replaced by
  * rows_host (tables made by mcp_index_load), or -- rows_host = NULL -- were changed in place by the owner of an adopted
@@ -183,7 +189,7 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
                                           double *out_scores64_device, void *stream);
 
 /* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
- * query before exact rescoring, >= k; automatic starts at max(2k, k + 32) and doubles, up to 4x, while more than 1 in 200
+ * query before exact rescoring, >= k; automatic starts at max(1.5 k, k + 32) and doubles, up to 4x, while more than 1 in 200
  * queries need the fp64 scan -- clustered registries -- and steps back after 64 clean status reads), "max_fallback" (queries one pass of the fp64 scan serves at a time, 1 .. 8; default 8),
  * "shadow" (default 1: load / adopt also build an fp16 image of the table (each row scaled by a power of two), +50 % device memory, which the batched scan
  * reads instead of the fp32 rows; the answer stays exact -- candidates are rescored in fp64 from the fp32 rows and certified
@@ -198,7 +204,8 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
  * non-pair shapes run as single CTAs with plain loads, multicast being kept to memory the library allocated itself),
  * "gemm_sync" (default 1: the CTAs of K2 that stream the same row tiles stay within this many tiles of each other, so the
  * tiles are served from L2 instead of being re-read from HBM by every query block; 0 = off),
- * "gemm_coop" (default 1; 0 = launch K2 without the cooperative attribute -- for Nsight Compute captures only),
+ * "gemm_coop" (default 1; 0 = launch K2 without the cooperative attribute -- for Nsight Compute captures only: co-residency
+ * of the CTAs K2's spin-waits rely on is then no longer guaranteed, so it is refused unless "gemm_debug" holds bit 4096),
  * "gemm_debug" (bit mask for timing experiments that switch off parts of K2 / K4 -- results are WRONG; default 0),
  * "gemm_bootstrap" (0 = K2 without the cross-CTA threshold bootstrap; default 1),
  * "time_coarse" (1 = bracket every coarse scan with CUDA events on the caller's stream; the sums

@@ -350,6 +350,24 @@ def test_update_rows_and_table_file(mcp, oracle, tmp_path):
         names = idx.load_file(p)
         assert names[7] == "n7"
         _assert_parity(idx.search(qs, 4), want_ids, want_s64)
+        # a row window of the file (what one rank of a sharded registry reads): ids stay the file's row numbers
+        names = idx.load_file(p, 900, 2200)
+        assert idx.n_rows == 2200 and names[0] == "n900" and len(names) == 2200
+        w_ids, w_s64, _ = oracle.topk(new[900:3100], qs, 4, 0, None, id_base=900)
+        _assert_parity(idx.search(qs, 4), w_ids, w_s64)
+        with pytest.raises(mcp.McpError):
+            idx.load_file(p, 4000, 2000)                               # past the end of the file
+    odd = rng.standard_normal((777, 250), dtype=np.float32)            # dim % 4 != 0: rows are padded on the way in
+    p2 = tmp_path / "odd.mcp"
+    mcp.ServiceIndex.save_table(p2, odd, id_base=10)
+    q2 = rng.standard_normal((3, 250), dtype=np.float32)
+    o_ids, o_s64, _ = oracle.topk(odd, q2, 5, 1, None, id_base=10)
+    with mcp.ServiceIndex(250, "l2") as idx:
+        idx.load_file(p2)
+        _assert_parity(idx.search(q2, 5), o_ids, o_s64)
+    with mcp.ServiceIndex(256, "cosine", [0, 0]) as multi:             # two shards, each reading its own half of the file
+        multi.load_file(p)
+        _assert_parity(multi.search(qs, 4), want_ids, want_s64)
 
 
 def test_query_chunking_paths_agree(mcp, oracle):

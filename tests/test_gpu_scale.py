@@ -57,7 +57,7 @@ def test_config3_share_full_size(mcp, oracle, metric):
     fails, unresolved = idx.sync_status()
     st = idx.stats()
     assert unresolved == 0
-    assert st["last_path"] == 4 and st["last_kprime"] == 128, st             # the fp16 shadow scan, k' = 2k
+    assert st["last_path"] == 4 and st["last_kprime"] == 96, st              # the fp16 shadow scan, k' = 1.5 k
     assert bool((s64[:, 1:] >= s64[:, :-1]).all())
     for path in ("gemm_tf32", "exact_fp64"):
         idx.set_option("path", path)
