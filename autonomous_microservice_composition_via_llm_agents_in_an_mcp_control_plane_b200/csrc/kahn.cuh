@@ -18,12 +18,15 @@
 #define KAHN_THREADS 256
 #define KAHN_WARPS (KAHN_THREADS / 32)
 
+#define KAHN_FE 4
 struct KahnWarp {
     u64 pred[64];
     u64 fm[64];            // frontier mask of each generation
     u64 key[64];
     uint32_t firste[64];
+    uint32_t fe[64][KAHN_FE];  // first edge index from each of a node's (up to KAHN_FE) parents in the previous generation
     unsigned char lvl[64], pos[64], ustar[64], order[64];
+    int fe_overflow;           // some node has more such parents than the table holds: this DAG rescans its edges per generation
 };
 
 template <bool WITH_ORDER>
@@ -77,42 +80,84 @@ kahn_levels_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__
         if (WITH_ORDER) {
             w.lvl[lane] = l0; w.lvl[lane + 32] = l1;
             w.order[lane] = 0xFF; w.order[lane + 32] = 0xFF;
+#pragma unroll
+            for (int j = 0; j < 2 * KAHN_FE; ++j) (&w.fe[0][0])[j * 32 + lane] = 0xFFFFFFFFu;
+            if (lane == 0) w.fe_overflow = 0;
             __syncwarp();
+            // One pass over the edges for the tie-break among siblings: the order of a generation needs, per node, the index
+            // of the first edge from the parent that released it -- one of its parents in the previous generation.  Which one
+            // is only known once that generation is ordered, so the first edge from EACH such parent is recorded here
+            // (slot = rank of the parent among them), instead of rescanning the edge list generation after generation.
+            for (uint32_t e = e0 + lane; e < e1; e += 32) {
+                const uchar2 uv = ed[e];
+                if (uv.x < n && uv.y < n) {
+                    const int lv = w.lvl[uv.y];
+                    if (lv != 0xFF && lv > 0 && w.lvl[uv.x] == lv - 1) {
+                        const u64 cand = w.pred[uv.y] & w.fm[lv - 1];
+                        const int slot = __popcll(cand & ((1ull << uv.x) - 1ull));
+                        if (slot < KAHN_FE) atomicMin(&w.fe[uv.y][slot], e - e0);
+                        else w.fe_overflow = 1;
+                    }
+                }
+            }
+            __syncwarp();
+            const bool rescan = w.fe_overflow != 0;
             int base = 0;
             for (int L = 0; L < level; ++L) {
                 const u64 f = w.fm[L];
                 const bool in0 = (f >> lane) & 1ull, in1 = (f >> (lane + 32)) & 1ull;
-                u64 k0 = (u64)lane, k1 = (u64)(lane + 32);       // generation 0: node order
-                if (L > 0) {
+                int rk0 = 0, rk1 = 0;
+                if (L == 0) {
+                    // generation 0 comes in node order: the rank is a population count
+                    rk0 = __popcll(f & ((1ull << lane) - 1ull));
+                    rk1 = __popcll(f & ((1ull << (lane + 32)) - 1ull));
+                } else {
                     const u64 prev = w.fm[L - 1];
-                    int bp0 = -1, bp1 = -1;
+                    int bp0 = -1, bp1 = -1, bu0 = 0, bu1 = 0;
                     if (in0) {
-                        u64 c = p0 & prev; int bu = 0;
-                        while (c) { int u = __ffsll((long long)c) - 1; c &= c - 1; int p = w.pos[u]; if (p > bp0) { bp0 = p; bu = u; } }
-                        w.ustar[lane] = (unsigned char)bu; w.firste[lane] = 0xFFFFFFFFu;
+                        u64 c = p0 & prev;
+                        while (c) { int u = __ffsll((long long)c) - 1; c &= c - 1; int p = w.pos[u]; if (p > bp0) { bp0 = p; bu0 = u; } }
                     }
                     if (in1) {
-                        u64 c = p1 & prev; int bu = 0;
-                        while (c) { int u = __ffsll((long long)c) - 1; c &= c - 1; int p = w.pos[u]; if (p > bp1) { bp1 = p; bu = u; } }
-                        w.ustar[lane + 32] = (unsigned char)bu; w.firste[lane + 32] = 0xFFFFFFFFu;
+                        u64 c = p1 & prev;
+                        while (c) { int u = __ffsll((long long)c) - 1; c &= c - 1; int p = w.pos[u]; if (p > bp1) { bp1 = p; bu1 = u; } }
                     }
-                    __syncwarp();
-                    for (uint32_t e = e0 + lane; e < e1; e += 32) {
-                        uchar2 uv = ed[e];
-                        if (uv.x < n && uv.y < n && w.lvl[uv.y] == L && w.ustar[uv.y] == uv.x)
-                            atomicMin(&w.firste[uv.y], e - e0);
+                    // Positions of the zeroing parents as a bit set.  When no two nodes of the generation share a parent
+                    // (most generations) the position alone orders them -- the rank is a population count and the edge list
+                    // need not be consulted; the first-edge index only breaks ties between siblings.
+                    const u64 m0 = in0 ? 1ull << bp0 : 0ull, m1 = in1 ? 1ull << bp1 : 0ull;
+                    const u64 mm = m0 | m1;
+                    const u64 BP = (u64)__reduce_or_sync(MCP_FULL, (unsigned)mm) | ((u64)__reduce_or_sync(MCP_FULL, (unsigned)(mm >> 32)) << 32);
+                    if (__popcll(BP) == __popcll(f)) {
+                        rk0 = in0 ? __popcll(BP & (m0 - 1ull)) : 0;
+                        rk1 = in1 ? __popcll(BP & (m1 - 1ull)) : 0;
+                    } else {
+                        uint32_t fe0 = 0, fe1 = 0;
+                        if (rescan) {
+                            if (in0) { w.ustar[lane] = (unsigned char)bu0; w.firste[lane] = 0xFFFFFFFFu; }
+                            if (in1) { w.ustar[lane + 32] = (unsigned char)bu1; w.firste[lane + 32] = 0xFFFFFFFFu; }
+                            __syncwarp();
+                            for (uint32_t e = e0 + lane; e < e1; e += 32) {
+                                uchar2 uv = ed[e];
+                                if (uv.x < n && uv.y < n && w.lvl[uv.y] == L && w.ustar[uv.y] == uv.x)
+                                    atomicMin(&w.firste[uv.y], e - e0);
+                            }
+                            __syncwarp();
+                            if (in0) fe0 = w.firste[lane];
+                            if (in1) fe1 = w.firste[lane + 32];
+                        } else {
+                            if (in0) fe0 = w.fe[lane][__popcll((p0 & prev) & ((1ull << bu0) - 1ull))];
+                            if (in1) fe1 = w.fe[lane + 32][__popcll((p1 & prev) & ((1ull << bu1) - 1ull))];
+                        }
+                        u64 k0 = 0, k1 = 0;
+                        if (in0) { k0 = ((u64)bp0 << 32) | fe0; w.key[lane] = k0; }
+                        if (in1) { k1 = ((u64)bp1 << 32) | fe1; w.key[lane + 32] = k1; }
+                        __syncwarp();
+                        for (u64 m = f; m; m &= m - 1) {
+                            u64 kx = w.key[__ffsll((long long)m) - 1];
+                            rk0 += kx < k0; rk1 += kx < k1;
+                        }
                     }
-                    __syncwarp();
-                    if (in0) k0 = ((u64)bp0 << 32) | w.firste[lane];
-                    if (in1) k1 = ((u64)bp1 << 32) | w.firste[lane + 32];
-                }
-                if (in0) w.key[lane] = k0;
-                if (in1) w.key[lane + 32] = k1;
-                __syncwarp();
-                int rk0 = 0, rk1 = 0;
-                for (u64 m = f; m; m &= m - 1) {
-                    u64 kx = w.key[__ffsll((long long)m) - 1];
-                    rk0 += kx < k0; rk1 += kx < k1;
                 }
                 if (in0) { w.pos[lane] = (unsigned char)(base + rk0); w.order[base + rk0] = (unsigned char)lane; }
                 if (in1) { w.pos[lane + 32] = (unsigned char)(base + rk1); w.order[base + rk1] = (unsigned char)(lane + 32); }
