@@ -428,6 +428,11 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if rank == 0 and os.environ.get("OMP_NUM_THREADS") == "1" and "MCP_BENCH_KEEP_OMP" not in os.environ:
+        # torchrun sets OMP_NUM_THREADS=1 for every rank it starts; the CPU arm runs on rank 0 alone and is meant to use every
+        # host core, so give them back before numpy / OpenBLAS read the variable
+        ncores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        os.environ["OMP_NUM_THREADS"] = os.environ["OPENBLAS_NUM_THREADS"] = str(ncores)
     if args.impl == "reference":
         return run_reference(args, world, rank)
 
