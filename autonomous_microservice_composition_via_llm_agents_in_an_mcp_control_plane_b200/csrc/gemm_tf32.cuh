@@ -521,12 +521,14 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
                 if (li == 0 && i > 1 && ((i - 1) & (i - 2)) == 0) {
                     const ulonglong2 *pp = reinterpret_cast<const ulonglong2 *>(pq);
-                    ulonglong2 x[16];
-#pragma unroll
-                    for (int l = 0; l < 16; ++l) x[l] = l < a.boot_lists / 2 ? __ldcg(pp + l) : make_ulonglong2(0ull, 0ull);
                     u64 t0 = 0;
+                    for (int l0 = 0; l0 < a.boot_lists / 2; l0 += 16) {          // 32 published keys per round of loads (64 lists: two rounds)
+                        ulonglong2 x[16];
 #pragma unroll
-                    for (int l = 0; l < 16; ++l) { t0 = x[l].x > t0 ? x[l].x : t0; t0 = x[l].y > t0 ? x[l].y : t0; }
+                        for (int l = 0; l < 16; ++l) x[l] = l0 + l < a.boot_lists / 2 ? __ldcg(pp + l0 + l) : make_ulonglong2(0ull, 0ull);
+#pragma unroll
+                        for (int l = 0; l < 16; ++l) { t0 = x[l].x > t0 ? x[l].x : t0; t0 = x[l].y > t0 ? x[l].y : t0; }
+                    }
                     const float tf = ord_f32((uint32_t)(t0 >> 32));
                     if (t0 != ~0ull && tf == tf) a.tau_pub[qg] = ((u64)a.epoch << 32) | (u64)__float_as_uint(tf);
                 }
@@ -861,7 +863,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     const size_t list_bytes = sizeof(u64) * (size_t)nq * L * cap;
     const size_t cnt_off = (hdr + list_bytes + 255) & ~(size_t)255;
     const size_t pub_off = (cnt_off + sizeof(int) * (size_t)nq * L + 255) & ~(size_t)255;
-    const size_t end_off = (pub_off + sizeof(u64) * (size_t)nq * 32 + 255) & ~(size_t)255;
+    const size_t end_off = (pub_off + sizeof(u64) * (size_t)nq * 64 + 255) & ~(size_t)255;
     if ((rc = ws.ensure(end_off))) { snprintf(p.err, sizeof p.err, "workspace allocation failed"); return rc; }
     unsigned char *wsb = reinterpret_cast<unsigned char *>(ws.p);
     GemmArgs a;
@@ -881,7 +883,9 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     a.idesc_single = g_idesc(kind, G_BM, G_BN);
     a.idesc_pair = g_idesc(kind, 2 * G_BM, bn);
     // bootstrap needs every CTA of a query block resident at once: cooperative launch, grid <= #SMs (1 CTA / SM)
+    // lists that publish: 32 when four keys each cover k' (fewer lists -> lower maximum), else up to 64 (k' up to 256)
     int boot_lists = std::min(L, 32) & ~1;                       // even: both halves of a CTA
+    if (boot_lists && (kprime + boot_lists - 1) / boot_lists > G_BOOT_MAX) boot_lists = std::min(L, 64) & ~1;
     const int m = boot_lists ? (kprime + boot_lists - 1) / boot_lists : G_BOOT_MAX + 1;
     if (p.coop < 0) {
         int dev = 0, v = 0;

@@ -868,7 +868,7 @@ static int run_fallback(mcp_index *idx, cudaStream_t st, const float *d_q, const
                   tm, idx->n_rows, idx->dim, d_q, nq2, idx->norm2.as<double>(), pen, idx->metric, flag_list, n_flag, 0, S,
                   (u64 *)nullptr, sp));
     KL();
-    CU(launch_pdl(exact_pick_kernel, dim3(std::min(cq, 2 * idx->n_sm)), dim3(256), 0, st, flag_list, n_flag, sp, k, idx->id_base, q_base,
+    CU(launch_pdl(exact_pick_kernel, dim3(std::min(cq, 64)), dim3(256), 0, st, flag_list, n_flag, sp, k, idx->id_base, q_base,
                   out_ids, out_scores, out_scores64, n_flag + 1, idx->h_status_dev, idx->unres.as<int>(), UNRES_MAX));
     KL();
     return MCP_OK;

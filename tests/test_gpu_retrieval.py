@@ -437,3 +437,40 @@ def test_bootstrap_tile_drops_are_caught_by_the_certificate(mcp, oracle):
         st = idx.stats()
         assert st["last_path"] == 2
         assert st["certificate_failures"] >= 1, "the dropped rows of the bootstrap tile went unnoticed"
+
+
+def test_foreign_memory_is_refused(mcp):
+    """Every device pointer handed to an index must be plain device memory of the index's own GPU (the kernels and the TMA
+    tensor maps built over those buffers read this GPU's memory only): pinned host memory, and on a multi-GPU box another
+    GPU's memory, are refused with MCP_EINVAL at the C ABI -- the Python wrapper's own checks are bypassed here."""
+    import ctypes as C
+
+    import torch
+
+    from autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 import _native as nat
+
+    lib = nat.lib()
+    d = 64
+    dev = torch.device("cuda:0")
+    rows = torch.randn((1000, d), device=dev)
+    with mcp.ServiceIndex(d, "cosine", 0) as idx:
+        idx.adopt(rows)
+        ids = torch.empty((4, 3), dtype=torch.int32, device=dev)
+        sc = torch.empty((4, 3), dtype=torch.float32, device=dev)
+        host_q = torch.randn((4, d)).pin_memory()
+        rc = lib.mcp_index_search_device(idx._h, C.c_void_p(host_q.data_ptr()), 4, 3, C.c_void_p(ids.data_ptr()), C.c_void_p(sc.data_ptr()), None, None)
+        assert rc == -1 and b"not device memory of GPU 0" in lib.mcp_last_error()
+        host_rows = torch.randn((100, d)).pin_memory()
+        rc = lib.mcp_index_adopt_device(idx._h, C.c_void_p(host_rows.data_ptr()), 100, d, 0, None)
+        assert rc == -1
+        if torch.cuda.device_count() >= 2:
+            peer = torch.randn((1000, d), device="cuda:1")
+            rc = lib.mcp_index_adopt_device(idx._h, C.c_void_p(peer.data_ptr()), 1000, d, 0, None)
+            assert rc == -1 and b"device 1" in lib.mcp_last_error()
+            peer_q = torch.randn((4, d), device="cuda:1")
+            rc = lib.mcp_index_search_device(idx._h, C.c_void_p(peer_q.data_ptr()), 4, 3, C.c_void_p(ids.data_ptr()), C.c_void_p(sc.data_ptr()), None, None)
+            assert rc == -1
+        q = torch.randn((4, d), device=dev)                                  # and the index still works afterwards
+        got = idx.search_device(q, 3)[0]
+        torch.cuda.synchronize()
+        assert got.shape == (4, 3) and int(got.min()) >= 0
