@@ -779,7 +779,8 @@ static const void *gemm_kernel_ptr(int mt, int kpl, int metric, bool pair) {
 // and their inverse scales in q_scale_inv [nq] / row_scale_inv [n_rows].
 template <class BufT>
 static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int kind, const void *rows, int64_t n_rows, int dim,
-                         int64_t ld, const void *queries, int64_t ldq, int nq, const float *inv_nq, const float *nq2f,
+                         int64_t ld, const void *queries, int64_t ldq, int nq_map /* rows of the query operand: >= nq, zero rows past nq */,
+                         int nq, const float *inv_nq, const float *nq2f,
                          const float *inv_ne, const double *ne2, const float *penalty, int metric, int kprime,
                          u64 **out_lists, int **out_cnt, int *out_L, int *out_cap, float *dump = nullptr,
                          unsigned int *drop_min = nullptr /* [nq], all-ones on entry: enables the cross-CTA bootstrap */,
@@ -792,7 +793,7 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     if (nq > G_MAX_QBLOCKS * G_BM) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch takes at most %d queries", G_MAX_QBLOCKS * G_BM); return -1; }
     const int MTsel = 1;                                         // 128-query CTAs
     CUtensorMap tmA;
-    int rc = gemm_encode_2d(p, &tmA, kind, queries, nq, dim, ldq, MTsel * G_BM);
+    int rc = gemm_encode_2d(p, &tmA, kind, queries, nq_map, dim, ldq, MTsel * G_BM);
     if (rc) return rc;
     const int nqb = (nq + MTsel * G_BM - 1) / (MTsel * G_BM);
     int n_tiles = (int)((n_rows + G_BN - 1) / G_BN);

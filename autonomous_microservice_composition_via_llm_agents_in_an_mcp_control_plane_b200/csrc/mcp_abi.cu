@@ -884,6 +884,7 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     if (is_gemm_path(path)) kprime = std::min(kprime, gemm_max_kprime());   // >= k since k <= 256
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
 
+    bool q_copied = false;                       // the tensor-core scan reads the library's operand image of the queries, not the caller's buffer
     if ((rc = idx->nq2.ensure(sizeof(double) * nq))) return rc;
     if ((rc = idx->inv_nq.ensure(sizeof(float) * nq))) return rc;
     if ((rc = idx->qflag.ensure(nq))) return rc;
@@ -903,18 +904,21 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
     } else {
         // the tensor-core scans read an operand image of the queries: scaled fp16 (pitch ldh), or -- tf32 with dim % 4 != 0 -- an fp32
         // copy whose pitch a tensor map accepts; otherwise the caller's queries are the operand
+        // (also when the batch is not a multiple of 8 queries: the image is padded with zero rows, see the kernel)
         void *q_out = nullptr; int ldq = dim, as_f16 = 0;
+        const int nq_pad = (nq + 7) & ~7;
         if (path == MCP_PATH_GEMM_F16) { ldq = (int)idx->ldh; as_f16 = 1; }
-        else if (path == MCP_PATH_GEMM_TF32 && (dim & 3)) ldq = (dim + 3) & ~3;
-        if (as_f16 || ldq != dim) {
-            if ((rc = idx->q_op.ensure((size_t)nq * ldq * (as_f16 ? 2 : 4)))) return rc;
+        else if (path == MCP_PATH_GEMM_TF32) ldq = (dim + 3) & ~3;
+        q_copied = as_f16 || (path == MCP_PATH_GEMM_TF32 && (ldq != dim || nq_pad != nq));
+        if (q_copied) {
+            if ((rc = idx->q_op.ensure((size_t)nq_pad * ldq * (as_f16 ? 2 : 4)))) return rc;
             q_out = idx->q_op.p;
         }
         if ((rc = idx->rho_q.ensure(sizeof(float) * 2 * (size_t)nq))) return rc;
         if ((rc = idx->q_scale.ensure(sizeof(float) * (size_t)nq))) return rc;
-        prep_queries_fast_kernel<<<(nq + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), n_flag,
+        prep_queries_fast_kernel<<<((q_copied ? nq_pad : nq) + 3) / 4, 128, 0, st>>>(d_q, nq, dim, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), n_flag,
                                                                idx->drop_min.as<unsigned int>(), idx->rho_q.as<float>(), q_out, ldq, as_f16,
-                                                               idx->q_scale.as<float>());
+                                                               idx->q_scale.as<float>(), q_copied ? nq_pad : nq);
         KL();
     }
 
@@ -995,9 +999,9 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             const bool bf = path == MCP_PATH_GEMM_F16;
             const int ldq = bf ? (int)idx->ldh : (dim + 3) & ~3;
             const void *qop = bf ? (const void *)(idx->q_op.as<__half>() + (int64_t)q0 * ldq)
-                                 : (dim & 3) ? (const void *)(idx->q_op.as<float>() + (int64_t)q0 * ldq) : (const void *)dq;
+                                 : q_copied ? (const void *)(idx->q_op.as<float>() + (int64_t)q0 * ldq) : (const void *)dq;
             if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, bf ? 1 : 0, bf ? (const void *)idx->shadow.p : (const void *)idx->d_rows,
-                                    n, dim, bf ? idx->ldh : idx->ld, qop, ldq, cq,
+                                    n, dim, bf ? idx->ldh : idx->ld, qop, ldq, q_copied ? (cq + 7) & ~7 : cq, cq,
                                     idx->inv_nq.as<float>() + q0, idx->nq2f.as<float>() + q0, idx->inv_norm.as<float>(),
                                     idx->norm2.as<double>(), pen, idx->metric, kprime, &lists, &cnts, &L, &cap, nullptr,
                                     idx->drop_min.as<unsigned int>() + q0, bf ? idx->q_scale.as<float>() + q0 : nullptr,
@@ -1223,15 +1227,16 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
     const bool bf = path == MCP_PATH_GEMM_F16;
     if (bf && !idx->has_shadow) return fail(MCP_ESTATE, "coarse_scores: the index holds no fp16 shadow table");
     const int ldq = bf ? (int)idx->ldh : (dim + 3) & ~3;
+    const int nq_pad = (n_queries + 7) & ~7;
     void *q_out = nullptr;
-    if (bf || (path == MCP_PATH_GEMM_TF32 && ldq != dim)) {
-        if ((rc = idx->q_op.ensure((size_t)n_queries * ldq * (bf ? 2 : 4)))) return rc;
+    if (bf || (path == MCP_PATH_GEMM_TF32 && (ldq != dim || nq_pad != n_queries))) {
+        if ((rc = idx->q_op.ensure((size_t)nq_pad * ldq * (bf ? 2 : 4)))) return rc;
         q_out = idx->q_op.p;
     }
     if ((rc = idx->q_scale.ensure(sizeof(float) * (size_t)n_queries))) return rc;
-    prep_queries_fast_kernel<<<(n_queries + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
+    prep_queries_fast_kernel<<<((q_out ? nq_pad : n_queries) + 3) / 4, 128, 0, st>>>(queries_device, n_queries, dim, idx->inv_nq.as<float>(),
                                                                  idx->nq2f.as<float>(), nullptr, nullptr, nullptr, q_out, ldq, bf ? 1 : 0,
-                                                                 idx->q_scale.as<float>());
+                                                                 idx->q_scale.as<float>(), q_out ? nq_pad : n_queries);
     KCHECK();
     const float *pen = idx->has_penalty ? idx->penalty.as<float>() : nullptr;
     if (path == MCP_PATH_STREAM_FP32) {
@@ -1246,7 +1251,7 @@ extern "C" int mcp_index_coarse_scores_device(mcp_index *idx, int path, const fl
         u64 *l; int *c; int L, cap;
         if ((rc = gemm_tf32_run(idx->gemm, idx->gemm_ws, st, idx->n_sm, bf ? 1 : 0, bf ? (const void *)idx->shadow.p : (const void *)idx->d_rows,
                                 idx->n_rows, dim, bf ? idx->ldh : idx->ld, q_out ? (const void *)q_out : (const void *)queries_device, ldq,
-                                n_queries, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), idx->inv_norm.as<float>(),
+                                q_out ? nq_pad : n_queries, n_queries, idx->inv_nq.as<float>(), idx->nq2f.as<float>(), idx->inv_norm.as<float>(),
                                 idx->norm2.as<double>(), pen, idx->metric, 64, &l, &c, &L, &cap, out_scores_device, nullptr,
                                 bf ? idx->q_scale.as<float>() : nullptr, bf ? idx->shadow_scale.as<float>() : nullptr)))
             return fail(rc, "%s", idx->gemm.err);
