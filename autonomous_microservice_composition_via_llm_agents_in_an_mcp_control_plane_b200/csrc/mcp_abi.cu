@@ -760,6 +760,10 @@ static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64
         if (L == 1 && cap <= kprime && !raw_in) break;   // already one list of at most k' ordered keys
         first = false;
         int G = std::min(L, SEL_THREADS);          // one CTA per query unless there are more than SEL_THREADS lists
+        // Few queries, many lists (one query over 1 M rows leaves ~300 lists and ~15 K keys): one CTA per query would chew
+        // through them 4096 keys at a time (55 us measured); groups of >= 16 lists go to CTAs of their own and a second round
+        // reduces the group results, so that about as many CTAs as there are SMs work at once.
+        if (nq < idx->n_sm && L > 32) G = std::min(L, std::max(16, (int)((int64_t)L * nq / idx->n_sm + 1)));
         int L_out = (L + G - 1) / G;
         Buf &ob = in_is_A ? idx->listsB : idx->listsA;
         Buf &oc = in_is_A ? idx->cntB : idx->cntA;
