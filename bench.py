@@ -40,7 +40,7 @@ CONFIGS = {
 METRIC_NAME = "top-k retrieval queries/sec"
 UNIT = "queries/s"
 PATH_KERNEL = {1: "scan_fp32_kernel", 2: "gemm_tf32_kernel (kind::tf32)", 3: "exact_scan2_kernel", 4: "gemm_tf32_kernel (kind::f16 over the fp16 shadow)"}
-MIN_WARM_S = 0.7          # steps run before the timed region until the part has been under load this long (clocks settle)
+MIN_WARM_S = 2.0          # steps run before the timed region until the part has been under load this long (clocks and power settle)
 
 
 def peaks():

@@ -140,7 +140,8 @@ def run(pkg, rows, pen, requests=10_000, clients=32, k=8, endpoint_requests=300)
         "retrieve_sequential_ms": {"p50": pct(lat, 50), "p99": pct(lat, 99), "mean": float(np.mean(lat) * 1e3), "n": len(lat),
                                    "note": "GraphPlanner.retrieve: hash embedding (numpy) + mcp_index_search + name lookup"},
         "mcp_index_search_ms": {"p50": pct(lat_abi, 50), "p99": pct(lat_abi, 99), "n": len(lat_abi),
-                                "hbm_floor_ms": n * rows.shape[1] * 4 / 6551.4e9 * 1e3, "path": idx.stats()["last_path"]},
+                                "hbm_floor_ms_fp32_rows": n * rows.shape[1] * 4 / 6551.4e9 * 1e3,
+                                "hbm_floor_ms_fp16_shadow": n * rows.shape[1] * 2 / 6551.4e9 * 1e3, "path": idx.stats()["last_path"]},
         "retrieve_concurrent_ms": {"clients": clients, "p50": pct(lat_c, 50), "p99": pct(lat_c, 99),
                                    "throughput_rps": len(lat_c) / wall_c},
         "retrieve_concurrent_microbatched_ms": {"clients": clients, "p50": pct(lat_m, 50), "p99": pct(lat_m, 99),
