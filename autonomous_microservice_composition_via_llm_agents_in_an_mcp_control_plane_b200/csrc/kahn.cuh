@@ -111,7 +111,7 @@ kahn_levels_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__
                     // generation 0 comes in node order: the rank is a population count
                     rk0 = __popcll(f & ((1ull << lane) - 1ull));
                     rk1 = __popcll(f & ((1ull << (lane + 32)) - 1ull));
-                } else {
+                } else if ((f & (f - 1ull)) != 0ull) {           // a generation of one node needs no ordering: rank 0
                     const u64 prev = w.fm[L - 1];
                     int bp0 = -1, bp1 = -1, bu0 = 0, bu1 = 0;
                     if (in0) {
