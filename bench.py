@@ -582,6 +582,29 @@ def main():
                                        "frac_of_aggregate_measured_hbm": round(n * dim * 4 / (ms_step * 1e-3) / 1e9 / (pk["hbm"] * world), 4),
                                        "note": "the 10M-row fp32 table's bytes per whole step over N x measured HBM; at 1024 queries per batch the scan is tensor-bound "
                                                "(3.93 TFLOP per GPU at N = 8 would need 2.7 PFLOP/s dense to meet 80 % of HBM; DESIGN.md section 4)"}}
+    # ---- the same sharded table below the ridge: 64 queries per batch, where the scan is HBM-bound (north_star's own target:
+    #      the sharded 10M-row scan at >= 80 % of the aggregate HBM roofline); every rank takes part
+    if not args.no_extras:
+        try:
+            qb = make_queries(torch, dev, 64, dim, 4242)
+            for _ in range(10):
+                sh.search_device(qb, k)
+            barrier()
+            ms64 = all_max(time_steps(torch, lambda: sh.search_device(qb, k), 30))
+            kms64, p64, _ = kernel_pass(torch, sh.local, lambda: sh.search_device(qb, k), 10)
+            kms64 = all_max(kms64)
+            sh.check()
+            b64, _ = alg_bytes_flops(n_loc, 64, k, dim, p64)
+            extra["sharded_scan_64_queries"] = {
+                "ms_per_step": round(ms64, 4), "queries_per_s": round(64 / ms64 * 1e3, 1), "scan_kernel_ms": round(kms64, 4), "path": p64,
+                "bytes_read_per_gpu": b64, "aggregate_GBps_scan_kernel": round(b64 * world / (kms64 * 1e-3) / 1e9, 1),
+                "frac_of_aggregate_measured_hbm_scan_kernel": round(b64 / (kms64 * 1e-3) / 1e9 / pk["hbm"], 4),
+                "frac_of_aggregate_measured_hbm_whole_step": round(b64 / (ms64 * 1e-3) / 1e9 / pk["hbm"], 4),
+                "fp32_table_equivalent_GBps_aggregate": round(n * dim * 4 / (ms64 * 1e-3) / 1e9, 1),
+                "note": "bytes actually read (the fp16 shadow when path = 4) per GPU over the scan kernel's / the whole step's time, against the measured HBM copy rate; max over ranks"}
+        except Exception as ex:  # noqa: BLE001
+            extra["sharded_scan_64_queries"] = {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
+
     cpu_baseline = None
     if rank == 0 and not args.no_cpu_baseline:
         # the oracle's numpy port on this box's host cores, on a bounded slice of THIS rank's rows (same queries), scaled to the table
