@@ -72,8 +72,9 @@ struct GemmArgs {
     uint32_t epoch;            // this launch's number: older entries in `progress` read as "not started"
     int boot_early;            // the bootstrap tile hands its accumulator back before the wait (large tables only, see gemm_tf32_run)
     int boot_m, boot_lists;    // lists 0 .. boot_lists-1 publish their boot_m-th smallest key (boot_lists even)
-    const float *rows;         // table base + row pitch, for the L2 row prefetch
-    int64_t ld;
+    const unsigned char *rows_b;   // operand table base, row pitch and row length in bytes, for the L2 row prefetch
+    int64_t row_pitch_b;
+    int row_len_b;
     int l2_prefetch;
     int bn;                    // rows per tile (<= 256, a multiple of the cluster size): chosen so that every CTA gets the same number of tiles
     int cluster;               // CTAs per cluster (1, 2 or 4): the query-block CTAs that share a row tile load a slice each and multicast it
@@ -350,17 +351,17 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 // each page one k-block later, long after other tiles have closed it.  Every 8 k-blocks the query
                 // block 0 CTA therefore pulls the *next* 1 KB of each of the tile's rows into L2 with one bulk prefetch
                 // per row (8 rows per lane): DRAM sees 1 KB bursts, the TMA boxes that follow hit L2.
-                if (a.l2_prefetch && a.kind == 0 && qb == 0 && (kb & 7) == 0) {
+                if (a.l2_prefetch && qb == 0 && (kb & 7) == 0) {
                     int pt = t, pk = kb + 8;
                     if (pk >= KB) { pt = t + ngroups; pk = 0; }
                     if (pt < n_tiles) {
-                        const int bytes = min(8 * G_BK, a.dim - pk * G_BK) * 4;
+                        const int bytes = min(1024, a.row_len_b - pk * 128);       // a k-block is 128 bytes of a row in either kind
                         const int64_t prow0 = (int64_t)pt * BN;
 #pragma unroll
                         for (int u = 0; u < G_BN / 32; ++u) {
                             const int64_t r = prow0 + u * 32 + lane;
-                            if (r < a.n_rows && bytes > 0)
-                                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.rows + r * a.ld + pk * G_BK), "r"(bytes & ~15) : "memory");
+                            if (r < a.n_rows && bytes >= 16)
+                                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.rows_b + r * a.row_pitch_b + pk * 128), "r"(bytes & ~15) : "memory");
                         }
                     }
                 }
@@ -876,7 +877,8 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     a.tau_pub = reinterpret_cast<u64 *>(wsb + tau_off);
     a.arrive = nullptr; a.arrive_next = nullptr;
     a.dump = dump;
-    a.rows = kind ? nullptr : (const float *)rows; a.ld = ld; a.l2_prefetch = (p.l2_prefetch && !kind) ? 1 : 0; a.debug = p.debug; a.cluster = C; a.bn = bn;
+    a.rows_b = (const unsigned char *)rows; a.row_pitch_b = ld * (kind ? 2 : 4); a.row_len_b = dim * (kind ? 2 : 4);
+    a.l2_prefetch = p.l2_prefetch ? 1 : 0; a.debug = p.debug; a.cluster = C; a.bn = bn;
     a.pair = pair ? 1 : 0;
     a.kind = kind; a.ek = kind ? 2 * G_BK : G_BK;
     a.q_scale_inv = q_scale_inv; a.row_scale_inv = row_scale_inv;

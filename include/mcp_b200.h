@@ -73,7 +73,7 @@ typedef struct mcp_stats {
  * Stands where GraphPlanner.__init__ opens its pgvector connection (control_plane.py:46-49):
  * the handle is the "connection" to the embedding table, now resident in HBM.              */
 int mcp_index_create(mcp_index **out, int device_id, int dim, int metric);
-int mcp_index_destroy(mcp_index *idx);
+int mcp_index_destroy(mcp_index *idx);   /* waits for the device; must not race with any other call on the same handle */
 /* The same "connection" over a table too large (or too hot) for one GPU: the reference is ONE process whose planner makes
  * plain method calls (control_plane.py:135-138, :57-75), so the sharding of SURVEY.md section 8e has to fit behind one
  * handle.  The handle owns one single-device index per entry of device_ids (contiguous row ranges, global ids) and one
@@ -195,7 +195,7 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
  * reads instead of the fp32 rows; the answer stays exact -- candidates are rescored in fp64 from the fp32 rows and certified
  * with a bound computed from the actual rounding residuals.  0 = no shadow, the batched scan reads the fp32 rows as tf32.
  * Set it before the table is loaded.  When the shadow does not fit in device memory the index quietly goes without),
- * "gemm_l2_prefetch" (1 = K2 with a per-row 1 KB L2 bulk prefetch; default 0, measured slower),
+ * "gemm_l2_prefetch" (1 = K2 with a per-row 1 KB L2 bulk prefetch; default 0, measured slower with either operand kind),
  * "gemm_balance" (1 = K2 tile height shrunk so that every CTA gets the same number of tiles; default 0 = 256-row tiles, measured equal),
  * "gemm_cluster" (CTAs per cluster that share a row tile: 0 = automatic -- 2 when the batch has an even number of
  * 128-query blocks, else 1 -- or 1 / 2 / 4),
