@@ -242,13 +242,9 @@ __device__ __forceinline__ u64 warp_prune_list(u64 *lp, int n, int kprime, int l
     return mx;
 }
 
-// MT = query blocks (of 128) per CTA.
-//   MT = 1: D[128 x 256], TMEM double-buffered (2 x 256 columns): epilogue of tile i overlaps the MMAs of tile i+1;
-//           48 KB per k-block stage, 4 stages.
-//   MT = 2: D[256 x 256] as two accumulators sharing the row tile (all 512 TMEM columns, single-buffered): the row
-//           tile is fetched once for 256 queries, which cuts shared-memory fill traffic per output by a third
-//           (6144 B x (1/256 + 1/256) instead of (1/128 + 1/256)); 64 KB per stage, 3 stages.  K2 is bound by
-//           L2 -> SM fill bandwidth (profiles/), so this is the better trade whenever there are >= 256 queries.
+// MT = query blocks (of 128) per CTA.  Only MT = 1 is instantiated: D[128 x 256], TMEM double-buffered (2 x 256 columns), so the
+// epilogue of tile i overlaps the MMAs of tile i+1.  (MT = 2 -- two accumulators sharing the row tile, all 512 TMEM columns,
+// single-buffered -- measured slower in round 1 and was retired; the template parameter stays for the shared-memory layout.)
 template <int MT, int PAIR = 0> struct GemmCfg {
     static constexpr int B_ROWS = PAIR ? G_BN / 2 : G_BN;      // rows of the tile this CTA's shared memory holds
     static constexpr int STAGES = PAIR ? 6 : (MT == 1 ? 4 : 3);   // pair: 32 KB per stage, 6 stages = 5 k-blocks (~1.8 us of MMA time) in flight

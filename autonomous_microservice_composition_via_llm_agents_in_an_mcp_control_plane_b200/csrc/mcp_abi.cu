@@ -1,12 +1,14 @@
 // mcp_abi.cu -- the C ABI (include/mcp_b200.h) and the host-side orchestration of the kernels.
 //
-//   K0 prep.cuh        row / query norms, penalty statistics
-//   K1 scan_fp32.cuh   fp32 streaming distance + telemetry score            (small batches)
-//   K2 gemm_tf32.cuh   tcgen05 / TMEM TF32 distance GEMM, fused score + top-k' filter (large batches)
+//   K0 prep.cuh        row / query norms, fp16 shadow rows and rounding residuals, row upsert, penalty statistics
+//   K1 scan_fp32.cuh   fp32 streaming distance + telemetry score            (small batches, tables without a shadow)
+//   K2 gemm_tf32.cuh   tcgen05 / TMEM distance GEMM over the fp16 shadow (kind::f16) or the fp32 rows (kind::tf32),
+//                      fused score + top-k' filter with a shared, tightening threshold
 //   K3 select.cuh      radix top-k' selection / list reduction
-//   K4 rescore.cuh     exact fp64 rescoring, final sort, certificate, fp64 fallback scan
+//   K4 rescore.cuh     exact fp64 rescoring, final sort, certificate; exact_scan.cuh: the fp64 scan behind it
 //   K5 merge.cuh       shard merge
-//   K6 kahn.cuh        batched Kahn levels
+//   K6 kahn.cuh        batched Kahn levels (<= 64 nodes per warp; 65..255 nodes per CTA)
+//      multi.cuh       one handle over several GPUs (worker thread per shard)
 //
 // There is no CPU implementation of any of these in the library: without a device every entry
 // point fails with MCP_ECUDA.

@@ -190,7 +190,7 @@ int mcp_index_search_exact_noalloc_device(mcp_index *idx, const float *queries_d
 
 /* options: "path" (MCP_PATH_*), "kprime" (0 = automatic oversampling, else candidates kept per
  * query before exact rescoring, >= k; automatic starts at max(1.5 k, k + 32) and doubles, up to 4x, while more than 1 in 200
- * queries need the fp64 scan -- clustered registries -- and steps back after 64 clean status reads), "max_fallback" (queries one pass of the fp64 scan serves at a time, 1 .. 8; default 8),
+ * queries need the fp64 scan -- clustered registries -- and steps back after 64 clean status reads), "max_fallback" (queries one pass of the fp64 scan serves at a time, 1 .. 6; default 6),
  * "shadow" (default 1: load / adopt also build an fp16 image of the table (each row scaled by a power of two), +50 % device memory, which the batched scan
  * reads instead of the fp32 rows; the answer stays exact -- candidates are rescored in fp64 from the fp32 rows and certified
  * with a bound computed from the actual rounding residuals.  0 = no shadow, the batched scan reads the fp32 rows as tf32.
