@@ -9,12 +9,14 @@ vectors for it, see ``oracle.c``); DAG levels are pinned against NetworkX.
 from .cpu_oracle import (  # noqa: F401
     COSINE,
     L2,
+    agrees_with_fp32_reference,
     build,
     dag_levels,
     merge,
     nx_levels,
     numpy_topk_baseline,
     numpy_topk_blocked,
+    pgvector_f32_scores,
     scores,
     telemetry_penalty,
     topk,

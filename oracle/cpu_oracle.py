@@ -42,6 +42,8 @@ def _load():
         u8, u32 = c.POINTER(c.c_uint8), c.POINTER(c.c_uint32)
         lib.oracle_scores.argtypes = [fp, c.c_int64, c.c_int, c.c_int64, fp, c.c_int, fp, dp]
         lib.oracle_scores.restype = None
+        lib.oracle_pgvector_f32_scores.argtypes = [fp, c.c_int64, c.c_int, c.c_int64, fp, c.c_int, fp, dp]
+        lib.oracle_pgvector_f32_scores.restype = None
         lib.oracle_topk.argtypes = [fp, c.c_int64, c.c_int, c.c_int64, fp, c.c_int, c.c_int, c.c_int, fp,
                                     c.c_int64, ip, dp, fp]
         lib.oracle_topk.restype = None
@@ -82,6 +84,32 @@ def scores(rows, query, metric=COSINE, penalty=None) -> np.ndarray:
     _load().oracle_scores(_p(rows, ctypes.c_float), n, d, d, _p(query, ctypes.c_float), metric,
                           _p(pen, ctypes.c_float), _p(out, ctypes.c_double))
     return out
+
+
+def pgvector_f32_scores(rows, query, metric=COSINE, penalty=None) -> np.ndarray:
+    """Scores with pgvector's own arithmetic (float accumulators in index order, see oracle.c): the "exact fp32 brute-force
+    reference" north_star measures the 1e-5 score tolerance against.  Not the oracle."""
+    rows, query = _f32(rows), _f32(query)
+    n, d = rows.shape
+    pen = _f32(penalty) if penalty is not None else None
+    out = np.empty(n, np.float64)
+    _load().oracle_pgvector_f32_scores(_p(rows, ctypes.c_float), n, d, d, _p(query, ctypes.c_float), metric,
+                                       _p(pen, ctypes.c_float), _p(out, ctypes.c_double))
+    return out
+
+
+def agrees_with_fp32_reference(ids, scores64, ref_scores, k, rel=1e-5):
+    """True when a top-k answer (ids [k], fp64 scores [k]) is the answer of the fp32 brute-force reference up to its own
+    rounding: every returned score within ``rel`` of the reference's score of the same row, and every row the reference
+    ranks in its top k that is missing from ``ids`` (or the other way round) within ``rel`` of the reference's k-th score."""
+    ids = np.asarray(ids)
+    ok = ids >= 0
+    if not np.allclose(scores64[ok], ref_scores[ids[ok]], rtol=rel, atol=0):
+        return False
+    order = np.lexsort((np.arange(ref_scores.size), ref_scores))[:k]
+    kth = ref_scores[order[min(k, order.size) - 1]]
+    diff = np.setxor1d(ids[ok], order)
+    return bool(np.all(np.abs(ref_scores[diff] - kth) <= rel * max(abs(kth), 1e-30)))
 
 
 def topk(rows, queries, k, metric=COSINE, penalty=None, id_base=0, threads=None):

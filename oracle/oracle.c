@@ -71,6 +71,46 @@ static double distance_f64(const float *q, const float *e, int dim, int metric, 
     }
 }
 
+/*
+ * The same two operators with the arithmetic pgvector itself uses (third-party, absent from /root/reference, version unpinned;
+ * restated from its published src/vector.c as SURVEY.md section 8(c) records it): `float` accumulators walked in index
+ * order, the division / square root in double.
+ *   cosine_distance: float dot, norma, normb;  similarity = (double)dot / sqrt((double)norma * (double)normb), clamped to
+ *                    [-1, 1];  distance = 1.0 - similarity
+ *   l2_distance:     float distance += diff * diff;  sqrt((double)distance)
+ * pgvector is built with -ftree-vectorize -fassociative-math, so its own low-order bits depend on the build; this is ONE of
+ * the summation orders it can take.  It is not the oracle (the oracle is the fp64 form above, which every such order
+ * approximates): tests use it to check north_star's tolerance -- scores within 1e-5 relative of "an exact fp32 brute-force
+ * reference of pgvector's semantics", ids equal except between rows whose fp32 scores are that close.
+ */
+void oracle_pgvector_f32_scores(const float *rows, int64_t n_rows, int dim, int64_t ld, const float *query,
+                                int metric, const float *penalty, double *out) {
+    for (int64_t r = 0; r < n_rows; ++r) {
+        const float *e = rows + r * ld;
+        double d;
+        if (metric == ORACLE_COSINE) {
+            float dot = 0.0f, na = 0.0f, nb = 0.0f;
+            for (int i = 0; i < dim; ++i) {
+                dot += query[i] * e[i];
+                na += query[i] * query[i];
+                nb += e[i] * e[i];
+            }
+            double sim = (double)dot / sqrt((double)na * (double)nb);
+            if (sim > 1.0) sim = 1.0;
+            else if (sim < -1.0) sim = -1.0;
+            d = 1.0 - sim;
+        } else {
+            float acc = 0.0f;
+            for (int i = 0; i < dim; ++i) {
+                float diff = query[i] - e[i];
+                acc += diff * diff;
+            }
+            d = sqrt((double)acc);
+        }
+        out[r] = d + (penalty ? (double)penalty[r] : 0.0);
+    }
+}
+
 /* scores[n] = distance + (double)penalty (penalty may be NULL => 0). */
 void oracle_scores(const float *rows, int64_t n_rows, int dim, int64_t ld, const float *query,
                    int metric, const float *penalty, double *out_scores) {

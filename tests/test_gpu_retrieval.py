@@ -474,3 +474,20 @@ def test_foreign_memory_is_refused(mcp):
         got = idx.search_device(q, 3)[0]
         torch.cuda.synchronize()
         assert got.shape == (4, 3) and int(got.min()) >= 0
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+def test_gpu_answer_within_tolerance_of_pgvector_style_fp32(mcp, oracle, metric):
+    """The bar as north_star words it: against an exact fp32 brute-force reference of pgvector's semantics (pgvector's own float
+    accumulators, oracle.c), scores within 1e-5 relative and ids equal except between rows that reference cannot tell apart."""
+    rng = np.random.default_rng(610 + metric)
+    rows = rng.standard_normal((30_000, 1536), dtype=np.float32)
+    rows /= np.linalg.norm(rows, axis=1, keepdims=True)
+    qs = rng.standard_normal((16, 1536), dtype=np.float32)
+    pen = (rng.random(30_000) * 0.02).astype(np.float32)
+    with mcp.ServiceIndex(1536, "cosine" if metric == 0 else "l2") as idx:
+        idx.load(rows).set_penalty(pen)
+        ids, s32, s64 = idx.search(qs, 32)
+    for i in range(qs.shape[0]):
+        ref = oracle.pgvector_f32_scores(rows, qs[i], metric, pen)
+        assert oracle.agrees_with_fp32_reference(ids[i], s64[i], ref, 32), i

@@ -114,3 +114,26 @@ def test_numpy_baseline_agrees_on_separated_data(oracle):
     ids, _ = oracle.numpy_topk_baseline(c["rows"], inv, c["queries"], 5, 0, c["penalty"])
     gi, _, _ = oracle.topk(c["rows"], c["queries"], 5, 0, c["penalty"])
     assert (ids == gi).mean() > 0.9
+
+
+@pytest.mark.parametrize("metric", [0, 1])
+def test_oracle_within_tolerance_of_pgvector_style_fp32(oracle, metric):
+    """north_star's bar: scores within 1e-5 relative of an exact fp32 brute-force reference of pgvector's `<=>` / `<->`.  The
+    fp64 oracle is held against pgvector's own arithmetic (float accumulators, oracle.c): every score within 1e-5, and the
+    two top-k answers equal except between rows whose fp32 scores are that close."""
+    rng = np.random.default_rng(600 + metric)
+    rows = rng.standard_normal((4000, 1536), dtype=np.float32)
+    rows /= np.linalg.norm(rows, axis=1, keepdims=True)
+    rows[100] = rows[7]                                                   # an exact tie
+    qs = rng.standard_normal((6, 1536), dtype=np.float32)
+    pen = (rng.random(4000) * 0.02).astype(np.float32)
+    ids, s64, _ = oracle.topk(rows, qs, 32, metric, pen)
+    for i in range(qs.shape[0]):
+        ref = oracle.pgvector_f32_scores(rows, qs[i], metric, pen)
+        assert np.allclose(oracle.scores(rows, qs[i], metric, pen), ref, rtol=1e-5, atol=0)
+        assert oracle.agrees_with_fp32_reference(ids[i], s64[i], ref, 32)
+    # and the checker itself notices a wrong answer
+    bad = ids[0].copy()
+    bad[3] = (bad[3] + 1777) % 4000
+    ref0 = oracle.pgvector_f32_scores(rows, qs[0], metric, pen)
+    assert not oracle.agrees_with_fp32_reference(bad, s64[0], ref0, 32)
