@@ -48,7 +48,26 @@ for devs in ([0], list(range(ngpu))) if ngpu > 1 else ([0], [0, 0]):
         t0 = time.perf_counter()
         idx.search(qs[:1024], 64)
         t_b = min(t_b, time.perf_counter() - t0)
+        # the same through the reference-facing call: GraphPlanner.retrieve (hash embedding + search + name lookup)
+        from autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plane_b200 import control_plane as cp
+
+        class _Reg:
+            def list_services(self):
+                return []
+
+        planner = cp.GraphPlanner(_Reg(), top_k=a.k)
+        planner.attach_index(idx, [f"svc{i:07d}" for i in range(a.rows)])
+        intents = [f"intent number {i}: book, translate, summarise and notify" for i in range(a.requests)]
+        for t in intents[:50]:
+            planner.retrieve(t)
+        lat_p = []
+        for t in intents:
+            t0 = time.perf_counter()
+            planner.retrieve(t)
+            lat_p.append(time.perf_counter() - t0)
+        planner._index = None
         out[f"devices_{len(devs)}" + ("_same_gpu" if len(set(devs)) < len(devs) else "")] = {
+            "planner_retrieve_p50_ms": round(float(np.percentile(lat_p, 50)) * 1e3, 4), "planner_retrieve_p99_ms": round(float(np.percentile(lat_p, 99)) * 1e3, 4),
             "p50_ms": round(float(np.percentile(lat, 50)) * 1e3, 4), "p99_ms": round(float(np.percentile(lat, 99)) * 1e3, 4),
             "batch_1024_top64_ms": round(t_b * 1e3, 3), "load_s": round(t_load, 2), "first_ids": ids[0, :3].tolist()}
 print(json.dumps(out))
