@@ -468,7 +468,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         u64 b0 = ~0ull, b1 = ~0ull, b2 = ~0ull, b3 = ~0ull;
         // ... and, from then on, four small scores of rows this list has seen, ascending (floats; +inf = none).  They need not be
         // THE four smallest: the maximum of any four seen scores bounds the list's fourth-smallest from above, which is all the
-        // shared bound asks for.  So they are updated only where that is cheap (from tile 4 on, when survivors are rare).
+        // shared bound asks for.  Only the lists that publish (the first boot_lists, a warp-uniform property) keep them current.
         float f0 = CUDART_INF_F, f1 = CUDART_INF_F, f2 = CUDART_INF_F, f3 = CUDART_INF_F;
         u64 tp = 0;                                            // tau_pub word read one tile ago (epoch 0 never matches)
         const bool refresh = a.boot_m > 0 && a.boot_early && !(a.debug & 64);
@@ -646,7 +646,7 @@ gemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 // score all 32 first and only then look for survivors: once the shared bound has tightened, whole chunks pass
                 // without one, and the loop below (a branch, a store and the four-smallest insertion per element) is skipped
                 bool any = false;
-                const bool ins = refresh && i >= 4;
+                const bool ins = refresh && li < a.boot_lists;  // warp-uniform: only the lists that publish keep the set current
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
                     const float sc = score(__uint_as_float(v[j]), mbuf, cbase + c + j);
@@ -724,6 +724,8 @@ struct GemmPlan {
     bool allow_boot = true;    // option "gemm_bootstrap"
     bool l2_prefetch = false;  // option "gemm_l2_prefetch"
     int debug = 0;             // option "gemm_debug" (timing experiments, wrong results)
+    const u64 *last_tau_pub = nullptr;   // the last launch's shared-bound words (NULL when that launch did not refresh the bound)
+    uint32_t last_epoch = 0;
     char err[256] = {0};
 };
 
@@ -933,5 +935,9 @@ static int gemm_tf32_run(GemmPlan &p, BufT &ws, cudaStream_t st, int n_sm, int k
     }
     if (e != cudaSuccess) { snprintf(p.err, sizeof p.err, "gemm_tf32 launch (cluster %d, grid %d): %s", C, nqb * ngroups, cudaGetErrorString(e)); return -2; }
     *out_lists = a.lists; *out_cnt = a.list_cnt; *out_L = L; *out_cap = cap;
+    // the list selection that follows may drop keys above the final shared bound -- only when this launch kept one
+    const bool refreshed = a.boot_m > 0 && a.boot_early && !(p.debug & 64);
+    p.last_tau_pub = refreshed ? a.tau_pub : nullptr;
+    p.last_epoch = a.epoch;
     return 0;
 }

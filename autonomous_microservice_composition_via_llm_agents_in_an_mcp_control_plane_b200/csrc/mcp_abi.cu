@@ -755,7 +755,8 @@ static int run_scan_pass(mcp_index *idx, cudaStream_t st, const float *q, int di
 
 // reduce [nq][L][cap] lists until one list per query is left; returns the final buffers
 static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64 *in, int *in_cnt, int L, int cap,
-                        bool in_is_A, u64 **out_keys, int **out_cnt, int *out_stride, bool raw_in = false) {
+                        bool in_is_A, u64 **out_keys, int **out_cnt, int *out_stride, bool raw_in = false,
+                        const u64 *tau_pub = nullptr /* K2's final shared bound per query, or NULL */, uint32_t epoch = 0) {
     int rc;
     bool first = true;
     while (L > 1 || first) {
@@ -765,14 +766,15 @@ static int reduce_lists(mcp_index *idx, cudaStream_t st, int nq, int kprime, u64
         // Few queries, many lists (one query over 1 M rows leaves ~300 lists and ~15 K keys): one CTA per query would chew
         // through them 4096 keys at a time (55 us measured); groups of >= 16 lists go to CTAs of their own and a second round
         // reduces the group results, so that about as many CTAs as there are SMs work at once.
-        if (nq < idx->n_sm && L > 32) G = std::min(L, std::max(16, (int)((int64_t)L * nq / idx->n_sm + 1)));
+        // (With K2's final bound at hand the keys are filtered as they are gathered and one CTA per query is enough.)
+        if (!(raw_in && tau_pub) && nq < idx->n_sm && L > 32) G = std::min(L, std::max(16, (int)((int64_t)L * nq / idx->n_sm + 1)));
         int L_out = (L + G - 1) / G;
         Buf &ob = in_is_A ? idx->listsB : idx->listsA;
         Buf &oc = in_is_A ? idx->cntB : idx->cntA;
         if ((rc = ob.ensure(sizeof(u64) * (size_t)nq * L_out * kprime))) return rc;
         if ((rc = oc.ensure(sizeof(int) * (size_t)nq * L_out))) return rc;
         CU(launch_pdl(select_from_lists_kernel, dim3(L_out, nq), dim3(SEL_THREADS), 0, st, in, in_cnt, L, cap, G, kprime, ob.as<u64>(),
-                      oc.as<int>(), kprime, raw_in ? 1 : 0));
+                      oc.as<int>(), kprime, raw_in ? 1 : 0, raw_in ? tau_pub : (const u64 *)nullptr, epoch));
         KL();
         in = ob.as<u64>(); in_cnt = oc.as<int>(); L = L_out; cap = kprime; in_is_A = !in_is_A; raw_in = false;
     }
@@ -1017,7 +1019,8 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             if ((rc = coarse_event(idx, st))) return rc;
             // the GEMM's lists live in gemm_ws; reductions ping-pong between listsA / listsB
             // K2 lists are raw (fp32 bits, row) pairs: always pass them through one reduction, which builds the ordered keys
-            if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride, true)))
+            if ((rc = reduce_lists(idx, st, cq, kprime, lists, cnts, L, cap, false, &cand, &cand_cnt, &cand_stride, true,
+                                   idx->gemm.last_tau_pub, idx->gemm.last_epoch)))
                 return rc;
         }
         {

@@ -127,19 +127,29 @@ select_from_scores_kernel(const float *__restrict__ scores, int64_t score_stride
 // Lists are usually far from full, so one CTA normally takes all of a query's lists at once; when their keys do
 // not fit the SEL_MAX-key buffer they are consumed in chunks, the best kprime so far riding along.
 // raw_in: the lists hold raw (fp32 score bits, row) pairs as the GEMM epilogue appends them.
+// tau_pub (raw lists only): the scan's final shared bound per query, (launch epoch << 32 | float bits).  At least kprime keys
+// of the query's lists lie at or below it, so keys above it are dropped as they are gathered -- the lists were filled under
+// looser, earlier bounds and hold several times what the final bound admits (one query over 1 M rows: ~15 K keys in ~300
+// lists, ~1.5 K under the bound).  Survivors are compacted into the buffer, chunk after chunk, and selected once.
 __global__ void __launch_bounds__(SEL_THREADS)
 select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_cnt, int L_in,
                          int cap_in, int G, int kprime, u64 *__restrict__ out,
-                         int *__restrict__ out_cnt, int cap_out, int raw_in) {
+                         int *__restrict__ out_cnt, int cap_out, int raw_in,
+                         const u64 *__restrict__ tau_pub, uint32_t epoch) {
     __shared__ SelectSmem s;
     __shared__ int base[SEL_THREADS + 1];      // exclusive prefix of the list lengths
     __shared__ int wsum[SEL_THREADS / 32];
-    __shared__ int s_lend;
+    __shared__ int s_lend, s_fill;
     pdl_trigger();
     pdl_wait();                                                // the scan that wrote the lists has completed
     const int g = blockIdx.x, q = blockIdx.y, L_out = gridDim.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int l0 = g * G, nl = min(G, L_in - l0);
+    float tau = CUDART_INF_F;
+    if (tau_pub && raw_in) {
+        const u64 wv = tau_pub[q];
+        if ((uint32_t)(wv >> 32) == epoch) tau = __uint_as_float((uint32_t)wv);
+    }
     const int mycnt = (int)threadIdx.x < nl ? min(in_cnt[(int64_t)q * L_in + l0 + threadIdx.x], cap_in) : 0;
     int incl = mycnt;
 #pragma unroll
@@ -170,6 +180,7 @@ select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_
                 le = a;
             }
             s_lend = le;
+            s_fill = carry;
         }
         __syncthreads();
         const int le = s_lend, b0 = base[ls], m = base[le] - b0;
@@ -192,15 +203,28 @@ select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_
 #pragma unroll
             for (int u = 0; u < SEL_MAX / SEL_THREADS; ++u) x[u] = src[u] ? __ldg(src[u]) : 0ull;
 #pragma unroll
-            for (int u = 0; u < SEL_MAX / SEL_THREADS; ++u)
-                if (src[u]) {
-                    const u64 v = x[u];
-                    s.keys[carry + threadIdx.x + u * SEL_THREADS] =
-                        raw_in ? (((u64)f32_ord(__uint_as_float((uint32_t)(v >> 32))) << 32) | (v & 0xFFFFFFFFull)) : v;
-                }
+            for (int u = 0; u < SEL_MAX / SEL_THREADS; ++u) {
+                const u64 v = x[u];
+                if (raw_in) {
+                    // at or below the final bound, or NaN: compacted behind what is held (one shared-memory atomic per warp)
+                    const float sc = __uint_as_float((uint32_t)(v >> 32));
+                    const bool keep = src[u] != nullptr && !(sc > tau);
+                    const uint32_t bal = __ballot_sync(MCP_FULL, keep);
+                    int wbase = 0;
+                    if (lane == 0 && bal) wbase = atomicAdd(&s_fill, __popc(bal));
+                    wbase = __shfl_sync(MCP_FULL, wbase, 0);
+                    if (keep) s.keys[wbase + __popc(bal & ((1u << lane) - 1u))] = ((u64)f32_ord(sc) << 32) | (v & 0xFFFFFFFFull);
+                } else if (src[u])
+                    s.keys[carry + threadIdx.x + u * SEL_THREADS] = v;
+            }
         }
         __syncthreads();
-        const int n = carry + m;
+        const int n = raw_in ? s_fill : carry + m;
+        if (le < nl && n <= SEL_MAX / 2) {                     // room left: keep gathering, select once at the end
+            carry = n; ls = le;
+            __syncthreads();                                   // s_fill / s_lend are rewritten at the top
+            continue;
+        }
         cta_select_write(s, n, min(kprime, n), dst, out_cnt + lo);
         if (le >= nl) break;
         __syncthreads();
