@@ -393,7 +393,8 @@ exact_pick_kernel(const int *__restrict__ flag_list, const int *__restrict__ n_f
             status[2] = 0;
             __threadfence();
             status[0] += nf;
-            if (host_status) { host_status[0] = status[0]; host_status[1] = *(volatile int *)&status[1]; __threadfence_system(); }
+            // nothing flagged: the totals the host last saw still stand (the host zeroes its mirror and the device counters together)
+            if (host_status && nf > 0) { host_status[0] = status[0]; host_status[1] = *(volatile int *)&status[1]; __threadfence_system(); }
         }
     }
 }

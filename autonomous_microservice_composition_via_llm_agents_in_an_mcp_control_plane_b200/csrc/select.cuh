@@ -130,7 +130,7 @@ select_from_scores_kernel(const float *__restrict__ scores, int64_t score_stride
 // tau_pub (raw lists only): the scan's final shared bound per query, (launch epoch << 32 | float bits).  At least kprime keys
 // of the query's lists lie at or below it, so keys above it are dropped as they are gathered -- the lists were filled under
 // looser, earlier bounds and hold several times what the final bound admits (one query over 1 M rows: ~15 K keys in ~300
-// lists, ~1.5 K under the bound).  Survivors are compacted into the buffer, chunk after chunk, and selected once.
+// lists, a few thousand under the bound).  Survivors are compacted into the buffer, chunk after chunk, and selected once.
 __global__ void __launch_bounds__(SEL_THREADS)
 select_from_lists_kernel(const u64 *__restrict__ in, const int *__restrict__ in_cnt, int L_in,
                          int cap_in, int G, int kprime, u64 *__restrict__ out,
