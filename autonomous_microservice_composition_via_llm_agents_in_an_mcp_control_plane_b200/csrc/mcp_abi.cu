@@ -222,6 +222,7 @@ extern "C" int mcp_index_create(mcp_index **out, int device_id, int dim, int met
     idx->h_status[0] = idx->h_status[1] = 0;
     CU(cudaHostGetDevicePointer(&idx->h_status_dev, idx->h_status, 0));
     CU(cudaFuncSetAttribute(rescore_finalize_kernel<5, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_LIMIT));
+    CU(cudaFuncSetAttribute(rescore_finalize_kernel<3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RF_SMEM_LIMIT));
     CU(cudaFuncSetAttribute(exact_scan2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XS_SMEM_LIMIT));
     int rc = idx->consts.ensure(sizeof(TableConsts));
     if (!rc) rc = idx->flags.ensure(sizeof(int) * 4096);
@@ -1028,9 +1029,14 @@ static int search_locked(mcp_index *idx, const float *d_q, int nq, int k, int32_
             const int G = (std::min(cand_stride, kprime) + RS_ROWS - 1) / RS_ROWS;
             int GP = std::max(1, cq <= idx->n_sm ? std::min(G, RF_MAXG) : std::min(G, 2));   // few queries: one pass; many: more CTAs per SM
             const int npow2 = pow2_at_least(std::max(std::min(cand_stride, kprime), 2));
-            const int stages = 5;
+            int stages = 5;
+            // Many queries, three groups of candidates (k' = 96): two passes of two groups leave a half-empty second pass.  A
+            // shallower ring (3 stages) takes all three groups in one pass and still fits two CTAs per SM.
+            const bool shallow = cq > idx->n_sm && G == 3 && RF_SMEM_BYTES(dim, 3, 3, npow2) <= 112 * 1024 && !(idx->gemm.debug & 16384);
+            if (shallow) { GP = 3; stages = 3; }
             while (GP > 1 && RF_SMEM_BYTES(dim, GP, stages, npow2) > RF_SMEM_LIMIT) --GP;
-            CU(launch_pdl(rescore_finalize_kernel<5, 3>, dim3(cq), dim3(32 * (GP + RF_NPROD + 1)), RF_SMEM_BYTES(dim, GP, stages, npow2), st,
+            auto rf_kernel = shallow ? rescore_finalize_kernel<3, 2> : rescore_finalize_kernel<5, 3>;
+            CU(launch_pdl(rf_kernel, dim3(cq), dim3(32 * (GP + RF_NPROD + 1)), RF_SMEM_BYTES(dim, GP, stages, npow2), st,
                           idx->d_rows, dim, idx->ld, dq, idx->norm2.as<double>(), pen, idx->metric, cand, cand_cnt, cand_stride,
                           npow2, k, idx->id_base, idx->consts.as<TableConsts>(), cp,
                           idx->nq2.as<double>() + q0, idx->qflag.as<unsigned char>() + q0, out_ids + (int64_t)q0 * k,
