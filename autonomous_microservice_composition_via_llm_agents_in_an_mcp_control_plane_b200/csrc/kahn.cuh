@@ -29,23 +29,20 @@ struct KahnWarp {
     int fe_overflow;           // some node has more such parents than the table holds: this DAG rescans its edges per generation
 };
 
+// One DAG, one warp.
 template <bool WITH_ORDER>
-__global__ void __launch_bounds__(KAHN_THREADS)
-kahn_levels_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__restrict__ edge_off,
-                   const unsigned char *__restrict__ edges, int64_t n_dags,
-                   unsigned char *__restrict__ out_level, unsigned char *__restrict__ out_order,
-                   unsigned char *__restrict__ out_n_levels, unsigned char *__restrict__ out_status) {
-    __shared__ KahnWarp sw[KAHN_WARPS];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    KahnWarp &w = sw[warp];
-    const uchar2 *ed = reinterpret_cast<const uchar2 *>(edges);
-    for (int64_t b = (int64_t)blockIdx.x * KAHN_WARPS + warp; b < n_dags; b += (int64_t)gridDim.x * KAHN_WARPS) {
+__device__ __forceinline__ void kahn_warp_dag(KahnWarp &w, const int lane, const int64_t b,
+                                              const unsigned char *__restrict__ n_nodes, const uint32_t *__restrict__ edge_off,
+                                              const uchar2 *__restrict__ ed,
+                                              unsigned char *__restrict__ out_level, unsigned char *__restrict__ out_order,
+                                              unsigned char *__restrict__ out_n_levels, unsigned char *__restrict__ out_status) {
+    {
         const int n = n_nodes[b];
         if (n > 64) {                                    // not this kernel's DAG (kahn_levels_wide_kernel takes up to 255 nodes): say so
             out_level[b * 64 + lane] = 0xFF; out_level[b * 64 + 32 + lane] = 0xFF;
             if (WITH_ORDER) { out_order[b * 64 + lane] = 0xFF; out_order[b * 64 + 32 + lane] = 0xFF; }
             if (lane == 0) { out_n_levels[b] = 0; out_status[b] = 2; }
-            continue;
+            return;
         }
         const uint32_t e0 = edge_off[b], e1 = edge_off[b + 1];
         w.pred[lane] = 0; w.pred[lane + 32] = 0;
@@ -168,6 +165,311 @@ kahn_levels_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__
             out_order[b * 64 + 32 + lane] = w.order[lane + 32];
             __syncwarp();
         }
+    }
+}
+
+template <bool WITH_ORDER>
+__global__ void __launch_bounds__(KAHN_THREADS)
+kahn_levels_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__restrict__ edge_off,
+                   const unsigned char *__restrict__ edges, int64_t n_dags,
+                   unsigned char *__restrict__ out_level, unsigned char *__restrict__ out_order,
+                   unsigned char *__restrict__ out_n_levels, unsigned char *__restrict__ out_status) {
+    __shared__ KahnWarp sw[KAHN_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uchar2 *ed = reinterpret_cast<const uchar2 *>(edges);
+    for (int64_t b = (int64_t)blockIdx.x * KAHN_WARPS + warp; b < n_dags; b += (int64_t)gridDim.x * KAHN_WARPS)
+        kahn_warp_dag<WITH_ORDER>(sw[warp], lane, b, n_nodes, edge_off, ed, out_level, out_order, out_n_levels, out_status);
+}
+
+// The DAGs kahn_fifo_kernel (below) handed back (status KAHN_DEFERRED): found by reading the status bytes 32 at a time.
+#define KAHN_DEFERRED 3
+template <bool WITH_ORDER>
+__global__ void __launch_bounds__(KAHN_THREADS)
+kahn_levels_deferred_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__restrict__ edge_off,
+                            const unsigned char *__restrict__ edges, int64_t n_dags,
+                            unsigned char *__restrict__ out_level, unsigned char *__restrict__ out_order,
+                            unsigned char *__restrict__ out_n_levels, unsigned char *__restrict__ out_status) {
+    __shared__ KahnWarp sw[KAHN_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uchar2 *ed = reinterpret_cast<const uchar2 *>(edges);
+    const int64_t n_groups = (n_dags + 31) / 32;
+    for (int64_t g = (int64_t)blockIdx.x * KAHN_WARPS + warp; g < n_groups; g += (int64_t)gridDim.x * KAHN_WARPS) {
+        const int64_t b = g * 32 + lane;
+        unsigned m = __ballot_sync(MCP_FULL, b < n_dags && out_status[b] == KAHN_DEFERRED);
+        for (; m; m &= m - 1)
+            kahn_warp_dag<WITH_ORDER>(sw[warp], lane, g * 32 + (__ffs((int)m) - 1), n_nodes, edge_off, ed, out_level, out_order, out_n_levels, out_status);
+    }
+}
+
+
+// ---- large batches: one THREAD per DAG ---------------------------------------------------------------------------------
+// The warp kernel above spends ~2.6 K warp instructions per DAG on the order (profiles/r2e_summary.md): it is issue-bound,
+// and what it issues is mostly per-generation fixed cost.  For a batch large enough to fill the machine with threads the
+// literal algorithm is cheaper: each thread runs dag.py:218-240 on its own DAG -- bucket the edges by source in first-seen
+// order (DiGraph's adjacency order; a repeated edge is dropped there), count distinct parents, then a FIFO: the queue IS
+// topological_sort's order, and a node's level is its releasing parent's + 1.  About (4 E + 3 n) short steps per DAG.
+//   * a warp costs its longest lane, so a CTA takes C consecutive DAGs, counting-sorts them by edge count in shared
+//     memory and deals them out in groups of 32 neighbours of that order, heaviest group first; each warp pulls its next
+//     group from a CTA counter -- no barrier until the chunk is done;
+//   * per-thread state lives in shared memory, word-interleaved across the lanes of a warp (word j of lane t at [j][t]):
+//     every access, whatever the index, is bank-conflict free; the bucketed children of a group share the warp's byte
+//     pool, and a group whose edges exceed it runs in several passes over fewer lanes;
+//   * edges are read twice from global memory, eight at a time (one 16-byte load per lane); levels go straight to the
+//     output row (one byte per release: the thread wrote the row's 0xFF fill itself, so program order holds);
+//   * a DAG whose edge list alone exceeds the pool (only possible with repeated edges) is handed back with status
+//     KAHN_DEFERRED for kahn_levels_deferred_kernel.
+#define KF_THREADS 128
+#define KF_WARPS (KF_THREADS / 32)
+#define KF_POOL 8192
+#define KF_BINS 1024
+#define KF_MIN_DAGS 16384
+struct KfWarp {
+    uint32_t start[32][32];    // 64 x u16 per DAG: out-degree -> list begin -> list end
+    uint32_t indeg[16][32];    // 64 x u8: distinct parents not yet done
+    uint32_t order[16][32];    // 64 x u8: the queue
+    unsigned char pool[KF_POOL];
+};
+template <int C>
+struct KfSmem {
+    KfWarp w[KF_WARPS];
+    unsigned short perm[C];    // position in edge-count order -> DAG of the chunk
+    unsigned short ecnt[C];    // position -> edge count
+    uint32_t wsum[KF_WARPS];
+    int next_group;
+};
+static_assert(KF_BINS * sizeof(uint32_t) <= KF_POOL, "the sort's histogram borrows warp 0's pool");
+
+// Byte i / half-word i of a lane's column, given the column's base (&a[0][lane]): word i >> 2 (i >> 1) sits 128 bytes on.
+__device__ __forceinline__ unsigned char *kf_b(unsigned char *col, int i) { return col + (i & 0xFC) * 31 + i; }
+__device__ __forceinline__ unsigned short *kf_h(unsigned char *col, int i) {
+    return reinterpret_cast<unsigned short *>(col + (i & 0xFE) * 62 + 2 * i);
+}
+
+// f(u, v) for every edge of [e0, e1) with both ends below n.  `edges` is 16-byte aligned (the launcher checks).
+template <class F>
+__device__ __forceinline__ void kf_edges(const unsigned char *__restrict__ edges, uint32_t e0, uint32_t e1, int n, F f) {
+    const unsigned short *e16 = reinterpret_cast<const unsigned short *>(edges);
+    uint32_t e = e0;
+    const uint32_t head_end = min(e1, (e0 + 7u) & ~7u);
+    for (; e < head_end; ++e) {
+        const unsigned x = __ldg(e16 + e);
+        const int u = x & 0xFF, v = x >> 8;
+        if (u < n && v < n) f(u, v);
+    }
+    if (e + 8 <= e1) {
+        uint4 q = __ldg(reinterpret_cast<const uint4 *>(e16 + e));
+        for (;;) {
+            const uint32_t en = e + 8;
+            const bool more = en + 8 <= e1;
+            uint4 qn = q;
+            if (more) qn = __ldg(reinterpret_cast<const uint4 *>(e16 + en));
+            const uint32_t ws[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int u0 = ws[j] & 0xFF, v0 = (ws[j] >> 8) & 0xFF, u1 = (ws[j] >> 16) & 0xFF, v1 = ws[j] >> 24;
+                if (u0 < n && v0 < n) f(u0, v0);
+                if (u1 < n && v1 < n) f(u1, v1);
+            }
+            e = en;
+            if (!more) break;
+            q = qn;
+        }
+    }
+    for (; e < e1; ++e) {
+        const unsigned x = __ldg(e16 + e);
+        const int u = x & 0xFF, v = x >> 8;
+        if (u < n && v < n) f(u, v);
+    }
+}
+
+// One DAG, one thread (the lane's columns of w; its children at pl).  Returns the status; *nlev_out = generations found.
+// A pool byte is a child id (6 bits) | 0x40 on the first entry of a source's list | 0x80 on a repeat of an earlier entry.
+__device__ __forceinline__ int kf_one_dag(KfWarp &w, const int lane, unsigned char *pl, const unsigned char *__restrict__ edges,
+                                          const uint32_t e0, const uint32_t e1, const int n,
+                                          unsigned char *__restrict__ lvl_row, int *nlev_out) {
+    unsigned char *const cs = reinterpret_cast<unsigned char *>(&w.start[0][lane]);
+    unsigned char *const ci = reinterpret_cast<unsigned char *>(&w.indeg[0][lane]);
+    unsigned char *const co = reinterpret_cast<unsigned char *>(&w.order[0][lane]);
+    // 1: out-degree per source (repeats included)
+    kf_edges(edges, e0, e1, n, [&](int u, int) { ++*kf_h(cs, u); });
+    // list begins
+    uint32_t acc = 0;
+    for (int j = 0; 2 * j < n; ++j) {
+        const uint32_t c = w.start[j][lane];
+        const uint32_t c0 = c & 0xFFFFu, c1 = c >> 16;
+        w.start[j][lane] = acc | ((acc + c0) << 16);
+        acc += c0 + c1;
+    }
+    // 2: children bucketed by source, in edge order; start[u] ends as the END of u's list
+    kf_edges(edges, e0, e1, n, [&](int u, int v) {
+        unsigned short *p = kf_h(cs, u);
+        const uint32_t s = *p;
+        *p = (unsigned short)(s + 1);
+        pl[s] = (unsigned char)v;
+    });
+    // mark where each source's list begins
+    {
+        uint32_t beg = 0;
+        for (int j = 0; 2 * j < n; ++j) {
+            const uint32_t c = w.start[j][lane];
+            const uint32_t x0 = c & 0xFFFFu, x1 = c >> 16;
+            if (x0 > beg) pl[beg] |= 0x40;
+            if (x1 > x0) pl[x0] |= 0x40;
+            beg = x1;
+        }
+    }
+    // 3: one pass over the bucketed children: flag repeats within a list, count distinct parents
+    {
+        u64 seen = 0;
+        for (uint32_t r = 0; r < acc; ++r) {
+            const uint32_t c = pl[r];
+            if (c & 0x40) seen = 0;
+            const int v = c & 0x3F;
+            const u64 bit = 1ull << v;
+            if (seen & bit) pl[r] = (unsigned char)(c | 0x80);
+            else ++*kf_b(ci, v);
+            seen |= bit;
+        }
+    }
+    // 4: the queue.  Generation g + 1 starts where the queue's tail stood when the first node of generation g was taken.
+    int tail = 0;
+    for (int v = 0; v < n; ++v)
+        if (*kf_b(ci, v) == 0) { *kf_b(co, tail++) = (unsigned char)v; lvl_row[v] = 0; }
+    int head = 0, lu = 0, bound = tail, nlev = 0;
+    uint32_t r = 0, rend = 0;
+    for (;;) {
+        if (r == rend) {                                   // take the next node off the queue
+            if (head == tail) break;
+            if (head == bound) { ++lu; bound = tail; }
+            const int u = *kf_b(co, head++);
+            nlev = lu + 1;
+            r = u ? *kf_h(cs, u - 1) : 0u;
+            rend = *kf_h(cs, u);
+        }
+        if (r < rend) {                                    // one child of the node in hand
+            const uint32_t c = pl[r++];
+            if (!(c & 0x80)) {
+                const int v = c & 0x3F;
+                unsigned char *pd = kf_b(ci, v);
+                const int d = *pd - 1;
+                *pd = (unsigned char)d;
+                if (d == 0) { *kf_b(co, tail++) = (unsigned char)v; lvl_row[v] = (unsigned char)(lu + 1); }
+            }
+        }
+    }
+    *nlev_out = nlev;
+    return tail != n;
+}
+
+template <bool WITH_ORDER, int C>
+__global__ void __launch_bounds__(KF_THREADS)
+kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__restrict__ edge_off,
+                 const unsigned char *__restrict__ edges, int64_t n_dags,
+                 unsigned char *__restrict__ out_level, unsigned char *__restrict__ out_order,
+                 unsigned char *__restrict__ out_n_levels, unsigned char *__restrict__ out_status) {
+    extern __shared__ __align__(16) unsigned char kf_raw[];
+    KfSmem<C> &S = *reinterpret_cast<KfSmem<C> *>(kf_raw);
+    constexpr int PER = C / KF_THREADS, GROUPS = C / 32;
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    KfWarp &w = S.w[warp];
+    uint32_t *hist = reinterpret_cast<uint32_t *>(S.w[0].pool);
+    const int64_t b0 = (int64_t)blockIdx.x * C;
+
+    // ---- counting sort of the chunk's DAGs by the work they are (clipped at KF_BINS - 1; those DAGs are neighbours anyway) ----
+#pragma unroll
+    for (int j = 0; j < KF_BINS / KF_THREADS; ++j) hist[t + j * KF_THREADS] = 0;
+    __syncthreads();
+    uint32_t ec[PER], key[PER], within[PER];
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+        const int64_t b = b0 + t + j * KF_THREADS;
+        uint32_t E = 0, nn = 0;
+        if (b < n_dags) {
+            const uint32_t a0 = edge_off[b], a1 = edge_off[b + 1];
+            E = a1 < a0 ? 0xFFFFu : min(a1 - a0, 0xFFFFu);
+            nn = n_nodes[b];
+        }
+        ec[j] = E;
+        key[j] = min((4u * E + 3u * nn) >> 1, (uint32_t)KF_BINS - 1u);      // ~ the steps the DAG will take
+        within[j] = atomicAdd(&hist[key[j]], 1u);
+    }
+    __syncthreads();
+    {
+        constexpr int BPT = KF_BINS / KF_THREADS;
+        uint32_t h[BPT], sum = 0;
+#pragma unroll
+        for (int j = 0; j < BPT; ++j) { h[j] = hist[t * BPT + j]; sum += h[j]; }
+        uint32_t inc = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t x = __shfl_up_sync(MCP_FULL, inc, d); if (lane >= d) inc += x; }
+        if (lane == 31) S.wsum[warp] = inc;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < KF_WARPS; ++j) inc += j < warp ? S.wsum[j] : 0u;
+        uint32_t run = inc - sum;
+#pragma unroll
+        for (int j = 0; j < BPT; ++j) { hist[t * BPT + j] = run; run += h[j]; }
+    }
+    if (t == 0) S.next_group = 0;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < PER; ++j) {
+        const uint32_t pos = hist[key[j]] + within[j];
+        S.perm[pos] = (unsigned short)(t + j * KF_THREADS);
+        S.ecnt[pos] = (unsigned short)ec[j];
+    }
+    __syncthreads();                                       // the histogram is done with: warp 0's pool is a pool again
+
+    // ---- groups of 32 neighbours, heaviest first ----
+    for (;;) {
+        int g = 0;
+        if (lane == 0) g = atomicAdd(&S.next_group, 1);
+        g = __shfl_sync(MCP_FULL, g, 0);
+        if (g >= GROUPS) break;
+        const int pos = (GROUPS - 1 - g) * 32 + lane;
+        const int64_t b = b0 + S.perm[pos];
+        const uint32_t E16 = S.ecnt[pos];
+        const bool valid = b < n_dags;
+        int n = valid ? n_nodes[b] : 0;
+        const bool wide = n > 64, over = !wide && E16 > KF_POOL;
+        const bool run = valid && !wide && !over;
+        const uint32_t e0 = run ? edge_off[b] : 0u;
+        const uint32_t E = run ? E16 : 0u;
+        if (!run) n = 0;
+        uint32_t inc = E;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t x = __shfl_up_sync(MCP_FULL, inc, d); if (lane >= d) inc += x; }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { w.indeg[j][lane] = 0; w.order[j][lane] = 0xFFFFFFFFu; }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) w.start[j][lane] = 0;
+        unsigned char *lvl_row = out_level + b * 64;
+        if (valid) {
+            uint4 *ol = reinterpret_cast<uint4 *>(lvl_row);
+            const uint4 ff = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) ol[i] = ff;
+        }
+        int nlev = 0, status = wide ? 2 : (over ? KAHN_DEFERRED : 0);
+        int first = 0;
+        while (first < 32) {                               // one pass unless the group's edges exceed the pool
+            const uint32_t pbase = __shfl_sync(MCP_FULL, inc - E, first);
+            const bool fit = lane >= first && inc - pbase <= KF_POOL;
+            if (run && fit) status = kf_one_dag(w, lane, w.pool + (inc - E - pbase), edges, e0, e0 + E, n, lvl_row, &nlev);
+            __syncwarp();
+            first += __popc(__ballot_sync(MCP_FULL, fit));
+        }
+        if (valid) {
+            if (WITH_ORDER) {
+                uint4 *oo = reinterpret_cast<uint4 *>(out_order + b * 64);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    oo[i] = make_uint4(w.order[4 * i][lane], w.order[4 * i + 1][lane], w.order[4 * i + 2][lane], w.order[4 * i + 3][lane]);
+            }
+            out_n_levels[b] = (unsigned char)nlev;
+            out_status[b] = (unsigned char)status;
+        }
+        __syncwarp();
     }
 }
 

@@ -17,6 +17,7 @@
 #include <stdarg.h>
 #include <unistd.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -1331,7 +1332,44 @@ static int dag_launch(int pitch, const uint8_t *n_nodes, const uint32_t *edge_of
     int dev = 0, n_sm = 148;
     CU(cudaGetDevice(&dev));
     CU(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-    if (pitch == 64) {
+    // Batches from KF_MIN_DAGS up go to the thread-per-DAG kernel (and whatever it hands back to the warp kernel); below that
+    // there are not enough DAGs to fill the machine with threads.  MCP_DAG_KERNEL = warp | fifo | fifo256 | fifo1024
+    // overrides the choice and the chunk a CTA sorts (measurement only).
+    const char *env = getenv("MCP_DAG_KERNEL");
+    const int dag_choice = !env ? 0 : !strcmp(env, "warp") ? 1 : !strcmp(env, "fifo") ? 2 : !strcmp(env, "fifo256") ? 3 : !strcmp(env, "fifo1024") ? 4 : 0;
+    const bool aligned16 = !((((uintptr_t)edges) | ((uintptr_t)out_level) | ((uintptr_t)out_order)) & 15);
+    if (pitch == 64 && aligned16 && dag_choice != 1 && (dag_choice >= 2 || (out_order && n_dags >= KF_MIN_DAGS))) {
+        typedef void (*kf_fn)(const unsigned char *, const uint32_t *, const unsigned char *, int64_t, unsigned char *, unsigned char *,
+                              unsigned char *, unsigned char *);
+        static const kf_fn fns[3][2] = {{kahn_fifo_kernel<false, 512>, kahn_fifo_kernel<true, 512>},
+                                        {kahn_fifo_kernel<false, 256>, kahn_fifo_kernel<true, 256>},
+                                        {kahn_fifo_kernel<false, 1024>, kahn_fifo_kernel<true, 1024>}};
+        static const int chunk_of[3] = {512, 256, 1024};
+        static const int smem_of[3] = {(int)sizeof(KfSmem<512>), (int)sizeof(KfSmem<256>), (int)sizeof(KfSmem<1024>)};
+        static std::mutex attr_mu;
+        static bool attr_set[NOALLOC_MAX_DEVICES_] = {};
+        {
+            std::lock_guard<std::mutex> lk(attr_mu);
+            if (dev >= 0 && dev < NOALLOC_MAX_DEVICES_ && !attr_set[dev]) {
+                for (int v = 0; v < 3; ++v)
+                    for (int o = 0; o < 2; ++o) {
+                        CU(cudaFuncSetAttribute((const void *)fns[v][o], cudaFuncAttributeMaxDynamicSharedMemorySize, smem_of[v]));
+                        CU(cudaFuncSetAttribute((const void *)fns[v][o], cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+                    }
+                attr_set[dev] = true;
+            }
+        }
+        const int v = dag_choice == 3 ? 1 : dag_choice == 4 ? 2 : 0;
+        const int64_t chunks = (n_dags + chunk_of[v] - 1) / chunk_of[v];
+        if (chunks > 0x7FFFFFFF) return fail(MCP_EINVAL, "n_dags too large");
+        fns[v][out_order ? 1 : 0]<<<(int)chunks, KF_THREADS, smem_of[v], st>>>(n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
+        KCHECK();
+        const int g2 = (int)std::min<int64_t>((int64_t)n_sm * 2, ((n_dags + 31) / 32 + KAHN_WARPS - 1) / KAHN_WARPS);
+        if (out_order)
+            kahn_levels_deferred_kernel<true><<<g2, KAHN_THREADS, 0, st>>>(n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
+        else
+            kahn_levels_deferred_kernel<false><<<g2, KAHN_THREADS, 0, st>>>(n_nodes, edge_off, edges, n_dags, out_level, nullptr, out_n_levels, out_status);
+    } else if (pitch == 64) {
         int64_t want = (n_dags + KAHN_WARPS - 1) / KAHN_WARPS;
         int grid = (int)std::min<int64_t>((int64_t)n_sm * 8, want);
         if (out_order)
