@@ -222,22 +222,23 @@ kahn_levels_deferred_kernel(const unsigned char *__restrict__ n_nodes, const uin
 #define KF_WARPS (KF_THREADS / 32)
 #define KF_POOL 8192
 #define KF_BINS 1024
-#define KF_MIN_DAGS 16384
+#define KF_MAXC 1024          // DAGs a CTA sorts at a time, at most
+#define KF_MIN_DAGS 262144    // below this the warp kernel wins: one thread walks its heaviest DAG for ~0.3 ms whatever the batch
 struct KfWarp {
     uint32_t start[32][32];    // 64 x u16 per DAG: out-degree -> list begin -> list end
     uint32_t indeg[16][32];    // 64 x u8: distinct parents not yet done
     uint32_t order[16][32];    // 64 x u8: the queue
-    unsigned char pool[KF_POOL];
+    unsigned char pool[KF_POOL + 4];   // + 4: the queue reads one entry ahead
 };
-template <int C>
 struct KfSmem {
     KfWarp w[KF_WARPS];
-    unsigned short perm[C];    // position in edge-count order -> DAG of the chunk
-    unsigned short ecnt[C];    // position -> edge count
+    unsigned short perm[KF_MAXC];   // position in the sorted order -> DAG of the chunk
+    unsigned short ecnt[KF_MAXC];   // position -> edge count
     uint32_t wsum[KF_WARPS];
     int next_group;
 };
 static_assert(KF_BINS * sizeof(uint32_t) <= KF_POOL, "the sort's histogram borrows warp 0's pool");
+static_assert(KF_MAXC % KF_THREADS == 0 && KF_MAXC <= 65535, "perm is 16-bit; each thread sorts KF_MAXC / KF_THREADS entries");
 
 // Byte i / half-word i of a lane's column, given the column's base (&a[0][lane]): word i >> 2 (i >> 1) sits 128 bytes on.
 __device__ __forceinline__ unsigned char *kf_b(unsigned char *col, int i) { return col + (i & 0xFC) * 31 + i; }
@@ -333,10 +334,16 @@ __device__ __forceinline__ int kf_one_dag(KfWarp &w, const int lane, unsigned ch
     }
     // 4: the queue.  Generation g + 1 starts where the queue's tail stood when the first node of generation g was taken.
     int tail = 0;
-    for (int v = 0; v < n; ++v)
-        if (*kf_b(ci, v) == 0) { *kf_b(co, tail++) = (unsigned char)v; lvl_row[v] = 0; }
+    for (int j = 0; 4 * j < n; ++j) {
+        const uint32_t wd = w.indeg[j][lane];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int v = 4 * j + k;
+            if (v < n && ((wd >> (8 * k)) & 0xFFu) == 0) { *kf_b(co, tail++) = (unsigned char)v; lvl_row[v] = 0; }
+        }
+    }
     int head = 0, lu = 0, bound = tail, nlev = 0;
-    uint32_t r = 0, rend = 0;
+    uint32_t r = 0, rend = 0, cur = 0;
     for (;;) {
         if (r == rend) {                                   // take the next node off the queue
             if (head == tail) break;
@@ -345,10 +352,12 @@ __device__ __forceinline__ int kf_one_dag(KfWarp &w, const int lane, unsigned ch
             nlev = lu + 1;
             r = u ? *kf_h(cs, u - 1) : 0u;
             rend = *kf_h(cs, u);
+            cur = pl[r];
         }
-        if (r < rend) {                                    // one child of the node in hand
-            const uint32_t c = pl[r++];
-            if (!(c & 0x80)) {
+        if (r < rend) {                                    // one child of the node in hand (the next one is already on its way)
+            const uint32_t c = cur;
+            cur = pl[++r];
+            if (!(c & 0x80u)) {
                 const int v = c & 0x3F;
                 unsigned char *pd = kf_b(ci, v);
                 const int d = *pd - 1;
@@ -361,19 +370,23 @@ __device__ __forceinline__ int kf_one_dag(KfWarp &w, const int lane, unsigned ch
     return tail != n;
 }
 
-template <bool WITH_ORDER, int C>
+// CTA i owns DAGs [i * per_cta, (i + 1) * per_cta) and takes them `sub` at a time (sub % 32 == 0, sub <= KF_MAXC): the launcher
+// splits the batch evenly over a grid that is resident at once, so no CTA is left with a chunk more than its neighbours.
+template <bool WITH_ORDER>
 __global__ void __launch_bounds__(KF_THREADS)
 kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__restrict__ edge_off,
-                 const unsigned char *__restrict__ edges, int64_t n_dags,
+                 const unsigned char *__restrict__ edges, int64_t n_dags, int64_t per_cta, int sub,
                  unsigned char *__restrict__ out_level, unsigned char *__restrict__ out_order,
                  unsigned char *__restrict__ out_n_levels, unsigned char *__restrict__ out_status) {
     extern __shared__ __align__(16) unsigned char kf_raw[];
-    KfSmem<C> &S = *reinterpret_cast<KfSmem<C> *>(kf_raw);
-    constexpr int PER = C / KF_THREADS, GROUPS = C / 32;
+    KfSmem &S = *reinterpret_cast<KfSmem *>(kf_raw);
+    constexpr int PER = KF_MAXC / KF_THREADS;
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     KfWarp &w = S.w[warp];
     uint32_t *hist = reinterpret_cast<uint32_t *>(S.w[0].pool);
-    const int64_t b0 = (int64_t)blockIdx.x * C;
+    const int64_t b_end = min(n_dags, ((int64_t)blockIdx.x + 1) * per_cta);
+  for (int64_t b0 = (int64_t)blockIdx.x * per_cta; b0 < b_end; b0 += sub) {
+    const int cs = (int)min((int64_t)sub, b_end - b0), GROUPS = (cs + 31) >> 5, padded = GROUPS * 32;
 
     // ---- counting sort of the chunk's DAGs by the work they are (clipped at KF_BINS - 1; those DAGs are neighbours anyway) ----
 #pragma unroll
@@ -382,16 +395,17 @@ kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__re
     uint32_t ec[PER], key[PER], within[PER];
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
-        const int64_t b = b0 + t + j * KF_THREADS;
+        const int i = t + j * KF_THREADS;
         uint32_t E = 0, nn = 0;
-        if (b < n_dags) {
-            const uint32_t a0 = edge_off[b], a1 = edge_off[b + 1];
+        if (i < cs) {
+            const uint32_t a0 = edge_off[b0 + i], a1 = edge_off[b0 + i + 1];
             E = a1 < a0 ? 0xFFFFu : min(a1 - a0, 0xFFFFu);
-            nn = n_nodes[b];
+            nn = n_nodes[b0 + i];
         }
         ec[j] = E;
         key[j] = min((4u * E + 3u * nn) >> 1, (uint32_t)KF_BINS - 1u);      // ~ the steps the DAG will take
-        within[j] = atomicAdd(&hist[key[j]], 1u);
+        within[j] = 0;
+        if (i < padded) within[j] = atomicAdd(&hist[key[j]], 1u);
     }
     __syncthreads();
     {
@@ -414,9 +428,12 @@ kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__re
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
-        const uint32_t pos = hist[key[j]] + within[j];
-        S.perm[pos] = (unsigned short)(t + j * KF_THREADS);
-        S.ecnt[pos] = (unsigned short)ec[j];
+        const int i = t + j * KF_THREADS;
+        if (i < padded) {
+            const uint32_t pos = hist[key[j]] + within[j];
+            S.perm[pos] = (unsigned short)i;
+            S.ecnt[pos] = (unsigned short)ec[j];
+        }
     }
     __syncthreads();                                       // the histogram is done with: warp 0's pool is a pool again
 
@@ -427,9 +444,10 @@ kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__re
         g = __shfl_sync(MCP_FULL, g, 0);
         if (g >= GROUPS) break;
         const int pos = (GROUPS - 1 - g) * 32 + lane;
-        const int64_t b = b0 + S.perm[pos];
+        const int mine = S.perm[pos];
+        const int64_t b = b0 + mine;
         const uint32_t E16 = S.ecnt[pos];
-        const bool valid = b < n_dags;
+        const bool valid = mine < cs;
         int n = valid ? n_nodes[b] : 0;
         const bool wide = n > 64, over = !wide && E16 > KF_POOL;
         const bool run = valid && !wide && !over;
@@ -471,6 +489,8 @@ kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__re
         }
         __syncwarp();
     }
+    __syncthreads();                                       // the next chunk's sort reuses the arrays
+  }
 }
 
 

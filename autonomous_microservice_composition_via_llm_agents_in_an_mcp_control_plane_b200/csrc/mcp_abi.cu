@@ -1333,36 +1333,40 @@ static int dag_launch(int pitch, const uint8_t *n_nodes, const uint32_t *edge_of
     CU(cudaGetDevice(&dev));
     CU(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
     // Batches from KF_MIN_DAGS up go to the thread-per-DAG kernel (and whatever it hands back to the warp kernel); below that
-    // there are not enough DAGs to fill the machine with threads.  MCP_DAG_KERNEL = warp | fifo | fifo256 | fifo1024
-    // overrides the choice and the chunk a CTA sorts (measurement only).
+    // there are not enough DAGs to fill the machine with threads.  MCP_DAG_KERNEL = warp | fifo overrides the choice, and
+    // MCP_DAG_SUB the number of DAGs a CTA sorts at a time (measurement only).
     const char *env = getenv("MCP_DAG_KERNEL");
-    const int dag_choice = !env ? 0 : !strcmp(env, "warp") ? 1 : !strcmp(env, "fifo") ? 2 : !strcmp(env, "fifo256") ? 3 : !strcmp(env, "fifo1024") ? 4 : 0;
+    const int dag_choice = !env ? 0 : !strcmp(env, "warp") ? 1 : !strcmp(env, "fifo") ? 2 : 0;
     const bool aligned16 = !((((uintptr_t)edges) | ((uintptr_t)out_level) | ((uintptr_t)out_order)) & 15);
-    if (pitch == 64 && aligned16 && dag_choice != 1 && (dag_choice >= 2 || (out_order && n_dags >= KF_MIN_DAGS))) {
-        typedef void (*kf_fn)(const unsigned char *, const uint32_t *, const unsigned char *, int64_t, unsigned char *, unsigned char *,
-                              unsigned char *, unsigned char *);
-        static const kf_fn fns[3][2] = {{kahn_fifo_kernel<false, 512>, kahn_fifo_kernel<true, 512>},
-                                        {kahn_fifo_kernel<false, 256>, kahn_fifo_kernel<true, 256>},
-                                        {kahn_fifo_kernel<false, 1024>, kahn_fifo_kernel<true, 1024>}};
-        static const int chunk_of[3] = {512, 256, 1024};
-        static const int smem_of[3] = {(int)sizeof(KfSmem<512>), (int)sizeof(KfSmem<256>), (int)sizeof(KfSmem<1024>)};
+    if (pitch == 64 && aligned16 && dag_choice != 1 && (dag_choice == 2 || (out_order && n_dags >= KF_MIN_DAGS))) {
         static std::mutex attr_mu;
-        static bool attr_set[NOALLOC_MAX_DEVICES_] = {};
+        static int ctas_per_sm[NOALLOC_MAX_DEVICES_] = {};
+        const int smem = (int)sizeof(KfSmem);
+        if (dev < 0 || dev >= NOALLOC_MAX_DEVICES_) return fail(MCP_EINVAL, "device %d out of range", dev);
         {
             std::lock_guard<std::mutex> lk(attr_mu);
-            if (dev >= 0 && dev < NOALLOC_MAX_DEVICES_ && !attr_set[dev]) {
-                for (int v = 0; v < 3; ++v)
-                    for (int o = 0; o < 2; ++o) {
-                        CU(cudaFuncSetAttribute((const void *)fns[v][o], cudaFuncAttributeMaxDynamicSharedMemorySize, smem_of[v]));
-                        CU(cudaFuncSetAttribute((const void *)fns[v][o], cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-                    }
-                attr_set[dev] = true;
+            if (!ctas_per_sm[dev]) {
+                CU(cudaFuncSetAttribute(kahn_fifo_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                CU(cudaFuncSetAttribute(kahn_fifo_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+                CU(cudaFuncSetAttribute(kahn_fifo_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+                CU(cudaFuncSetAttribute(kahn_fifo_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+                int occ = 0;
+                CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kahn_fifo_kernel<true>, KF_THREADS, smem));
+                ctas_per_sm[dev] = std::max(1, occ);
             }
         }
-        const int v = dag_choice == 3 ? 1 : dag_choice == 4 ? 2 : 0;
-        const int64_t chunks = (n_dags + chunk_of[v] - 1) / chunk_of[v];
-        if (chunks > 0x7FFFFFFF) return fail(MCP_EINVAL, "n_dags too large");
-        fns[v][out_order ? 1 : 0]<<<(int)chunks, KF_THREADS, smem_of[v], st>>>(n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
+        // every CTA resident at once, each with an equal share of the batch, taken in equal pieces of at most KF_MAXC
+        const int64_t slots = (int64_t)n_sm * ctas_per_sm[dev];
+        const int grid = (int)std::min<int64_t>(slots, (n_dags + 31) / 32);
+        const int64_t per_cta = (n_dags + grid - 1) / grid;
+        int64_t max_sub = KF_MAXC;
+        if (const char *e2 = getenv("MCP_DAG_SUB")) max_sub = std::min<int64_t>(KF_MAXC, std::max<int64_t>(32, atoi(e2)));
+        const int64_t pieces = (per_cta + max_sub - 1) / max_sub;
+        const int sub = (int)((((per_cta + pieces - 1) / pieces) + 31) & ~(int64_t)31);
+        if (out_order)
+            kahn_fifo_kernel<true><<<grid, KF_THREADS, smem, st>>>(n_nodes, edge_off, edges, n_dags, per_cta, sub, out_level, out_order, out_n_levels, out_status);
+        else
+            kahn_fifo_kernel<false><<<grid, KF_THREADS, smem, st>>>(n_nodes, edge_off, edges, n_dags, per_cta, sub, out_level, nullptr, out_n_levels, out_status);
         KCHECK();
         const int g2 = (int)std::min<int64_t>((int64_t)n_sm * 2, ((n_dags + 31) / 32 + KAHN_WARPS - 1) / KAHN_WARPS);
         if (out_order)

@@ -61,6 +61,69 @@ def test_synthetic_100k_bit_exact(mcp, oracle):
     assert 500 < status.sum() < 1500                                                      # about 1 % cyclic
 
 
+def _with_repeats_and_noise(enc, seed=3):
+    """Every third DAG gets half of its edges again (shuffled in), some get a self loop or edges naming nodes that do not
+    exist, the three with the most edges get their edge lists over and over (more edges than the thread-per-DAG kernel's pool
+    holds: it hands those DAGs back)."""
+    rng = np.random.default_rng(seed)
+    parts, off = [], [0]
+    big = set(np.argsort(np.diff(enc.edge_off.astype(np.int64)))[-3:].tolist())
+    for i in range(len(enc.n_nodes)):
+        e = enc.edges[enc.edge_off[i]:enc.edge_off[i + 1]]
+        if i % 3 == 0 and len(e):
+            e = np.concatenate([e, e[rng.permutation(len(e))[:max(1, len(e) // 2)]]])
+            e = e[rng.permutation(len(e))]
+        if i % 50 == 0:
+            e = np.concatenate([e, np.array([[0, 0]], np.uint8)])
+        if i % 70 == 0:
+            e = np.concatenate([e, np.array([[200, 1], [1, 99]], np.uint8)])
+        if i in big:
+            e = np.concatenate([e] * (8192 // len(e) + 2))
+        parts.append(e)
+        off.append(off[-1] + len(e))
+    return np.concatenate(parts), np.asarray(off, np.uint32)
+
+
+@pytest.mark.parametrize("kernel", ["warp", "fifo"])
+def test_both_kernels_on_repeated_edges_self_loops_and_handed_back_dags(mcp, oracle, monkeypatch, kernel):
+    """The thread-per-DAG kernel (large batches; forced here) and the warp kernel give the oracle's bytes on data with
+    repeated edges, self loops, out-of-range edges, DAGs it hands back (edge list beyond its pool) and groups that need
+    several passes over the pool; then the golden file and the oversized-DAG status through the same kernel."""
+    import torch
+
+    monkeypatch.setenv("MCP_DAG_KERNEL", kernel)
+    base = mcp.dag.synthetic_dags(20_000, seed=77)
+    edges, off = _with_repeats_and_noise(base)
+    assert (np.diff(off.astype(np.int64)) > 8192).sum() >= 1
+    enc = mcp.dag.EncodedDags(base.n_nodes, off, edges, [])
+    level, order, nlev, status = oracle.dag_levels(enc.n_nodes, enc.edge_off, enc.edges)
+    _same(mcp.dag.levels(enc), level, order, nlev, status)
+    res = mcp.dag.levels(enc, with_order=False)
+    assert np.array_equal(res.level, level) and np.array_equal(res.status, status)
+    g = np.load(GOLD / "dag_golden.npz")
+    _same(mcp.dag.levels(mcp.dag.EncodedDags(g["n_nodes"], g["edge_off"], g["edges"], [])), g["level"], g["order"], g["n_levels"], g["status"])
+    dev = torch.device("cuda:0")
+    nn = torch.tensor([3, 200, 2], dtype=torch.uint8, device=dev)
+    o3 = torch.tensor([0, 2, 2, 3], dtype=torch.int32, device=dev)
+    ed = torch.tensor([[0, 1], [1, 2], [0, 1]], dtype=torch.uint8, device=dev)
+    lv, od, nl, st = mcp.dag.levels_device(nn, o3, ed)
+    torch.cuda.synchronize()
+    assert st.cpu().tolist() == [0, 2, 0] and nl.cpu().tolist() == [3, 0, 2]
+    assert (lv[1] == 0xFF).all() and (od[1] == 0xFF).all() and od[0, :3].cpu().tolist() == [0, 1, 2]
+
+
+def test_large_batch_takes_the_thread_per_dag_kernel_and_stays_bit_exact(mcp, oracle, monkeypatch):
+    """300 K DAGs is past the library's own switch to the thread-per-DAG kernel (no override): same bytes as the oracle,
+    and the same bytes as the warp kernel."""
+    monkeypatch.delenv("MCP_DAG_KERNEL", raising=False)
+    enc = mcp.dag.synthetic_dags(300_000, seed=31)
+    level, order, nlev, status = oracle.dag_levels(enc.n_nodes, enc.edge_off, enc.edges)
+    res = mcp.dag.levels(enc)
+    _same(res, level, order, nlev, status)
+    monkeypatch.setenv("MCP_DAG_KERNEL", "warp")
+    _same(mcp.dag.levels(enc), level, order, nlev, status)
+
+
 def test_device_api_and_invariants(mcp):
     """device-pointer entry point; and the size-independent property: for every edge (u,v) of an
     acyclic DAG level[u] < level[v], and every non-root has a parent exactly one level up."""
