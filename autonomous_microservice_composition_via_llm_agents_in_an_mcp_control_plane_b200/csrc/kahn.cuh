@@ -12,6 +12,8 @@
 //           the first edge parent->node), which is the order dag.py:224-234 appends them in.
 // HBM traffic per DAG: 1 + 8 + 2E bytes in, 64 (+64) + 2 bytes out; everything else is
 // shared memory and registers.
+// Three kernels, identical bytes out: kahn_levels_kernel (a warp per DAG, any batch), kahn_fifo_kernel
+// (a thread per DAG, large batches with the order; further down) and kahn_levels_wide_kernel (65..255 nodes).
 #pragma once
 #include "common.cuh"
 
@@ -205,24 +207,29 @@ kahn_levels_deferred_kernel(const unsigned char *__restrict__ n_nodes, const uin
 // ---- large batches: one THREAD per DAG ---------------------------------------------------------------------------------
 // The warp kernel above spends ~2.6 K warp instructions per DAG on the order (profiles/r2e_summary.md): it is issue-bound,
 // and what it issues is mostly per-generation fixed cost.  For a batch large enough to fill the machine with threads the
-// literal algorithm is cheaper: each thread runs dag.py:218-240 on its own DAG -- bucket the edges by source in first-seen
-// order (DiGraph's adjacency order; a repeated edge is dropped there), count distinct parents, then a FIFO: the queue IS
-// topological_sort's order, and a node's level is its releasing parent's + 1.  About (4 E + 3 n) short steps per DAG.
-//   * a warp costs its longest lane, so a CTA takes C consecutive DAGs, counting-sorts them by edge count in shared
-//     memory and deals them out in groups of 32 neighbours of that order, heaviest group first; each warp pulls its next
-//     group from a CTA counter -- no barrier until the chunk is done;
+// literal algorithm is cheaper (563 instructions per DAG, profiles/r2k_summary.md): each thread runs dag.py:218-240 on its
+// own DAG -- bucket the edges by source in first-seen order (DiGraph's adjacency order; a repeated edge is dropped there),
+// count distinct parents, then a FIFO: the queue IS topological_sort's order, and a node's level is its releasing parent's
+// + 1.  About (4 E + 3 n) short steps per DAG.
+//   * the grid is resident at once and every CTA owns an equal, contiguous share of the batch (no CTA is left a chunk
+//     behind its neighbours); it takes the share in pieces of at most KF_MAXC DAGs;
+//   * a warp costs its longest lane, so the CTA counting-sorts a piece by the work each DAG is (4 E + 3 n) in shared memory
+//     and deals it out in groups of 32 neighbours of that order, heaviest group first; each warp pulls its next group
+//     from a CTA counter -- no barrier until the piece is done;
 //   * per-thread state lives in shared memory, word-interleaved across the lanes of a warp (word j of lane t at [j][t]):
 //     every access, whatever the index, is bank-conflict free; the bucketed children of a group share the warp's byte
 //     pool, and a group whose edges exceed it runs in several passes over fewer lanes;
 //   * edges are read twice from global memory, eight at a time (one 16-byte load per lane); levels go straight to the
 //     output row (one byte per release: the thread wrote the row's 0xFF fill itself, so program order holds);
+//   * counters are plain load-add-store on the lane's own words: shared-memory atomics in their place measured 5.7 x
+//     slower for the whole kernel (r2k);
 //   * a DAG whose edge list alone exceeds the pool (only possible with repeated edges) is handed back with status
 //     KAHN_DEFERRED for kahn_levels_deferred_kernel.
 #define KF_THREADS 128
 #define KF_WARPS (KF_THREADS / 32)
 #define KF_POOL 8192
 #define KF_BINS 1024
-#define KF_MAXC 1024          // DAGs a CTA sorts at a time, at most
+#define KF_MAXC 2304          // DAGs a CTA sorts at a time, at most (1 M DAGs over 148 x 3 CTAs: one piece each)
 #define KF_MIN_DAGS 262144    // below this the warp kernel wins: one thread walks its heaviest DAG for ~0.3 ms whatever the batch
 struct KfWarp {
     uint32_t start[32][32];    // 64 x u16 per DAG: out-degree -> list begin -> list end

@@ -7,7 +7,7 @@
 //   K3 select.cuh      radix top-k' selection / list reduction
 //   K4 rescore.cuh     exact fp64 rescoring, final sort, certificate; exact_scan.cuh: the fp64 scan behind it
 //   K5 merge.cuh       shard merge
-//   K6 kahn.cuh        batched Kahn levels (<= 64 nodes per warp; 65..255 nodes per CTA)
+//   K6 kahn.cuh        batched Kahn levels (<= 64 nodes: per warp, or per thread for large batches; 65..255 nodes per CTA)
 //      multi.cuh       one handle over several GPUs (worker thread per shard)
 //
 // There is no CPU implementation of any of these in the library: without a device every entry
@@ -92,7 +92,7 @@ extern "C" int mcp_device_count(void) {
 extern "C" const char *mcp_build_info(void) {
     return "mcp_b200 sm_100a nvcc " MCP_STR(__CUDACC_VER_MAJOR__) "." MCP_STR(__CUDACC_VER_MINOR__)
            " kernels: prep_rows prep_queries scan_fp32 gemm_tf32_tcgen05 (cta_group::1 / cta_group::2) select_from_scores"
-           " select_from_lists rescore_finalize exact_scan2 exact_pick exact_select shadow_rows merge_shards kahn_levels";
+           " select_from_lists rescore_finalize exact_scan2 exact_pick exact_select shadow_rows merge_shards kahn_levels kahn_fifo";
 }
 
 // ---------------------------------------------------------------------------------------------
