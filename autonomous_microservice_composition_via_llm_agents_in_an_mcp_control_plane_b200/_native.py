@@ -66,6 +66,7 @@ SIGNATURES = {
     "mcp_dag_levels_device": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "mcp_dag_levels_wide": (_i32, [_i32, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp]),
     "mcp_dag_levels_wide_device": (_i32, [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "mcp_dag_launch_count": (_i64, [_i32]),
     "mcp_last_error": (C.c_char_p, []),
     "mcp_device_count": (_i32, []),
     "mcp_build_info": (C.c_char_p, []),

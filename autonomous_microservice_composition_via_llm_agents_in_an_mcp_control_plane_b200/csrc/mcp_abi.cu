@@ -21,6 +21,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <condition_variable>
 #include <functional>
@@ -1323,6 +1324,9 @@ extern "C" int mcp_merge_topk_packed_device(const void *packed_device, int n_sha
 // ---------------------------------------------------------------------------------------------
 // DAG levels
 // ---------------------------------------------------------------------------------------------
+static std::atomic<int64_t> g_dag_launches[3];
+extern "C" int64_t mcp_dag_launch_count(int which) { return which >= 0 && which < 3 ? g_dag_launches[which].load() : -1; }
+
 static int dag_launch(int pitch, const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges, int64_t n_dags,
                       uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels, uint8_t *out_status, cudaStream_t st) {
     if (!n_nodes || !edge_off || !out_level || !out_n_levels || !out_status) return fail(MCP_EINVAL, "NULL buffer");
@@ -1368,12 +1372,15 @@ static int dag_launch(int pitch, const uint8_t *n_nodes, const uint32_t *edge_of
         else
             kahn_fifo_kernel<false><<<grid, KF_THREADS, smem, st>>>(n_nodes, edge_off, edges, n_dags, per_cta, sub, out_level, nullptr, out_n_levels, out_status);
         KCHECK();
+        ++g_dag_launches[1];
+        ++g_dag_launches[2];
         const int g2 = (int)std::min<int64_t>((int64_t)n_sm * 2, ((n_dags + 31) / 32 + KAHN_WARPS - 1) / KAHN_WARPS);
         if (out_order)
             kahn_levels_deferred_kernel<true><<<g2, KAHN_THREADS, 0, st>>>(n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
         else
             kahn_levels_deferred_kernel<false><<<g2, KAHN_THREADS, 0, st>>>(n_nodes, edge_off, edges, n_dags, out_level, nullptr, out_n_levels, out_status);
     } else if (pitch == 64) {
+        ++g_dag_launches[0];
         int64_t want = (n_dags + KAHN_WARPS - 1) / KAHN_WARPS;
         int grid = (int)std::min<int64_t>((int64_t)n_sm * 8, want);
         if (out_order)
@@ -1433,7 +1440,9 @@ static int dag_levels_host(int pitch, int max_nodes, int device_id, const uint8_
     std::lock_guard<std::mutex> lk(w.mu);
     if (!w.st) CU(cudaStreamCreateWithFlags(&w.st, cudaStreamNonBlocking));
     // device layout in: [edge_off | edges | n_nodes], out: [level | order | n_levels | status]
-    const size_t B = (size_t)n_dags, off_bytes = sizeof(uint32_t) * (B + 1), ed_bytes = (2 * n_edges + 3) & ~(size_t)3;
+    // (edges start on a 16-byte boundary: the thread-per-DAG kernel reads them 16 bytes at a time)
+    const size_t B = (size_t)n_dags, off_len = sizeof(uint32_t) * (B + 1), off_bytes = (off_len + 15) & ~(size_t)15;
+    const size_t ed_bytes = (2 * n_edges + 3) & ~(size_t)3;
     const size_t in_bytes = off_bytes + ed_bytes + B, lv_bytes = B * (size_t)pitch;
     const size_t out_bytes = lv_bytes * (out_order ? 2 : 1) + 2 * B;
     int rc;
@@ -1450,12 +1459,12 @@ static int dag_levels_host(int pitch, int max_nodes, int device_id, const uint8_
         w.h_cap = std::min<size_t>(want, DAG_PINNED_MAX);
     }
     if (staged) {
-        memcpy(w.h, edge_off, off_bytes);
+        memcpy(w.h, edge_off, off_len);
         if (n_edges) memcpy(w.h + off_bytes, edges, 2 * n_edges);
         memcpy(w.h + off_bytes + ed_bytes, n_nodes, B);
         CU(cudaMemcpyAsync(di, w.h, in_bytes, cudaMemcpyHostToDevice, w.st));
     } else {
-        CU(cudaMemcpyAsync(di, edge_off, off_bytes, cudaMemcpyHostToDevice, w.st));
+        CU(cudaMemcpyAsync(di, edge_off, off_len, cudaMemcpyHostToDevice, w.st));
         if (n_edges) CU(cudaMemcpyAsync(di + off_bytes, edges, 2 * n_edges, cudaMemcpyHostToDevice, w.st));
         CU(cudaMemcpyAsync(di + off_bytes + ed_bytes, n_nodes, B, cudaMemcpyHostToDevice, w.st));
     }

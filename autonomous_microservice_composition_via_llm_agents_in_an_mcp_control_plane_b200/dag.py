@@ -117,6 +117,12 @@ def levels(enc: EncodedDags, device: int = 0, with_order: bool = True) -> DagLev
     return DagLevels(level, order, nlev, status)
 
 
+def launch_counts() -> Dict[str, int]:
+    """Kernel launches so far in this process behind the <= 64-node entry points (``mcp_dag_launch_count``)."""
+    lib = nat.lib()
+    return {name: int(lib.mcp_dag_launch_count(i)) for i, name in enumerate(("warp", "thread", "handed_back"))}
+
+
 def levels_device(n_nodes, edge_off, edges, out=None, with_order: bool = True):
     """CUDA uint8 / int32-viewed-as-uint32 tensors in and out on the current stream (no copies)."""
     import torch

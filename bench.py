@@ -355,11 +355,28 @@ def dag_extra(torch, np, pkg, dev, n_dags):
     ed = torch.from_numpy(enc.edges).to(dev).contiguous()
     byts = enc.n_nodes.size * (1 + 4 + 64 + 2) + enc.edges.size
     for order in (True, False):
+        before = pkg.dag.launch_counts()
         outb = pkg.dag.levels_device(nn, off, ed, with_order=order)
         torch.cuda.synchronize()
         ms = time_steps(torch, lambda: pkg.dag.levels_device(nn, off, ed, out=outb, with_order=order), 10)
         b = byts + (enc.n_nodes.size * 64 if order else 0)
-        out["with_order" if order else "levels_only"] = {"ms": round(ms, 4), "dags_per_s": round(n_dags / ms * 1e3), "GBps": round(b / (ms * 1e-3) / 1e9, 1)}
+        after = pkg.dag.launch_counts()
+        out["with_order" if order else "levels_only"] = {
+            "ms": round(ms, 4), "dags_per_s": round(n_dags / ms * 1e3), "GBps": round(b / (ms * 1e-3) / 1e9, 1),
+            "kernel": "thread per DAG (kahn_fifo_kernel)" if after["thread"] > before["thread"] else "warp per DAG (kahn_levels_kernel)"}
+    # the warp-per-DAG kernel on the same batch with the order (what smaller batches run), for comparison
+    prev = os.environ.get("MCP_DAG_KERNEL")
+    os.environ["MCP_DAG_KERNEL"] = "warp"
+    try:
+        outb = pkg.dag.levels_device(nn, off, ed, with_order=True)
+        torch.cuda.synchronize()
+        ms = time_steps(torch, lambda: pkg.dag.levels_device(nn, off, ed, out=outb, with_order=True), 10)
+        out["with_order_warp_kernel_ms"] = round(ms, 4)
+    finally:
+        if prev is None:
+            os.environ.pop("MCP_DAG_KERNEL", None)
+        else:
+            os.environ["MCP_DAG_KERNEL"] = prev
     out["dags"] = n_dags
     # CPU: NetworkX, graph build included (the reference builds the DiGraph per request)
     import multiprocessing as mp

@@ -264,6 +264,11 @@ int mcp_dag_levels_wide_device(const uint8_t *n_nodes, const uint32_t *edge_off,
                                int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
                                uint8_t *out_n_levels, uint8_t *out_status, void *stream);
 
+/* Launches so far in this process of the kernel behind the <= 64-node pair: which = 0 the warp-per-DAG kernel, 1 the
+ * thread-per-DAG kernel, 2 the pass over the DAGs it handed back (launched with it every time; it finds work only when some
+ * DAG's edge list exceeded the thread kernel's pool).  For tests and benchmarks that must know which kernel answered.     */
+int64_t mcp_dag_launch_count(int which);
+
 /* ---- misc ------------------------------------------------------------------------------------ */
 const char *mcp_last_error(void);
 int mcp_device_count(void);          /* 0 when no CUDA device is usable */

@@ -97,9 +97,13 @@ def test_both_kernels_on_repeated_edges_self_loops_and_handed_back_dags(mcp, ora
     assert (np.diff(off.astype(np.int64)) > 8192).sum() >= 1
     enc = mcp.dag.EncodedDags(base.n_nodes, off, edges, [])
     level, order, nlev, status = oracle.dag_levels(enc.n_nodes, enc.edge_off, enc.edges)
+    before = mcp.dag.launch_counts()
     _same(mcp.dag.levels(enc), level, order, nlev, status)
     res = mcp.dag.levels(enc, with_order=False)
     assert np.array_equal(res.level, level) and np.array_equal(res.status, status)
+    after = mcp.dag.launch_counts()
+    ran = {k: after[k] - before[k] for k in after}
+    assert ran == ({"warp": 2, "thread": 0, "handed_back": 0} if kernel == "warp" else {"warp": 0, "thread": 2, "handed_back": 2}), ran
     g = np.load(GOLD / "dag_golden.npz")
     _same(mcp.dag.levels(mcp.dag.EncodedDags(g["n_nodes"], g["edge_off"], g["edges"], [])), g["level"], g["order"], g["n_levels"], g["status"])
     dev = torch.device("cuda:0")
@@ -118,10 +122,13 @@ def test_large_batch_takes_the_thread_per_dag_kernel_and_stays_bit_exact(mcp, or
     monkeypatch.delenv("MCP_DAG_KERNEL", raising=False)
     enc = mcp.dag.synthetic_dags(300_000, seed=31)
     level, order, nlev, status = oracle.dag_levels(enc.n_nodes, enc.edge_off, enc.edges)
+    before = mcp.dag.launch_counts()
     res = mcp.dag.levels(enc)
     _same(res, level, order, nlev, status)
+    assert mcp.dag.launch_counts()["thread"] == before["thread"] + 1        # the library's own choice at this size
     monkeypatch.setenv("MCP_DAG_KERNEL", "warp")
     _same(mcp.dag.levels(enc), level, order, nlev, status)
+    assert mcp.dag.launch_counts()["thread"] == before["thread"] + 1
 
 
 def test_device_api_and_invariants(mcp):
