@@ -253,40 +253,32 @@ __device__ __forceinline__ unsigned short *kf_h(unsigned char *col, int i) {
     return reinterpret_cast<unsigned short *>(col + (i & 0xFE) * 62 + 2 * i);
 }
 
-// f(u, v) for every edge of [e0, e1) with both ends below n.  `edges` is 16-byte aligned (the launcher checks).
+// f(u, v) for every edge of [e0, e1) with both ends below n, eight edges (one aligned 16-byte load) at a time; the first and
+// the last load of a DAG may cover neighbours' edges, which are masked off.  `edges` is 16-byte aligned (the launcher checks), so
+// a load never leaves the 16-byte granule that holds one of the DAG's own edges.
 template <class F>
 __device__ __forceinline__ void kf_edges(const unsigned char *__restrict__ edges, uint32_t e0, uint32_t e1, int n, F f) {
-    const unsigned short *e16 = reinterpret_cast<const unsigned short *>(edges);
-    uint32_t e = e0;
-    const uint32_t head_end = min(e1, (e0 + 7u) & ~7u);
-    for (; e < head_end; ++e) {
-        const unsigned x = __ldg(e16 + e);
-        const int u = x & 0xFF, v = x >> 8;
-        if (u < n && v < n) f(u, v);
-    }
-    if (e + 8 <= e1) {
-        uint4 q = __ldg(reinterpret_cast<const uint4 *>(e16 + e));
-        for (;;) {
-            const uint32_t en = e + 8;
-            const bool more = en + 8 <= e1;
-            uint4 qn = q;
-            if (more) qn = __ldg(reinterpret_cast<const uint4 *>(e16 + en));
-            const uint32_t ws[4] = {q.x, q.y, q.z, q.w};
+    if (e0 >= e1) return;
+    const uint32_t E = e1 - e0;
+    const uint4 *e128 = reinterpret_cast<const uint4 *>(edges);
+    uint32_t e = e0 & ~7u;
+    uint4 q = __ldg(e128 + (e >> 3));
+    for (;;) {
+        const uint32_t en = e + 8;
+        const bool more = en < e1;
+        uint4 qn = q;
+        if (more) qn = __ldg(e128 + (en >> 3));
+        const uint32_t ws[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int u0 = ws[j] & 0xFF, v0 = (ws[j] >> 8) & 0xFF, u1 = (ws[j] >> 16) & 0xFF, v1 = ws[j] >> 24;
-                if (u0 < n && v0 < n) f(u0, v0);
-                if (u1 < n && v1 < n) f(u1, v1);
-            }
-            e = en;
-            if (!more) break;
-            q = qn;
+        for (int j = 0; j < 4; ++j) {
+            const int u0 = ws[j] & 0xFF, v0 = (ws[j] >> 8) & 0xFF, u1 = (ws[j] >> 16) & 0xFF, v1 = ws[j] >> 24;
+            const uint32_t ra = e - e0 + 2 * j;                       // edge index within the DAG; wraps for a neighbour's edge in front
+            if (ra < E && u0 < n && v0 < n) f(u0, v0);
+            if (ra + 1 < E && u1 < n && v1 < n) f(u1, v1);
         }
-    }
-    for (; e < e1; ++e) {
-        const unsigned x = __ldg(e16 + e);
-        const int u = x & 0xFF, v = x >> 8;
-        if (u < n && v < n) f(u, v);
+        if (!more) break;
+        e = en;
+        q = qn;
     }
 }
 
@@ -329,14 +321,16 @@ __device__ __forceinline__ int kf_one_dag(KfWarp &w, const int lane, unsigned ch
     // 3: one pass over the bucketed children: flag repeats within a list, count distinct parents
     {
         u64 seen = 0;
+        uint32_t c = pl[0];
         for (uint32_t r = 0; r < acc; ++r) {
-            const uint32_t c = pl[r];
+            const uint32_t cn = pl[r + 1];                 // (the pool has room for the read past the last entry)
             if (c & 0x40) seen = 0;
             const int v = c & 0x3F;
             const u64 bit = 1ull << v;
             if (seen & bit) pl[r] = (unsigned char)(c | 0x80);
             else ++*kf_b(ci, v);
             seen |= bit;
+            c = cn;
         }
     }
     // 4: the queue.  Generation g + 1 starts where the queue's tail stood when the first node of generation g was taken.
