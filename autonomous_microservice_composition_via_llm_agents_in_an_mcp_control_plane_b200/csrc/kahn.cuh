@@ -2,7 +2,7 @@
 //
 // Stands for nx.topological_generations (networkx dag.py:218-240) on the DiGraph that
 // control_plane.py:94-100 builds.  One warp per DAG (<= 64 nodes): lane l owns nodes l and l+32.
-//   build   pred[v] = 64-bit mask of v's distinct predecessors (atomicOr: a duplicate edge sets
+//   build   pred[v] = 64-bit mask of v's distinct predecessors (atomicOr on its 32-bit half: a duplicate edge sets
 //           the same bit again, which is exactly DiGraph's "same edge collapses"; a self loop
 //           sets bit v of pred[v], so v can never become ready -> cycle)
 //   levels  generation L = { v not done : pred[v] & ~done == 0 }, found with two ballots; no
@@ -51,7 +51,8 @@ __device__ __forceinline__ void kahn_warp_dag(KahnWarp &w, const int lane, const
         __syncwarp();
         for (uint32_t e = e0 + lane; e < e1; e += 32) {
             uchar2 uv = ed[e];
-            if (uv.x < n && uv.y < n) atomicOr(&w.pred[uv.y], 1ull << uv.x);
+            // (a 32-bit OR on the half that holds the bit: native; the 64-bit form compiles to a compare-and-swap loop)
+            if (uv.x < n && uv.y < n) atomicOr(reinterpret_cast<unsigned *>(&w.pred[uv.y]) + (uv.x >> 5), 1u << (uv.x & 31));
         }
         __syncwarp();
         const u64 p0 = w.pred[lane], p1 = w.pred[lane + 32];
@@ -531,7 +532,7 @@ kahn_levels_wide_kernel(const unsigned char *__restrict__ n_nodes, const uint32_
         __syncthreads();
         for (uint32_t e = e0 + v; e < e1; e += KAHNW_THREADS) {
             const uchar2 uv = ed[e];
-            if (uv.x < n && uv.y < n) atomicOr(&w.pred[uv.y][uv.x >> 6], 1ull << (uv.x & 63));
+            if (uv.x < n && uv.y < n) atomicOr(reinterpret_cast<unsigned *>(&w.pred[uv.y][0]) + (uv.x >> 5), 1u << (uv.x & 31));
         }
         __syncthreads();
         u64 p[4];
