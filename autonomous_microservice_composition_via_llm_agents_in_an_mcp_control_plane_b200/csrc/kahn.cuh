@@ -60,6 +60,20 @@ __device__ __forceinline__ void kahn_warp_dag(KahnWarp &w, const int lane, const
         u64 done = 0;
         int level = 0;
         unsigned char l0 = 0xFF, l1 = 0xFF;
+        if (n <= 32) {                                   // (warp-uniform) every node and every predecessor bit in the low half
+            const unsigned q0 = (unsigned)p0;
+            unsigned done32 = 0;
+            for (;;) {
+                const bool r0 = ok0 && !((done32 >> lane) & 1u) && ((q0 & ~done32) == 0u);
+                const unsigned f = __ballot_sync(MCP_FULL, r0);
+                if (f == 0u) break;
+                if (r0) l0 = (unsigned char)level;
+                if (WITH_ORDER && lane == 0) w.fm[level] = (u64)f;
+                done32 |= f;
+                ++level;
+            }
+            done = (u64)done32;
+        } else
         for (;;) {
             bool r0 = ok0 && !((done >> lane) & 1ull) && ((p0 & ~done) == 0ull);
             bool r1 = ok1 && !((done >> (lane + 32)) & 1ull) && ((p1 & ~done) == 0ull);
