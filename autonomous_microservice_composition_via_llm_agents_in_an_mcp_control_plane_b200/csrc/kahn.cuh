@@ -245,7 +245,7 @@ kahn_levels_deferred_kernel(const unsigned char *__restrict__ n_nodes, const uin
 #define KF_POOL 8192
 #define KF_BINS 1024
 #define KF_MAXC 2304          // DAGs a CTA sorts at a time, at most (1 M DAGs over 148 x 3 CTAs: one piece each)
-#define KF_MIN_DAGS 262144    // below this the warp kernel wins: one thread walks its heaviest DAG for ~0.3 ms whatever the batch
+#define KF_MIN_DAGS 131072    // below ~100 K the warp kernel wins: one thread walks its heaviest DAG for ~0.3 ms whatever the batch
 struct KfWarp {
     uint32_t start[32][32];    // 64 x u16 per DAG: out-degree -> list begin -> list end
     uint32_t indeg[16][32];    // 64 x u8: distinct parents not yet done

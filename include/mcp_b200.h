@@ -246,7 +246,7 @@ int mcp_merge_topk_packed_device(const void *packed_device, int n_shards, int n_
  * once the workspace has seen a size a call allocates nothing, so the one-graph-per-request use in Orchestrator.execute
  * does not stall scans running on other streams.  The device variant enqueues on `stream`.
  * Two kernels stand behind the <= 64-node pair, with identical bytes out: one warp per DAG (any batch size), and from
- * 262,144 DAGs up, when the order is asked for, one thread per DAG (2.7 x faster at 1 M DAGs; it needs `edges`,
+ * 131,072 DAGs up, when the order is asked for, one thread per DAG (2.7 x faster at 1 M DAGs; it needs `edges`,
  * `out_level` and `out_order` 16-byte aligned -- otherwise the warp kernel runs).  Environment variable
  * MCP_DAG_KERNEL = warp | fifo forces one of them (measurement only).
  * The _wide pair is the same for plans of 65 .. MCP_MAX_WIDE_DAG_NODES nodes (the reference's topological_sort takes any
