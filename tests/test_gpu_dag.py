@@ -116,6 +116,27 @@ def test_both_kernels_on_repeated_edges_self_loops_and_handed_back_dags(mcp, ora
     assert (lv[1] == 0xFF).all() and (od[1] == 0xFF).all() and od[0, :3].cpu().tolist() == [0, 1, 2]
 
 
+@pytest.mark.parametrize("kernel", ["warp", "fifo"])
+def test_dense_plans_many_passes_over_the_pool(mcp, oracle, monkeypatch, kernel):
+    """3000 plans of 40..64 nodes with half or all of the forward pairs as edges (up to 2016 edges each, shuffled): a group of
+    32 such DAGs holds several times the thread-per-DAG kernel's pool, so it runs them a few lanes at a time."""
+    monkeypatch.setenv("MCP_DAG_KERNEL", kernel)
+    rng = np.random.default_rng(11)
+    nn, parts, off = [], [], [0]
+    for i in range(3000):
+        n = int(rng.integers(40, 65))
+        perm = rng.permutation(n).astype(np.uint8)
+        iu, ju = np.triu_indices(n, 1)
+        keep = np.ones(iu.size, bool) if i % 2 else rng.random(iu.size) < 0.5
+        e = np.stack([perm[iu[keep]], perm[ju[keep]]], axis=1).astype(np.uint8)
+        e = e[rng.permutation(len(e))]
+        nn.append(n); parts.append(e); off.append(off[-1] + len(e))
+    enc = mcp.dag.EncodedDags(np.asarray(nn, np.uint8), np.asarray(off, np.uint32), np.concatenate(parts), [])
+    level, order, nlev, status = oracle.dag_levels(enc.n_nodes, enc.edge_off, enc.edges)
+    assert status.sum() == 0 and nlev.max() == 64
+    _same(mcp.dag.levels(enc), level, order, nlev, status)
+
+
 def test_large_batch_takes_the_thread_per_dag_kernel_and_stays_bit_exact(mcp, oracle, monkeypatch):
     """300 K DAGs is past the library's own switch to the thread-per-DAG kernel (no override): same bytes as the oracle,
     and the same bytes as the warp kernel."""
