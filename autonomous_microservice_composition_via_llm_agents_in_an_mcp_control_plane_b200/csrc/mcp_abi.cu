@@ -1415,13 +1415,131 @@ extern "C" int mcp_dag_levels_wide_device(const uint8_t *n_nodes, const uint32_t
 // stream) and never touches the legacy default stream.  Calls on one device take turns (the lock is held for the call).
 struct DagWorkspace {
     std::mutex mu;
-    cudaStream_t st = nullptr;
+    cudaStream_t st = nullptr, st2 = nullptr;
     Buf in, out;
     unsigned char *h = nullptr;
     size_t h_cap = 0;
+    // large batches: pinned slots of the chunk pipeline (below)
+    unsigned char *hp = nullptr;
+    size_t hp_cap = 0;
+    cudaEvent_t done[3] = {nullptr, nullptr, nullptr};
 };
 static DagWorkspace g_dag_ws[NOALLOC_MAX_DEVICES_];
-#define DAG_PINNED_MAX (8u << 20)      // larger batches are copied straight from / to the caller's memory
+#define DAG_PINNED_MAX (8u << 20)      // larger batches are copied straight from / to the caller's memory, or piped in chunks
+#define DAG_PIPE_CHUNK 131072          // DAGs per chunk of the pipeline (= KF_MIN_DAGS: a full chunk takes the thread-per-DAG kernel)
+#define DAG_PIPE_SLOTS 3
+static_assert(DAG_PIPE_CHUNK >= KF_MIN_DAGS && DAG_PIPE_CHUNK % 16 == 0, "chunk size");
+
+// Large host batches (two chunks or more): the caller's arrays are pageable, so a plain cudaMemcpy of 300 MB each way is
+// what the call costs (1 M DAGs: 47 ms around a 1.2 ms kernel).  Here the batch goes through in chunks of DAG_PIPE_CHUNK
+// DAGs over three pinned slots and two streams: this thread copies chunk i into its slot and enqueues H2D, kernel, D2H;
+// a helper thread waits for chunk i's event and copies its results out; so the staging copies, both DMA directions and the
+// kernel overlap.  A chunk keeps ABSOLUTE edge offsets: its edges sit in the slot at the same address modulo 16 as in the
+// caller's array and the kernel gets the base pointer that makes edges[edge_off[b]] land on them (the thread-per-DAG kernel
+// wants that base 16-byte aligned).
+static int dag_levels_host_piped(DagWorkspace &w, int pitch, int device_id, const uint8_t *n_nodes, const uint32_t *edge_off,
+                                 const uint8_t *edges, int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
+                                 uint8_t *out_n_levels, uint8_t *out_status) {
+    const int64_t n_chunks = (n_dags + DAG_PIPE_CHUNK - 1) / DAG_PIPE_CHUNK;
+    const int n_out = out_order ? 2 : 1;
+    size_t in_cap = 0;
+    for (int64_t c = 0; c < n_chunks; ++c) {
+        const int64_t b0 = c * DAG_PIPE_CHUNK, b1 = std::min<int64_t>(n_dags, b0 + DAG_PIPE_CHUNK);
+        in_cap = std::max<size_t>(in_cap, 2 * (size_t)(edge_off[b1] - edge_off[b0]));
+    }
+    const size_t off_bytes = ((sizeof(uint32_t) * (DAG_PIPE_CHUNK + 1)) + 15) & ~(size_t)15;
+    const size_t ed_cap = (in_cap + 16 + 32 + 15) & ~(size_t)15;                  // shift (< 16) + the bytes + slack for the last aligned load
+    const size_t in_slot = (off_bytes + ed_cap + DAG_PIPE_CHUNK + 255) & ~(size_t)255;
+    const size_t out_slot = ((size_t)DAG_PIPE_CHUNK * pitch * n_out + 2 * (size_t)DAG_PIPE_CHUNK + 255) & ~(size_t)255;
+    int rc;
+    if ((rc = w.in.ensure(in_slot * DAG_PIPE_SLOTS))) return rc;
+    if ((rc = w.out.ensure(out_slot * DAG_PIPE_SLOTS))) return rc;
+    if ((in_slot + out_slot) * DAG_PIPE_SLOTS > w.hp_cap) {
+        if (w.hp) cudaFreeHost(w.hp);
+        w.hp = nullptr; w.hp_cap = 0;
+        CU(cudaMallocHost(&w.hp, (in_slot + out_slot) * DAG_PIPE_SLOTS));
+        w.hp_cap = (in_slot + out_slot) * DAG_PIPE_SLOTS;
+    }
+    if (!w.st2) CU(cudaStreamCreateWithFlags(&w.st2, cudaStreamNonBlocking));
+    for (int i = 0; i < DAG_PIPE_SLOTS; ++i)
+        if (!w.done[i]) CU(cudaEventCreateWithFlags(&w.done[i], cudaEventDisableTiming));
+    unsigned char *h_in = w.hp, *h_out = w.hp + in_slot * DAG_PIPE_SLOTS;
+
+    std::mutex mu;
+    std::condition_variable cv;
+    int64_t enqueued = 0, drained = 0;       // chunks whose work is on a stream / whose results are in the caller's arrays
+    bool failed = false;
+    std::thread drain([&] {
+        cudaSetDevice(device_id);
+        for (int64_t c = 0; c < n_chunks; ++c) {
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return enqueued > c || failed; });
+                if (enqueued <= c) return;                                    // the producer gave up before this chunk
+            }
+            const int slot = (int)(c % DAG_PIPE_SLOTS);
+            const bool ok = cudaEventSynchronize(w.done[slot]) == cudaSuccess;
+            if (ok) {
+                const int64_t b0 = c * DAG_PIPE_CHUNK, cnt = std::min<int64_t>(n_dags, b0 + DAG_PIPE_CHUNK) - b0;
+                const unsigned char *ho = h_out + out_slot * slot;
+                const size_t lv = (size_t)cnt * pitch;
+                memcpy(out_level + (size_t)b0 * pitch, ho, lv);
+                if (out_order) memcpy(out_order + (size_t)b0 * pitch, ho + lv, lv);
+                memcpy(out_n_levels + b0, ho + lv * n_out, (size_t)cnt);
+                memcpy(out_status + b0, ho + lv * n_out + cnt, (size_t)cnt);
+            }
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                if (!ok) failed = true;
+                drained = c + 1;
+            }
+            cv.notify_all();
+        }
+    });
+    rc = MCP_OK;
+    for (int64_t c = 0; c < n_chunks && rc == MCP_OK; ++c) {
+        const int slot = (int)(c % DAG_PIPE_SLOTS);
+        {
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait(lk, [&] { return drained + DAG_PIPE_SLOTS > c || failed; });      // the slot's previous chunk has left it
+            if (failed) { rc = fail(MCP_ECUDA, "DAG pipeline: a chunk failed on the device"); break; }
+        }
+        const int64_t b0 = c * DAG_PIPE_CHUNK, cnt = std::min<int64_t>(n_dags, b0 + DAG_PIPE_CHUNK) - b0;
+        const size_t e_first = edge_off[b0], e_bytes = 2 * (size_t)(edge_off[b0 + cnt] - e_first), shift = (2 * e_first) & 15;
+        unsigned char *hi = h_in + in_slot * slot, *di = w.in.as<unsigned char>() + in_slot * slot, *d_o = w.out.as<unsigned char>() + out_slot * slot;
+        memcpy(hi, edge_off + b0, sizeof(uint32_t) * (size_t)(cnt + 1));
+        if (e_bytes) memcpy(hi + off_bytes + shift, edges + 2 * e_first, e_bytes);
+        memcpy(hi + off_bytes + ed_cap, n_nodes + b0, (size_t)cnt);
+        cudaStream_t st = (c & 1) ? w.st2 : w.st;
+        const size_t lv = (size_t)cnt * pitch;
+        cudaError_t e = cudaMemcpyAsync(di, hi, off_bytes + ed_cap + (size_t)cnt, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) {
+            // edges[edge_off[b]] for b in this chunk must land on di + off_bytes + shift + 2 * (edge_off[b] - e_first)
+            const unsigned char *ed_base = reinterpret_cast<const unsigned char *>((uintptr_t)(di + off_bytes + shift) - 2 * (uintptr_t)e_first);
+            rc = dag_launch(pitch, di + off_bytes + ed_cap, reinterpret_cast<const uint32_t *>(di), ed_base, cnt, d_o, out_order ? d_o + lv : nullptr,
+                            d_o + lv * n_out, d_o + lv * n_out + cnt, st);
+            if (rc == MCP_OK) e = cudaMemcpyAsync(h_out + out_slot * slot, d_o, lv * n_out + 2 * (size_t)cnt, cudaMemcpyDeviceToHost, st);
+            if (rc == MCP_OK && e == cudaSuccess) e = cudaEventRecord(w.done[slot], st);
+        }
+        if (rc == MCP_OK && e != cudaSuccess) rc = fail(MCP_ECUDA, "DAG pipeline: %s", cudaGetErrorString(e));
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            if (rc == MCP_OK) enqueued = c + 1;
+            else failed = true;
+        }
+        cv.notify_all();
+    }
+    if (rc != MCP_OK) {
+        std::lock_guard<std::mutex> lk(mu);
+        failed = true;
+        cv.notify_all();
+    }
+    drain.join();
+    cudaStreamSynchronize(w.st);
+    cudaStreamSynchronize(w.st2);
+    if (rc == MCP_OK && failed) rc = fail(MCP_ECUDA, "DAG pipeline: a chunk failed on the device");
+    return rc;
+}
 
 static int dag_levels_host(int pitch, int max_nodes, int device_id, const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,
                            int64_t n_dags, uint8_t *out_level, uint8_t *out_order, uint8_t *out_n_levels, uint8_t *out_status) {
@@ -1439,6 +1557,8 @@ static int dag_levels_host(int pitch, int max_nodes, int device_id, const uint8_
     DagWorkspace &w = g_dag_ws[device_id];
     std::lock_guard<std::mutex> lk(w.mu);
     if (!w.st) CU(cudaStreamCreateWithFlags(&w.st, cudaStreamNonBlocking));
+    if (pitch == 64 && n_dags >= 2 * (int64_t)DAG_PIPE_CHUNK)
+        return dag_levels_host_piped(w, pitch, device_id, n_nodes, edge_off, edges, n_dags, out_level, out_order, out_n_levels, out_status);
     // device layout in: [edge_off | edges | n_nodes], out: [level | order | n_levels | status]
     // (edges start on a 16-byte boundary: the thread-per-DAG kernel reads them 16 bytes at a time)
     const size_t B = (size_t)n_dags, off_len = sizeof(uint32_t) * (B + 1), off_bytes = (off_len + 15) & ~(size_t)15;

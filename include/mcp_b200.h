@@ -244,7 +244,9 @@ int mcp_merge_topk_packed_device(const void *packed_device, int n_shards, int n_
  *                            the host variants refuse such a batch with MCP_EINVAL)
  * The host variant copies in/out on `device_id` through a per-device workspace that only grows and a stream of its own:
  * once the workspace has seen a size a call allocates nothing, so the one-graph-per-request use in Orchestrator.execute
- * does not stall scans running on other streams.  The device variant enqueues on `stream`.
+ * does not stall scans running on other streams.  A host batch of 262,144 DAGs or more is piped through in chunks (pinned
+ * slots, two streams, a helper thread for the results), so staging, both copy directions and the kernel overlap.  The device
+ * variant enqueues on `stream`.
  * Two kernels stand behind the <= 64-node pair, with identical bytes out: one warp per DAG (any batch size), and from
  * 131,072 DAGs up, when the order is asked for, one thread per DAG (2.7 x faster at 1 M DAGs; it needs `edges`,
  * `out_level` and `out_order` 16-byte aligned -- otherwise the warp kernel runs -- and reads `edges` in aligned 16-byte pieces,
