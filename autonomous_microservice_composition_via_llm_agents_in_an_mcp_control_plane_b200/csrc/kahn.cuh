@@ -242,7 +242,7 @@ kahn_levels_deferred_kernel(const unsigned char *__restrict__ n_nodes, const uin
 //     KAHN_DEFERRED for kahn_levels_deferred_kernel.
 #define KF_THREADS 128
 #define KF_WARPS (KF_THREADS / 32)
-#define KF_POOL 8192
+#define KF_POOL 9344          // bytes of bucketed children per warp (what 3 CTAs per SM leave after the per-thread state and the sort arrays)
 #define KF_BINS 1024
 #define KF_MAXC 2304          // DAGs a CTA sorts at a time, at most (1 M DAGs over 148 x 3 CTAs: one piece each)
 #define KF_MIN_DAGS 131072    // below ~100 K the warp kernel wins: one thread walks its heaviest DAG for ~0.3 ms whatever the batch
@@ -254,8 +254,7 @@ struct KfWarp {
 };
 struct KfSmem {
     KfWarp w[KF_WARPS];
-    unsigned short perm[KF_MAXC];   // position in the sorted order -> DAG of the chunk
-    unsigned short ecnt[KF_MAXC];   // position -> edge count
+    unsigned short perm[KF_MAXC];   // position in the sorted order -> DAG of the chunk (its edge count is read again from edge_off)
     uint32_t wsum[KF_WARPS];
     int next_group;
 };
@@ -408,7 +407,7 @@ kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__re
 #pragma unroll
     for (int j = 0; j < KF_BINS / KF_THREADS; ++j) hist[t + j * KF_THREADS] = 0;
     __syncthreads();
-    uint32_t ec[PER], key[PER], within[PER];
+    uint32_t key[PER], within[PER];
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
         const int i = t + j * KF_THREADS;
@@ -418,7 +417,6 @@ kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__re
             E = a1 < a0 ? 0xFFFFu : min(a1 - a0, 0xFFFFu);
             nn = n_nodes[b0 + i];
         }
-        ec[j] = E;
         key[j] = min((4u * E + 3u * nn) >> 1, (uint32_t)KF_BINS - 1u);      // ~ the steps the DAG will take
         within[j] = 0;
         if (i < padded) within[j] = atomicAdd(&hist[key[j]], 1u);
@@ -448,7 +446,6 @@ kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__re
         if (i < padded) {
             const uint32_t pos = hist[key[j]] + within[j];
             S.perm[pos] = (unsigned short)i;
-            S.ecnt[pos] = (unsigned short)ec[j];
         }
     }
     __syncthreads();                                       // the histogram is done with: warp 0's pool is a pool again
@@ -462,12 +459,17 @@ kahn_fifo_kernel(const unsigned char *__restrict__ n_nodes, const uint32_t *__re
         const int pos = (GROUPS - 1 - g) * 32 + lane;
         const int mine = S.perm[pos];
         const int64_t b = b0 + mine;
-        const uint32_t E16 = S.ecnt[pos];
         const bool valid = mine < cs;
+        uint32_t E16 = 0, e_first = 0;
+        if (valid) {
+            e_first = edge_off[b];
+            const uint32_t e_last = edge_off[b + 1];
+            E16 = e_last < e_first ? 0xFFFFu : min(e_last - e_first, 0xFFFFu);
+        }
         int n = valid ? n_nodes[b] : 0;
         const bool wide = n > 64, over = !wide && E16 > KF_POOL;
         const bool run = valid && !wide && !over;
-        const uint32_t e0 = run ? edge_off[b] : 0u;
+        const uint32_t e0 = run ? e_first : 0u;
         const uint32_t E = run ? E16 : 0u;
         if (!run) n = 0;
         uint32_t inc = E;
