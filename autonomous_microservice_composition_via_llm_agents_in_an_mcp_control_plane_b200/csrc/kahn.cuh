@@ -240,12 +240,12 @@ kahn_levels_deferred_kernel(const unsigned char *__restrict__ n_nodes, const uin
 //     slower for the whole kernel (r2k);
 //   * a DAG whose edge list alone exceeds the pool (only possible with repeated edges) is handed back with status
 //     KAHN_DEFERRED for kahn_levels_deferred_kernel.
-#define KF_THREADS 128
+#define KF_THREADS 160
 #define KF_WARPS (KF_THREADS / 32)
-#define KF_POOL 9344          // bytes of bucketed children per warp (what 3 CTAs per SM leave after the per-thread state and the sort arrays)
-#define KF_BINS 1024
-#define KF_MAXC 2304          // DAGs a CTA sorts at a time, at most (1 M DAGs over 148 x 3 CTAs: one piece each)
-#define KF_MIN_DAGS 131072    // below ~100 K the warp kernel wins: one thread walks its heaviest DAG for ~0.3 ms whatever the batch
+#define KF_POOL 13424         // bytes of bucketed children per warp (what 2 CTAs of 5 warps per SM leave after the per-thread state and the sort arrays)
+#define KF_BINS 1280
+#define KF_MAXC 3520          // DAGs a CTA sorts at a time, at most (1 M DAGs over 148 x 2 CTAs: one piece each)
+#define KF_MIN_DAGS 65536     // below ~50 K the warp kernel wins: one thread walks its heaviest DAG for ~0.17 ms whatever the batch
 struct KfWarp {
     uint32_t start[32][32];    // 64 x u16 per DAG: out-degree -> list begin -> list end
     uint32_t indeg[16][32];    // 64 x u8: distinct parents not yet done

@@ -1426,7 +1426,7 @@ struct DagWorkspace {
 };
 static DagWorkspace g_dag_ws[NOALLOC_MAX_DEVICES_];
 #define DAG_PINNED_MAX (8u << 20)      // larger batches are copied straight from / to the caller's memory, or piped in chunks
-#define DAG_PIPE_CHUNK 131072          // DAGs per chunk of the pipeline (= KF_MIN_DAGS: a full chunk takes the thread-per-DAG kernel)
+#define DAG_PIPE_CHUNK 131072          // DAGs per chunk of the pipeline (>= KF_MIN_DAGS: a full chunk takes the thread-per-DAG kernel)
 #define DAG_PIPE_SLOTS 3
 static_assert(DAG_PIPE_CHUNK >= KF_MIN_DAGS && DAG_PIPE_CHUNK % 16 == 0, "chunk size");
 

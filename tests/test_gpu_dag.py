@@ -78,7 +78,7 @@ def _with_repeats_and_noise(enc, seed=3):
         if i % 70 == 0:
             e = np.concatenate([e, np.array([[200, 1], [1, 99]], np.uint8)])
         if i in big:
-            e = np.concatenate([e] * (8192 // len(e) + 2))
+            e = np.concatenate([e] * (16384 // len(e) + 2))
         parts.append(e)
         off.append(off[-1] + len(e))
     return np.concatenate(parts), np.asarray(off, np.uint32)
@@ -94,7 +94,7 @@ def test_both_kernels_on_repeated_edges_self_loops_and_handed_back_dags(mcp, ora
     monkeypatch.setenv("MCP_DAG_KERNEL", kernel)
     base = mcp.dag.synthetic_dags(20_000, seed=77)
     edges, off = _with_repeats_and_noise(base)
-    assert (np.diff(off.astype(np.int64)) > 8192).sum() >= 1
+    assert (np.diff(off.astype(np.int64)) > 16384).sum() >= 1
     enc = mcp.dag.EncodedDags(base.n_nodes, off, edges, [])
     level, order, nlev, status = oracle.dag_levels(enc.n_nodes, enc.edge_off, enc.edges)
     before = mcp.dag.launch_counts()
