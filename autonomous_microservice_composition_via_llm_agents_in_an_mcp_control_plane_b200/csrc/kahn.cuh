@@ -222,7 +222,7 @@ kahn_levels_deferred_kernel(const unsigned char *__restrict__ n_nodes, const uin
 // ---- large batches: one THREAD per DAG ---------------------------------------------------------------------------------
 // The warp kernel above spends ~2.6 K warp instructions per DAG on the order (profiles/r2e_summary.md): it is issue-bound,
 // and what it issues is mostly per-generation fixed cost.  For a batch large enough to fill the machine with threads the
-// literal algorithm is cheaper (582 instructions per DAG, profiles/r2k_summary.md): each thread runs dag.py:218-240 on its
+// literal algorithm is cheaper (470 instructions per DAG, profiles/r2k_summary.md): each thread runs dag.py:218-240 on its
 // own DAG -- bucket the edges by source in first-seen order (DiGraph's adjacency order; a repeated edge is dropped there),
 // count distinct parents, then a FIFO: the queue IS topological_sort's order, and a node's level is its releasing parent's
 // + 1.  About (4 E + 3 n) short steps per DAG.

@@ -248,7 +248,7 @@ int mcp_merge_topk_packed_device(const void *packed_device, int n_shards, int n_
  * slots, two streams, a helper thread for the results), so staging, both copy directions and the kernel overlap.  The device
  * variant enqueues on `stream`.
  * Two kernels stand behind the <= 64-node pair, with identical bytes out: one warp per DAG (any batch size), and from
- * 131,072 DAGs up, when the order is asked for, one thread per DAG (2.7 x faster at 1 M DAGs; it needs `edges`,
+ * 65,536 DAGs up, when the order is asked for, one thread per DAG (2.7 x faster at 1 M DAGs; it needs `edges`,
  * `out_level` and `out_order` 16-byte aligned -- otherwise the warp kernel runs -- and reads `edges` in aligned 16-byte pieces,
  * so the buffer must be readable up to the 16-byte boundary after its last edge, as any cudaMalloc'd buffer is).  Environment variable
  * MCP_DAG_KERNEL = warp | fifo forces one of them (measurement only).
