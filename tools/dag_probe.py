@@ -3,7 +3,8 @@
 kernel (MCP_DAG_KERNEL = warp | fifo, MCP_DAG_SUB = DAGs a CTA sorts at a time; unset = the library's own choice), at
 several batch sizes, and a bit-for-bit comparison of every output of the thread-per-DAG kernel against the warp kernel's.
 
-  python tools/dag_probe.py [n_dags] [dup]        dup: every edge list repeated (reversed) -- repeated edges must collapse
+  python tools/dag_probe.py [n_dags] [dup|tiny]   dup: every edge list repeated (reversed) -- repeated edges must collapse;
+                                                  tiny: plans of 2..10 nodes
 """
 import os
 import sys
@@ -17,10 +18,21 @@ import autonomous_microservice_composition_via_llm_agents_in_an_mcp_control_plan
 
 n_max = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 dup = len(sys.argv) > 2 and sys.argv[2] == "dup"
+tiny = len(sys.argv) > 2 and sys.argv[2] == "tiny"
 dev = torch.device("cuda:0")
 enc = pkg.dag.synthetic_dags(n_max, seed=4004)
 edges = enc.edges
 edge_off = enc.edge_off
+if tiny:     # plans the size a planner emits: 2..10 nodes, every forward pair an edge with probability 0.3
+    rng = np.random.default_rng(77)
+    nn_t = rng.integers(2, 11, n_max).astype(np.uint8)
+    iu, ju = np.triu_indices(10, 1)
+    keep = (rng.random((n_max, iu.size)) < 0.3) & (ju[None, :] < nn_t[:, None])
+    cnt = keep.sum(1)
+    rows, cols = np.nonzero(keep)
+    edges = np.stack([iu[cols], ju[cols]], axis=1).astype(np.uint8)
+    edge_off = np.concatenate([[0], np.cumsum(cnt)]).astype(np.uint32)
+    enc = pkg.dag.EncodedDags(nn_t, edge_off, edges, [])
 if dup:
     parts, off = [], [0]
     for i in range(n_max):
@@ -32,7 +44,7 @@ if dup:
 nn_all = torch.from_numpy(enc.n_nodes).to(dev)
 off_all = torch.from_numpy(edge_off.view(np.int32)).to(dev)
 ed = torch.from_numpy(np.ascontiguousarray(edges)).to(dev).contiguous()
-sizes = [n for n in (4096, 16384, 50_000, 100_000, 200_000, 400_000) if n < n_max] + [n_max]
+sizes = [n for n in (1024, 4096, 16384, 50_000, 100_000, 200_000, 400_000) if n < n_max] + [n_max]
 choices = [("warp", None), ("fifo", "1024"), ("fifo", None), (None, None)]
 if os.environ.get("DAG_PROBE_ONLY"):        # one size, the library's own choice after the reference: for an ncu capture
     sizes, choices = [n_max], [("warp", None), (None, None)]
