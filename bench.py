@@ -378,6 +378,18 @@ def dag_extra(torch, np, pkg, dev, n_dags):
         else:
             os.environ["MCP_DAG_KERNEL"] = prev
     out["dags"] = n_dags
+    # the same batch through the host-buffer entry point (pageable numpy arrays in and out: mcp_dag_levels)
+    try:
+        pkg.dag.levels(enc)
+        ts = []
+        for _ in range(3):
+            t0 = time.perf_counter()
+            pkg.dag.levels(enc)
+            ts.append(time.perf_counter() - t0)
+        out["with_order_host_buffers_ms"] = round(min(ts) * 1e3, 2)
+        out["host_bytes_moved"] = int(enc.n_nodes.size * (1 + 4 + 64 + 64 + 2) + enc.edges.size)
+    except Exception as ex:  # noqa: BLE001
+        out["with_order_host_buffers_ms"] = {"error": str(ex)[:200]}
     # CPU: NetworkX, graph build included (the reference builds the DiGraph per request)
     import multiprocessing as mp
 
