@@ -1422,21 +1422,21 @@ struct DagWorkspace {
     // large batches: pinned slots of the chunk pipeline (below)
     unsigned char *hp = nullptr;
     size_t hp_cap = 0;
-    cudaEvent_t done[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t done[4] = {nullptr, nullptr, nullptr, nullptr};
 };
 static DagWorkspace g_dag_ws[NOALLOC_MAX_DEVICES_];
 #define DAG_PINNED_MAX (8u << 20)      // larger batches are copied straight from / to the caller's memory, or piped in chunks
 #define DAG_PIPE_CHUNK 131072          // DAGs per chunk of the pipeline (>= KF_MIN_DAGS: a full chunk takes the thread-per-DAG kernel)
-#define DAG_PIPE_SLOTS 3
+#define DAG_PIPE_SLOTS 4               // two per lane
 static_assert(DAG_PIPE_CHUNK >= KF_MIN_DAGS && DAG_PIPE_CHUNK % 16 == 0, "chunk size");
 
 // Large host batches (two chunks or more): the caller's arrays are pageable, so a plain cudaMemcpy of 300 MB each way is
 // what the call costs (1 M DAGs: 47 ms around a 1.2 ms kernel).  Here the batch goes through in chunks of DAG_PIPE_CHUNK
-// DAGs over three pinned slots and two streams: this thread copies chunk i into its slot and enqueues H2D, kernel, D2H;
-// a helper thread waits for chunk i's event and copies its results out; so the staging copies, both DMA directions and the
-// kernel overlap.  A chunk keeps ABSOLUTE edge offsets: its edges sit in the slot at the same address modulo 16 as in the
-// caller's array and the kernel gets the base pointer that makes edges[edge_off[b]] land on them (the thread-per-DAG kernel
-// wants that base 16-byte aligned).
+// DAGs in two lanes (even chunks / odd chunks), each with two pinned slots, a stream of its own and two threads: one copies
+// chunk i into its slot and enqueues H2D, kernel, D2H, the other waits for chunk i's event and copies its results out; so
+// the staging copies (two cores each way), both DMA directions and the kernels overlap.  A chunk keeps ABSOLUTE edge
+// offsets: its edges sit in the slot at the same address modulo 16 as in the caller's array and the kernel gets the base
+// pointer that makes edges[edge_off[b]] land on them (the thread-per-DAG kernel wants that base 16-byte aligned).
 static int dag_levels_host_piped(DagWorkspace &w, int pitch, int device_id, const uint8_t *n_nodes, const uint32_t *edge_off,
                                  const uint8_t *edges, int64_t n_dags, uint8_t *out_level, uint8_t *out_order,
                                  uint8_t *out_n_levels, uint8_t *out_status) {
@@ -1465,80 +1465,90 @@ static int dag_levels_host_piped(DagWorkspace &w, int pitch, int device_id, cons
         if (!w.done[i]) CU(cudaEventCreateWithFlags(&w.done[i], cudaEventDisableTiming));
     unsigned char *h_in = w.hp, *h_out = w.hp + in_slot * DAG_PIPE_SLOTS;
 
-    std::mutex mu;
-    std::condition_variable cv;
-    int64_t enqueued = 0, drained = 0;       // chunks whose work is on a stream / whose results are in the caller's arrays
-    bool failed = false;
-    std::thread drain([&] {
+    struct LaneResult { int rc = MCP_OK; std::string msg; };
+    auto lane_fn = [&](const int lane, LaneResult &res) {
         cudaSetDevice(device_id);
-        for (int64_t c = 0; c < n_chunks; ++c) {
+        cudaStream_t st = lane ? w.st2 : w.st;
+        const int64_t mine = (n_chunks - lane + 1) / 2;                       // chunks lane, lane + 2, ...
+        std::mutex mu;
+        std::condition_variable cv;
+        int64_t enqueued = 0, drained = 0;   // of this lane's chunks: work on the stream / results in the caller's arrays
+        bool failed = false;
+        std::thread drain([&] {
+            cudaSetDevice(device_id);
+            for (int64_t k = 0; k < mine; ++k) {
+                {
+                    std::unique_lock<std::mutex> lk(mu);
+                    cv.wait(lk, [&] { return enqueued > k || failed; });
+                    if (enqueued <= k) return;                                // the producer gave up before this chunk
+                }
+                const int slot = lane * 2 + (int)(k & 1);
+                const bool ok = cudaEventSynchronize(w.done[slot]) == cudaSuccess;
+                if (ok) {
+                    const int64_t b0 = (lane + 2 * k) * (int64_t)DAG_PIPE_CHUNK, cnt = std::min<int64_t>(n_dags, b0 + DAG_PIPE_CHUNK) - b0;
+                    const unsigned char *ho = h_out + out_slot * slot;
+                    const size_t lv = (size_t)cnt * pitch;
+                    memcpy(out_level + (size_t)b0 * pitch, ho, lv);
+                    if (out_order) memcpy(out_order + (size_t)b0 * pitch, ho + lv, lv);
+                    memcpy(out_n_levels + b0, ho + lv * n_out, (size_t)cnt);
+                    memcpy(out_status + b0, ho + lv * n_out + cnt, (size_t)cnt);
+                }
+                {
+                    std::lock_guard<std::mutex> lk(mu);
+                    if (!ok) failed = true;
+                    drained = k + 1;
+                }
+                cv.notify_all();
+            }
+        });
+        for (int64_t k = 0; k < mine && res.rc == MCP_OK; ++k) {
+            const int slot = lane * 2 + (int)(k & 1);
             {
                 std::unique_lock<std::mutex> lk(mu);
-                cv.wait(lk, [&] { return enqueued > c || failed; });
-                if (enqueued <= c) return;                                    // the producer gave up before this chunk
+                cv.wait(lk, [&] { return drained + 2 > k || failed; });       // the slot's previous chunk has left it
+                if (failed) break;
             }
-            const int slot = (int)(c % DAG_PIPE_SLOTS);
-            const bool ok = cudaEventSynchronize(w.done[slot]) == cudaSuccess;
-            if (ok) {
-                const int64_t b0 = c * DAG_PIPE_CHUNK, cnt = std::min<int64_t>(n_dags, b0 + DAG_PIPE_CHUNK) - b0;
-                const unsigned char *ho = h_out + out_slot * slot;
-                const size_t lv = (size_t)cnt * pitch;
-                memcpy(out_level + (size_t)b0 * pitch, ho, lv);
-                if (out_order) memcpy(out_order + (size_t)b0 * pitch, ho + lv, lv);
-                memcpy(out_n_levels + b0, ho + lv * n_out, (size_t)cnt);
-                memcpy(out_status + b0, ho + lv * n_out + cnt, (size_t)cnt);
+            const int64_t b0 = (lane + 2 * k) * (int64_t)DAG_PIPE_CHUNK, cnt = std::min<int64_t>(n_dags, b0 + DAG_PIPE_CHUNK) - b0;
+            const size_t e_first = edge_off[b0], e_bytes = 2 * (size_t)(edge_off[b0 + cnt] - e_first), shift = (2 * e_first) & 15;
+            unsigned char *hi = h_in + in_slot * slot, *di = w.in.as<unsigned char>() + in_slot * slot, *d_o = w.out.as<unsigned char>() + out_slot * slot;
+            memcpy(hi, edge_off + b0, sizeof(uint32_t) * (size_t)(cnt + 1));
+            if (e_bytes) memcpy(hi + off_bytes + shift, edges + 2 * e_first, e_bytes);
+            memcpy(hi + off_bytes + ed_cap, n_nodes + b0, (size_t)cnt);
+            const size_t lv = (size_t)cnt * pitch;
+            cudaError_t e = cudaMemcpyAsync(di, hi, off_bytes + ed_cap + (size_t)cnt, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) {
+                // edges[edge_off[b]] for b in this chunk must land on di + off_bytes + shift + 2 * (edge_off[b] - e_first)
+                const unsigned char *ed_base = reinterpret_cast<const unsigned char *>((uintptr_t)(di + off_bytes + shift) - 2 * (uintptr_t)e_first);
+                res.rc = dag_launch(pitch, di + off_bytes + ed_cap, reinterpret_cast<const uint32_t *>(di), ed_base, cnt, d_o, out_order ? d_o + lv : nullptr,
+                                    d_o + lv * n_out, d_o + lv * n_out + cnt, st);
+                if (res.rc != MCP_OK) res.msg = mcp_last_error();
+                if (res.rc == MCP_OK) e = cudaMemcpyAsync(h_out + out_slot * slot, d_o, lv * n_out + 2 * (size_t)cnt, cudaMemcpyDeviceToHost, st);
+                if (res.rc == MCP_OK && e == cudaSuccess) e = cudaEventRecord(w.done[slot], st);
             }
+            if (res.rc == MCP_OK && e != cudaSuccess) { res.rc = MCP_ECUDA; res.msg = std::string("DAG pipeline: ") + cudaGetErrorString(e); }
             {
                 std::lock_guard<std::mutex> lk(mu);
-                if (!ok) failed = true;
-                drained = c + 1;
+                if (res.rc == MCP_OK) enqueued = k + 1;
+                else failed = true;
             }
             cv.notify_all();
         }
-    });
-    rc = MCP_OK;
-    for (int64_t c = 0; c < n_chunks && rc == MCP_OK; ++c) {
-        const int slot = (int)(c % DAG_PIPE_SLOTS);
-        {
-            std::unique_lock<std::mutex> lk(mu);
-            cv.wait(lk, [&] { return drained + DAG_PIPE_SLOTS > c || failed; });      // the slot's previous chunk has left it
-            if (failed) { rc = fail(MCP_ECUDA, "DAG pipeline: a chunk failed on the device"); break; }
-        }
-        const int64_t b0 = c * DAG_PIPE_CHUNK, cnt = std::min<int64_t>(n_dags, b0 + DAG_PIPE_CHUNK) - b0;
-        const size_t e_first = edge_off[b0], e_bytes = 2 * (size_t)(edge_off[b0 + cnt] - e_first), shift = (2 * e_first) & 15;
-        unsigned char *hi = h_in + in_slot * slot, *di = w.in.as<unsigned char>() + in_slot * slot, *d_o = w.out.as<unsigned char>() + out_slot * slot;
-        memcpy(hi, edge_off + b0, sizeof(uint32_t) * (size_t)(cnt + 1));
-        if (e_bytes) memcpy(hi + off_bytes + shift, edges + 2 * e_first, e_bytes);
-        memcpy(hi + off_bytes + ed_cap, n_nodes + b0, (size_t)cnt);
-        cudaStream_t st = (c & 1) ? w.st2 : w.st;
-        const size_t lv = (size_t)cnt * pitch;
-        cudaError_t e = cudaMemcpyAsync(di, hi, off_bytes + ed_cap + (size_t)cnt, cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess) {
-            // edges[edge_off[b]] for b in this chunk must land on di + off_bytes + shift + 2 * (edge_off[b] - e_first)
-            const unsigned char *ed_base = reinterpret_cast<const unsigned char *>((uintptr_t)(di + off_bytes + shift) - 2 * (uintptr_t)e_first);
-            rc = dag_launch(pitch, di + off_bytes + ed_cap, reinterpret_cast<const uint32_t *>(di), ed_base, cnt, d_o, out_order ? d_o + lv : nullptr,
-                            d_o + lv * n_out, d_o + lv * n_out + cnt, st);
-            if (rc == MCP_OK) e = cudaMemcpyAsync(h_out + out_slot * slot, d_o, lv * n_out + 2 * (size_t)cnt, cudaMemcpyDeviceToHost, st);
-            if (rc == MCP_OK && e == cudaSuccess) e = cudaEventRecord(w.done[slot], st);
-        }
-        if (rc == MCP_OK && e != cudaSuccess) rc = fail(MCP_ECUDA, "DAG pipeline: %s", cudaGetErrorString(e));
         {
             std::lock_guard<std::mutex> lk(mu);
-            if (rc == MCP_OK) enqueued = c + 1;
-            else failed = true;
+            if (res.rc != MCP_OK) failed = true;
         }
         cv.notify_all();
-    }
-    if (rc != MCP_OK) {
-        std::lock_guard<std::mutex> lk(mu);
-        failed = true;
-        cv.notify_all();
-    }
-    drain.join();
-    cudaStreamSynchronize(w.st);
-    cudaStreamSynchronize(w.st2);
-    if (rc == MCP_OK && failed) rc = fail(MCP_ECUDA, "DAG pipeline: a chunk failed on the device");
-    return rc;
+        drain.join();
+        cudaStreamSynchronize(st);
+        if (res.rc == MCP_OK && failed) { res.rc = MCP_ECUDA; res.msg = "DAG pipeline: a chunk failed on the device"; }
+    };
+    LaneResult r0, r1;
+    std::thread other(lane_fn, 1, std::ref(r1));
+    lane_fn(0, r0);
+    other.join();
+    if (r0.rc != MCP_OK) return fail(r0.rc, "%s", r0.msg.c_str());
+    if (r1.rc != MCP_OK) return fail(r1.rc, "%s", r1.msg.c_str());
+    return MCP_OK;
 }
 
 static int dag_levels_host(int pitch, int max_nodes, int device_id, const uint8_t *n_nodes, const uint32_t *edge_off, const uint8_t *edges,

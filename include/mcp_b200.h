@@ -245,7 +245,7 @@ int mcp_merge_topk_packed_device(const void *packed_device, int n_shards, int n_
  * The host variant copies in/out on `device_id` through a per-device workspace that only grows and a stream of its own:
  * once the workspace has seen a size a call allocates nothing, so the one-graph-per-request use in Orchestrator.execute
  * does not stall scans running on other streams.  A host batch of 262,144 DAGs or more is piped through in chunks (pinned
- * slots, two streams, a helper thread for the results), so staging, both copy directions and the kernel overlap.  The device
+ * slots, two streams, three helper threads for the duration of the call), so staging, both copy directions and the kernel overlap.  The device
  * variant enqueues on `stream`.
  * Two kernels stand behind the <= 64-node pair, with identical bytes out: one warp per DAG (any batch size), and from
  * 65,536 DAGs up, when the order is asked for, one thread per DAG (2.7 x faster at 1 M DAGs; it needs `edges`,
