@@ -260,6 +260,8 @@ struct KfSmem {
 };
 static_assert(KF_BINS * sizeof(uint32_t) <= KF_POOL, "the sort's histogram borrows warp 0's pool");
 static_assert(KF_MAXC % KF_THREADS == 0 && KF_MAXC <= 65535, "perm is 16-bit; each thread sorts KF_MAXC / KF_THREADS entries");
+static_assert(KF_BINS % KF_THREADS == 0 && KF_POOL <= 32767, "each thread scans KF_BINS / KF_THREADS bins; list offsets are 16-bit");
+static_assert(2 * (sizeof(KfSmem) + 1024) <= 232448, "two CTAs per SM");
 
 // Byte i / half-word i of a lane's column, given the column's base (&a[0][lane]): word i >> 2 (i >> 1) sits 128 bytes on.
 __device__ __forceinline__ unsigned char *kf_b(unsigned char *col, int i) { return col + (i & 0xFC) * 31 + i; }
